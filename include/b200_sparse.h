@@ -1,0 +1,194 @@
+/*
+ * b200_sparse.h — C ABI of the B200-native sparse hot path (libb200sparse.so).
+ *
+ * Every entry point takes raw DEVICE pointers, sizes and a cudaStream_t (passed as
+ * void*), launches on that stream without any device-wide synchronisation, and returns
+ * 0 on success or a cudaError_t / negative B200_E* code.  No torch types cross this
+ * boundary; the Python host layer (torchrec-oldfork_b200/fbgemm_gpu) binds it with
+ * ctypes and registers the torch.ops.fbgemm.* operators on top of it.
+ *
+ * Each function cites the reference interface it replaces.  Paths are relative to the
+ * reference checkout; "fbgemm_gpu/" abbreviates third_party/fbgemm/fbgemm_gpu/.
+ */
+#ifndef B200_SPARSE_H_
+#define B200_SPARSE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* dtype codes shared by all entry points */
+enum {
+  B200_I32 = 0,
+  B200_I64 = 1,
+  B200_F32 = 2,
+  B200_F16 = 3,
+  B200_BF16 = 4,
+  B200_U8 = 5
+};
+
+/* error codes below zero are ours; positive values are cudaError_t */
+enum {
+  B200_OK = 0,
+  B200_EINVAL = -1,      /* bad argument combination */
+  B200_EUNSUPPORTED = -2 /* valid in the reference, not built here */
+};
+
+enum { B200_POOL_SUM = 0, B200_POOL_MEAN = 1 };
+enum { B200_OPT_SGD = 0, B200_OPT_ROWWISE_ADAGRAD = 1 };
+enum { B200_BOUNDS_FATAL = 0, B200_BOUNDS_WARNING = 1, B200_BOUNDS_IGNORE = 2 };
+enum { B200_CUMSUM_COMPLETE = 0, B200_CUMSUM_INCLUSIVE = 1, B200_CUMSUM_EXCLUSIVE = 2 };
+
+/* Human-readable text for a return code of any function below. */
+const char* b200_error_string(int code);
+/* Library/ABI version, bumped when a signature changes. */
+int b200_abi_version(void);
+/* Bytes of the small fixed scratch area (`ws`) the scan-based ops need. */
+size_t b200_scan_workspace_bytes(void);
+
+/* ---------------------------------------------------------------- jagged integer ops */
+
+/* torch.ops.fbgemm.asynchronous_{complete,inclusive,exclusive}_cumsum
+ * (fbgemm_gpu/src/sparse_ops.cu:189,226,263; CPU twin sparse_ops_cpu.cpp:1028-1090).
+ * complete: out has n+1 entries, out[0]=0.  dtype is B200_I32 or B200_I64. */
+int b200_cumsum(const void* in, void* out, int64_t n, int dtype, int mode, void* ws,
+                void* stream);
+
+/* torch.ops.fbgemm.permute_2D_sparse_data (fbgemm_gpu/src/sparse_ops.cu:309-486; CPU
+ * sparse_ops_cpu.cpp:512) and, with B == 1, permute_1D_sparse_data (sparse_ops.cu:490-665).
+ * lengths is [T, B]; permute is int32[Tp] with entries in [0, T) (duplicates allowed).
+ * Step 1 writes out_lengths [Tp, B] and the two exclusive scans (in_offsets [T*B+1],
+ * out_offsets [Tp*B+1], both int64 scratch supplied by the caller).  Step 2 copies the
+ * value (and optional weight) segments.  out_offsets[Tp*B] is the permuted total.  */
+int b200_permute_lengths(const int32_t* permute, const void* lengths, int lengths_dtype,
+                         int32_t T, int32_t Tp, int32_t B, void* out_lengths,
+                         int64_t* in_offsets, int64_t* out_offsets, void* ws, void* stream);
+int b200_permute_data(const int32_t* permute, int32_t Tp, int32_t B,
+                      const int64_t* in_offsets, const int64_t* out_offsets,
+                      const void* values, void* out_values, int value_bytes,
+                      const void* weights, void* out_weights, int weight_bytes,
+                      int64_t out_capacity, void* stream);
+
+/* torch.ops.fbgemm.expand_into_jagged_permute (fbgemm_gpu/src/sparse_ops.cu:671-730). */
+int b200_expand_into_jagged_permute(const int32_t* permute, const void* input_offsets,
+                                    const void* output_offsets, int dtype, int64_t permute_size,
+                                    void* output_permute, int64_t output_size, void* stream);
+
+/* torch.ops.fbgemm.offsets_range (fbgemm_gpu/src/sparse_ops.cu:62-187). */
+int b200_offsets_range(const void* offsets, int dtype, int64_t n_offsets, void* out,
+                       int64_t range_size, void* stream);
+
+/* torch.ops.fbgemm.block_bucketize_sparse_features (fbgemm_gpu/src/sparse_ops.cu:736-1228;
+ * unsigned arithmetic of kernel1/kernel2 :759-761,806-812).  lengths [T*B] (offset dtype),
+ * indices [N] (index dtype), block_sizes [T] (index dtype).  new_lengths is [W*T*B].
+ * Scratch: offsets [T*B+1] and new_offsets [W*T*B+1], both int64.  Optional outputs may
+ * be NULL.  Output order inside a bucket keeps the in-bag order of the input. */
+int b200_block_bucketize(const void* lengths, int offset_dtype, const void* indices,
+                         int index_dtype, const void* block_sizes, int32_t T, int32_t B,
+                         int32_t W, int64_t N, const float* weights, void* new_lengths,
+                         void* new_indices, float* new_weights, void* new_pos,
+                         void* unbucketize_permute, int64_t* offsets_scratch,
+                         int64_t* new_offsets_scratch, void* ws, void* stream);
+
+/* torch.ops.fbgemm.bounds_check_indices (fbgemm_gpu/codegen/embedding_bounds_check.cu:12-110).
+ * In-place on indices / offsets.  warning is int64[1] (count of violations). */
+int b200_bounds_check(const int64_t* rows_per_table, void* indices, void* offsets, int dtype,
+                      int32_t T, int32_t B, int64_t num_indices, int mode, int64_t* warning,
+                      void* ws, void* stream);
+
+/* ---------------------------------------------------------------- pooled lookup (TBE) */
+
+/* split_embedding_codegen_forward_{un,}weighted_cuda
+ * (fbgemm_gpu/codegen/embedding_forward_split_template.cu:43-474).
+ * weights: flat table-concatenated buffer; weights_offsets int64[T] (element offsets);
+ * D_offsets int32[T+1]; offsets [T*B+1] table-major; output [B, total_D] row-major.
+ * per_sample_weights may be NULL.  All D must be multiples of 4. */
+int b200_tbe_forward(const void* weights, int weight_dtype, const int64_t* weights_offsets,
+                     const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
+                     int32_t max_D, int32_t all_D_mult8, const void* indices,
+                     const void* offsets, int index_dtype, const float* per_sample_weights,
+                     int pooling_mode, void* output, int output_dtype, void* stream);
+
+/* transpose_embedding_input (fbgemm_gpu/src/split_embeddings_utils.cu:63-306): linearise
+ * (table,row) keys and sort them stably.  sorted_keys holds uint32 keys when key_bits <= 32,
+ * else uint64.  sorted_payload holds b_t = t*B+b, or the original position p when
+ * payload_is_position != 0 (weighted lookups); bag_of_pos (int32[N], may be NULL unless
+ * payload_is_position) receives b_t per position.  sort_ws/sort_ws_bytes from the query. */
+size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits);
+int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
+                          const int64_t* hash_size_cumsum, int32_t T, int32_t B, int64_t N,
+                          int key_bits, int payload_is_position, void* sorted_keys,
+                          int32_t* sorted_payload, int32_t* bag_of_pos, void* sort_ws,
+                          size_t sort_ws_bytes, void* stream);
+
+/* split_embedding_backward_codegen_{sgd,rowwise_adagrad}_{un,}weighted_exact_cuda
+ * (fbgemm_gpu/codegen/embedding_backward_split_template.cu:81-1138, optimizer bodies
+ * embedding_backward_code_generator.py:376-401,629-632).  Consumes the sorted keys,
+ * reduces grad_output rows per unique (table,row) in sorted order (deterministic) and
+ * applies the optimizer in place.  partial_scratch: b200_tbe_backward_scratch_bytes(). */
+size_t b200_tbe_backward_scratch_bytes(int64_t N, int32_t max_D);
+int b200_tbe_backward(const float* grad_output, int64_t grad_stride, const void* sorted_keys,
+                      const int32_t* sorted_payload, const int32_t* bag_of_pos, int64_t N,
+                      int key_bits, void* weights, int weight_dtype,
+                      const int64_t* weights_offsets, const int32_t* D_offsets,
+                      const int64_t* hash_size_cumsum, int32_t T, int32_t B, int32_t max_D,
+                      int32_t all_D_mult8, const void* offsets, int index_dtype,
+                      const float* per_sample_weights, int pooling_mode, int optimizer,
+                      float* momentum1, const int64_t* momentum1_offsets, float learning_rate,
+                      float eps, void* partial_scratch, void* stream);
+
+/* split_embedding_codegen_grad_indice_weights_cuda
+ * (fbgemm_gpu/codegen/embedding_backward_split_indice_weights_template.cu). */
+int b200_tbe_grad_indice_weights(const float* grad_output, int64_t grad_stride,
+                                 const void* weights, int weight_dtype,
+                                 const int64_t* weights_offsets, const int32_t* D_offsets,
+                                 int32_t T, int32_t B, const void* indices, const void* offsets,
+                                 int index_dtype, float* grad_indice_weights, void* stream);
+
+/* ---------------------------------------------------------------- int8 inference path */
+
+/* torch.ops.fbgemm.FloatToFusedNBitRowwiseQuantizedSBHalf(w, 8)
+ * (fbgemm_gpu/src/quantize_ops.cu `_float_to_fusednbitrowwise_cuda_kernel`, CPU
+ * quantize_ops_cpu.cpp): rows of ncols uint8 followed by fp16 scale, fp16 bias. */
+int b200_quantize_rowwise_8bit_sbhalf(const float* in, int64_t nrows, int32_t ncols,
+                                      uint8_t* out, void* stream);
+
+/* int_nbit_split_embedding_codegen_lookup_function, INT8 rows only
+ * (fbgemm_gpu/codegen/embedding_forward_quantized_split_template.cu:154-450).
+ * Row layout: [fp16 scale, fp16 bias, D x uint8], padded to row_alignment bytes;
+ * weights_offsets are BYTE offsets.  idx == -1 contributes zeros.  Output fp16/fp32. */
+int b200_tbe_int8_forward(const uint8_t* weights, const int64_t* weights_offsets,
+                          const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
+                          int32_t max_D, int32_t row_alignment, const void* indices,
+                          const void* offsets, int index_dtype,
+                          const float* per_sample_weights, int pooling_mode, void* output,
+                          int output_dtype, void* stream);
+
+/* ---------------------------------------------------------------- DLRM dot interaction */
+
+/* InteractionArch.forward (torchrec/models/dlrm.py:193-219):
+ * dense [B, D], sparse [B, F, D] -> out [B, D + (F+1)F/2] = [dense | triu(X X^T, 1)],
+ * X = [dense; sparse]; row-major upper triangle, fp32. */
+int b200_interaction_forward(const float* dense, const float* sparse, int32_t B, int32_t F,
+                             int32_t D, float* out, void* stream);
+/* Backward of the same: grad_out [B, D + (F+1)F/2] -> grad_dense [B, D], grad_sparse [B,F,D]. */
+int b200_interaction_backward(const float* dense, const float* sparse, const float* grad_out,
+                              int32_t B, int32_t F, int32_t D, float* grad_dense,
+                              float* grad_sparse, void* stream);
+
+/* ---------------------------------------------------------------- sharded data movement */
+
+/* Receive-side layout change of PooledEmbeddingsAllToAll
+ * (torchrec/distributed/comm_ops.py:555-560 split+view+cat, and its backward :418-428):
+ * src is W contiguous blocks, block r = [B_local, dims[r]]; dst is [B_local, sum dims]
+ * (forward=1) or the inverse with an optional scale (forward=0; the 1/W of :527-528). */
+int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsum /*[W+1]*/,
+                          int32_t W, int32_t B_local, int forward, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_SPARSE_H_ */

@@ -1,0 +1,398 @@
+"""Tensor-level wrappers over the C ABI: argument checks, allocation, stream lookup.
+
+Every function requires CUDA tensors and launches on torch's *current* stream (the reference
+ops use at::cuda::getCurrentCUDAStream(), embedding_forward_split_template.cu:400), never
+the legacy default stream, and never synchronises the device.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import cabi
+from .cabi import check, lib
+
+_DT = {torch.int32: cabi.I32, torch.int64: cabi.I64, torch.float32: cabi.F32,
+       torch.float16: cabi.F16, torch.bfloat16: cabi.BF16, torch.uint8: cabi.U8}
+
+_WS: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def _need_cuda(*ts: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in ts:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(
+                "b200_sparse ops have a CUDA (sm_100a) implementation only; got a tensor on "
+                f"{t.device}. There is no CPU fallback by design."
+            )
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    assert dev is not None
+    return dev
+
+
+def _stream(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _ws(dev: torch.device) -> torch.Tensor:
+    """Scan scratch, one per (device, stream) so ops on side streams never share it."""
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), _stream(dev))
+    w = _WS.get(key)
+    if w is None:
+        w = torch.zeros(lib.b200_scan_workspace_bytes() // 8, dtype=torch.int64, device=dev)
+        _WS[key] = w
+    return w
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _idx_dt(t: torch.Tensor, what: str) -> int:
+    if t.dtype not in (torch.int32, torch.int64):
+        raise TypeError(f"{what} must be int32 or int64, got {t.dtype}")
+    return _DT[t.dtype]
+
+
+# ------------------------------------------------------------------------ jagged ops
+def cumsum(t_in: torch.Tensor, mode: int) -> torch.Tensor:
+    dev = _need_cuda(t_in)
+    if t_in.dim() != 1:
+        # reference: TORCH_CHECK(t_in.dim() == 1) for complete; others flatten
+        if mode == cabi.CUMSUM_COMPLETE:
+            raise RuntimeError("asynchronous_complete_cumsum expects a 1-D tensor")
+    x = t_in.contiguous()
+    n = x.numel()
+    if n >= 2 ** 31:
+        raise RuntimeError("cumsum: numel must be < 2^31")
+    dt = _idx_dt(x, "cumsum input")
+    shape = (n + 1,) if mode == cabi.CUMSUM_COMPLETE else x.shape
+    out = torch.empty(shape, dtype=x.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_cumsum(_p(x), _p(out), n, dt, mode, _p(_ws(dev)), _stream(dev)), "b200_cumsum")
+    return out
+
+
+def permute_sparse_data(
+    permute: torch.Tensor,
+    lengths: torch.Tensor,
+    values: torch.Tensor,
+    weights: Optional[torch.Tensor],
+    permuted_lengths_sum: Optional[int],
+    two_d: bool,
+) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+    dev = _need_cuda(permute, lengths, values, weights)
+    if permute.dtype != torch.int32:
+        raise TypeError("permute must be int32")
+    permute = permute.contiguous()
+    lengths_c = lengths.contiguous()
+    values_c = values.contiguous()
+    weights_c = weights.contiguous() if weights is not None else None
+    if two_d:
+        if lengths_c.dim() != 2:
+            raise RuntimeError("permute_2D_sparse_data: lengths must be [T, B]")
+        T, B = lengths_c.shape
+    else:
+        T, B = lengths_c.numel(), 1
+    Tp = permute.numel()
+    ldt = _idx_dt(lengths_c, "lengths")
+    out_shape = (Tp, B) if two_d else (Tp,)
+    out_lengths = torch.empty(out_shape, dtype=lengths_c.dtype, device=dev)
+    if Tp == 0 or B == 0:
+        return out_lengths, values_c.new_empty(0), (None if weights_c is None else weights_c.new_empty(0))
+    in_off = torch.empty(T * B + 1, dtype=torch.int64, device=dev)
+    out_off = torch.empty(Tp * B + 1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        check(lib.b200_permute_lengths(_p(permute), _p(lengths_c), ldt, T, Tp, B, _p(out_lengths),
+                                       _p(in_off), _p(out_off), _p(_ws(dev)), st),
+              "b200_permute_lengths")
+        if permuted_lengths_sum is None:
+            # same host sync as the reference when the caller does not pass the total
+            # (sparse_ops.cu:412)
+            permuted_lengths_sum = int(out_off[-1].item())
+        total = int(permuted_lengths_sum)
+        out_values = torch.empty(total, dtype=values_c.dtype, device=dev)
+        out_weights = None
+        if weights_c is not None:
+            out_weights = torch.empty(total, dtype=weights_c.dtype, device=dev)
+        check(lib.b200_permute_data(_p(permute), Tp, B, _p(in_off), _p(out_off), _p(values_c),
+                                    _p(out_values), values_c.element_size(), _p(weights_c),
+                                    _p(out_weights),
+                                    weights_c.element_size() if weights_c is not None else 4,
+                                    total, st),
+              "b200_permute_data")
+    return out_lengths, out_values, out_weights
+
+
+def expand_into_jagged_permute(permute: torch.Tensor, input_offsets: torch.Tensor,
+                               output_offsets: torch.Tensor, output_size: int) -> torch.Tensor:
+    dev = _need_cuda(permute, input_offsets, output_offsets)
+    if permute.dtype != torch.int32:
+        permute = permute.to(torch.int32)
+    if input_offsets.dtype != output_offsets.dtype:
+        raise TypeError("input_offsets and output_offsets must share a dtype")
+    n = permute.numel()
+    if input_offsets.numel() != n + 1 or output_offsets.numel() != n + 1:
+        raise RuntimeError("offsets must have permute.numel() + 1 entries")
+    dt = _idx_dt(input_offsets, "offsets")
+    out = torch.empty(int(output_size), dtype=input_offsets.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_expand_into_jagged_permute(_p(permute.contiguous()), _p(input_offsets.contiguous()),
+                                                  _p(output_offsets.contiguous()), dt, n, _p(out),
+                                                  int(output_size), _stream(dev)),
+              "b200_expand_into_jagged_permute")
+    return out
+
+
+def offsets_range(offsets: torch.Tensor, range_size: int) -> torch.Tensor:
+    dev = _need_cuda(offsets)
+    dt = _idx_dt(offsets, "offsets")
+    out = torch.empty(int(range_size), dtype=offsets.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_offsets_range(_p(offsets.contiguous()), dt, offsets.numel(), _p(out),
+                                     int(range_size), _stream(dev)), "b200_offsets_range")
+    return out
+
+
+def block_bucketize_sparse_features(
+    lengths: torch.Tensor, indices: torch.Tensor, bucketize_pos: bool, sequence: bool,
+    block_sizes: torch.Tensor, my_size: int, weights: Optional[torch.Tensor] = None,
+) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor], Optional[torch.Tensor]]:
+    dev = _need_cuda(lengths, indices, block_sizes, weights)
+    lengths = lengths.contiguous()
+    indices = indices.contiguous()
+    block_sizes = block_sizes.contiguous()
+    if block_sizes.dtype != indices.dtype:
+        raise TypeError("block_sizes must have the dtype of indices (sparse_ops.cu:855)")
+    if weights is not None and weights.dtype != torch.float32:
+        raise TypeError("bucketize weights must be float32")
+    odt, idt = _idx_dt(lengths, "lengths"), _idx_dt(indices, "indices")
+    T = block_sizes.numel()
+    TB = lengths.numel()
+    if T == 0 or TB % T != 0:
+        raise RuntimeError("lengths.numel() must be a multiple of block_sizes.numel()")
+    B = TB // T
+    N = indices.numel()
+    W = int(my_size)
+    new_lengths = torch.empty(TB * W, dtype=lengths.dtype, device=dev)
+    new_indices = torch.empty_like(indices)
+    new_weights = torch.empty_like(weights) if weights is not None else None
+    new_pos = torch.empty_like(indices) if bucketize_pos else None
+    unbucketize = torch.empty_like(indices) if sequence else None
+    if TB == 0:
+        return new_lengths, new_indices, new_weights, new_pos, unbucketize
+    off = torch.empty(TB + 1, dtype=torch.int64, device=dev)
+    noff = torch.empty(TB * W + 1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_block_bucketize(_p(lengths), odt, _p(indices), idt, _p(block_sizes), T, B, W, N,
+                                       _p(weights.contiguous() if weights is not None else None),
+                                       _p(new_lengths), _p(new_indices), _p(new_weights), _p(new_pos),
+                                       _p(unbucketize), _p(off), _p(noff), _p(_ws(dev)), _stream(dev)),
+              "b200_block_bucketize")
+    return new_lengths, new_indices, new_weights, new_pos, unbucketize
+
+
+def bounds_check_indices(rows_per_table: torch.Tensor, indices: torch.Tensor, offsets: torch.Tensor,
+                         mode: int, warning: torch.Tensor) -> None:
+    dev = _need_cuda(rows_per_table, indices, offsets, warning)
+    if indices.dtype != offsets.dtype:
+        raise TypeError("indices and offsets must share a dtype")
+    if not (indices.is_contiguous() and offsets.is_contiguous()):
+        raise RuntimeError("bounds_check_indices works in place and needs contiguous tensors")
+    dt = _idx_dt(indices, "indices")
+    T = rows_per_table.numel()
+    if T == 0:
+        return
+    B = (offsets.numel() - 1) // T
+    with torch.cuda.device(dev):
+        check(lib.b200_bounds_check(_p(rows_per_table), _p(indices), _p(offsets), dt, T, B,
+                                    indices.numel(), int(mode), _p(warning), _p(_ws(dev)), _stream(dev)),
+              "b200_bounds_check")
+
+
+# ------------------------------------------------------------------------ pooled lookup
+def tbe_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
+                total_D: int, max_D: int, all_D_mult8: bool, indices: torch.Tensor,
+                offsets: torch.Tensor, per_sample_weights: Optional[torch.Tensor], pooling_mode: int,
+                output_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    dev = _need_cuda(weights, weights_offsets, D_offsets, indices, offsets, per_sample_weights)
+    if indices.dtype != offsets.dtype:
+        raise TypeError("indices and offsets must share a dtype")
+    idt = _idx_dt(indices, "indices")
+    T = D_offsets.numel() - 1
+    if T <= 0:
+        raise RuntimeError("TBE forward needs at least one table")
+    if (offsets.numel() - 1) % T != 0:
+        raise RuntimeError("offsets must have T*B+1 entries")
+    B = (offsets.numel() - 1) // T
+    if per_sample_weights is not None:
+        if per_sample_weights.dtype != torch.float32:
+            per_sample_weights = per_sample_weights.float()
+        per_sample_weights = per_sample_weights.contiguous()
+    out = torch.empty((B, total_D), dtype=output_dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_tbe_forward(_p(weights), _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
+                                   T, B, total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
+                                   _p(offsets.contiguous()), idt, _p(per_sample_weights),
+                                   int(pooling_mode), _p(out), _DT[output_dtype], _stream(dev)),
+              "b200_tbe_forward")
+    return out
+
+
+class SortedIndices:
+    """Result of the index transpose: sorted (table,row) keys with their bag payload."""
+
+    __slots__ = ("keys", "payload", "bag_of_pos", "N", "key_bits", "ws")
+
+    def __init__(self, keys, payload, bag_of_pos, N, key_bits, ws):
+        self.keys, self.payload, self.bag_of_pos = keys, payload, bag_of_pos
+        self.N, self.key_bits, self.ws = N, key_bits, ws
+
+
+def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cumsum: torch.Tensor,
+                     total_hash_size_bits: int, B: int, weighted: bool) -> SortedIndices:
+    dev = _need_cuda(indices, offsets, hash_size_cumsum)
+    idt = _idx_dt(indices, "indices")
+    T = hash_size_cumsum.numel() - 1
+    N = indices.numel()
+    key_bits = max(1, int(total_hash_size_bits))
+    kdt = torch.int64 if key_bits > 32 else torch.int32
+    keys = torch.empty(N, dtype=kdt, device=dev)
+    payload = torch.empty(N, dtype=torch.int32, device=dev)
+    bag_of_pos = torch.empty(N, dtype=torch.int32, device=dev) if weighted else None
+    ws_bytes = lib.b200_tbe_sort_workspace_bytes(N, key_bits)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
+                                        key_bits, int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
+                                        _p(ws), ws_bytes, _stream(dev)), "b200_tbe_sort_indices")
+    return SortedIndices(keys, payload, bag_of_pos, N, key_bits, ws)
+
+
+def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.Tensor,
+                 weights_offsets: torch.Tensor, D_offsets: torch.Tensor, hash_size_cumsum: torch.Tensor,
+                 B: int, max_D: int, all_D_mult8: bool, offsets: torch.Tensor,
+                 per_sample_weights: Optional[torch.Tensor], pooling_mode: int, optimizer: int,
+                 momentum1: Optional[torch.Tensor], momentum1_offsets: Optional[torch.Tensor],
+                 learning_rate: float, eps: float) -> None:
+    dev = _need_cuda(grad_output, weights, weights_offsets, D_offsets, hash_size_cumsum, offsets)
+    if grad_output.dtype != torch.float32:
+        grad_output = grad_output.float()
+    # the reference forces a contiguous, 16-byte aligned gradient
+    # (embedding_backward_split_host_template.cpp:274-278)
+    if not grad_output.is_contiguous() or grad_output.data_ptr() % 16 != 0 or grad_output.stride(0) % 4 != 0:
+        grad_output = grad_output.contiguous().clone(memory_format=torch.contiguous_format)
+    T = D_offsets.numel() - 1
+    scratch_bytes = lib.b200_tbe_backward_scratch_bytes(srt.N, max_D)
+    scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
+    if per_sample_weights is not None:
+        per_sample_weights = per_sample_weights.float().contiguous()
+    with torch.cuda.device(dev):
+        check(lib.b200_tbe_backward(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
+                                    _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),
+                                    _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
+                                    _p(hash_size_cumsum), T, B, max_D, int(all_D_mult8), _p(offsets),
+                                    _idx_dt(offsets, "offsets"), _p(per_sample_weights),
+                                    int(pooling_mode), int(optimizer), _p(momentum1),
+                                    _p(momentum1_offsets), float(learning_rate), float(eps),
+                                    _p(scratch), _stream(dev)), "b200_tbe_backward")
+
+
+def tbe_grad_indice_weights(grad_output: torch.Tensor, weights: torch.Tensor,
+                            weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
+                            indices: torch.Tensor, offsets: torch.Tensor) -> torch.Tensor:
+    dev = _need_cuda(grad_output, weights, indices, offsets)
+    grad_output = grad_output.float().contiguous()
+    T = D_offsets.numel() - 1
+    B = (offsets.numel() - 1) // T
+    out = torch.empty(indices.numel(), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_tbe_grad_indice_weights(_p(grad_output), grad_output.stride(0), _p(weights),
+                                               _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
+                                               T, B, _p(indices), _p(offsets),
+                                               _idx_dt(indices, "indices"), _p(out), _stream(dev)),
+              "b200_tbe_grad_indice_weights")
+    return out
+
+
+# ------------------------------------------------------------------------ int8 inference
+def quantize_rowwise_8bit_sbhalf(w: torch.Tensor) -> torch.Tensor:
+    dev = _need_cuda(w)
+    if w.dim() != 2:
+        raise RuntimeError("expected a 2-D weight")
+    w = w.float().contiguous()
+    out = torch.empty((w.shape[0], w.shape[1] + 4), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_quantize_rowwise_8bit_sbhalf(_p(w), w.shape[0], w.shape[1], _p(out), _stream(dev)),
+              "b200_quantize_rowwise_8bit_sbhalf")
+    return out
+
+
+def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
+                     total_D: int, max_D: int, row_alignment: int, indices: torch.Tensor,
+                     offsets: torch.Tensor, per_sample_weights: Optional[torch.Tensor],
+                     pooling_mode: int, output_dtype: torch.dtype) -> torch.Tensor:
+    dev = _need_cuda(weights, weights_offsets, D_offsets, indices, offsets, per_sample_weights)
+    if indices.dtype != offsets.dtype:
+        raise TypeError("indices and offsets must share a dtype")
+    T = D_offsets.numel() - 1
+    B = (offsets.numel() - 1) // T
+    out = torch.empty((B, total_D), dtype=output_dtype, device=dev)
+    if per_sample_weights is not None:
+        per_sample_weights = per_sample_weights.float().contiguous()
+    with torch.cuda.device(dev):
+        check(lib.b200_tbe_int8_forward(_p(weights), _p(weights_offsets), _p(D_offsets), T, B, total_D,
+                                        max_D, int(row_alignment), _p(indices.contiguous()),
+                                        _p(offsets.contiguous()), _idx_dt(indices, "indices"),
+                                        _p(per_sample_weights), int(pooling_mode), _p(out),
+                                        _DT[output_dtype], _stream(dev)), "b200_tbe_int8_forward")
+    return out
+
+
+# ------------------------------------------------------------------------ dot interaction
+def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor) -> torch.Tensor:
+    dev = _need_cuda(dense, sparse)
+    B, D = dense.shape
+    F = sparse.shape[1]
+    dense = dense.float().contiguous()
+    sparse = sparse.float().contiguous()
+    out = torch.empty((B, D + (F + 1) * F // 2), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_interaction_forward(_p(dense), _p(sparse), B, F, D, _p(out), _stream(dev)),
+              "b200_interaction_forward")
+    return out
+
+
+def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
+                         grad_out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    dev = _need_cuda(dense, sparse, grad_out)
+    B, D = dense.shape
+    F = sparse.shape[1]
+    grad_out = grad_out.float().contiguous()
+    gd = torch.empty_like(dense)
+    gs = torch.empty_like(sparse)
+    with torch.cuda.device(dev):
+        check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), B, F, D, _p(gd), _p(gs),
+                                            _stream(dev)), "b200_interaction_backward")
+    return gd, gs
+
+
+# ------------------------------------------------------------------------ pooled a2a layout
+def pooled_a2a_recat(src: torch.Tensor, dim_cumsum: torch.Tensor, B_local: int, forward: bool,
+                     scale: float = 1.0) -> torch.Tensor:
+    dev = _need_cuda(src, dim_cumsum)
+    W = dim_cumsum.numel() - 1
+    src = src.contiguous()
+    dst = torch.empty_like(src)
+    with torch.cuda.device(dev):
+        check(lib.b200_pooled_a2a_recat(_p(src), _p(dst), _p(dim_cumsum), W, int(B_local), int(forward),
+                                        float(scale), _stream(dev)), "b200_pooled_a2a_recat")
+    return dst

@@ -1,0 +1,145 @@
+// Small entry points: error text, ABI version, per-sample-weight gradient, and the
+// receive-side layout change of the pooled all-to-all.
+#include "common.cuh"
+
+namespace b200 {
+
+// grad wrt per-sample weights: grad_w[p] = sum_d grad_out[b, D_begin + d] * W_t[idx_p, d]
+// (fbgemm_gpu/codegen/embedding_backward_split_indice_weights_template.cu).  One warp per
+// 32-bag tile of one table walks the tile's ids as a stream (same layout as the forward).
+template <typename W, int EPV>
+__global__ void __launch_bounds__(128)
+grad_indice_weights_kernel(const float* __restrict__ grad, int64_t grad_stride,
+                           const W* __restrict__ weights,
+                           const int64_t* __restrict__ weights_offsets,
+                           const int32_t* __restrict__ D_offsets, int32_t T, int32_t B,
+                           int32_t tiles_per_table, const void* __restrict__ indices,
+                           const void* __restrict__ offsets, bool idx64, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= (int64_t)T * tiles_per_table) return;
+  const int t = (int)(tile / tiles_per_table);
+  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
+  const int nb = min(32, B - b0);
+  const int D_begin = D_offsets[t];
+  const int D = D_offsets[t + 1] - D_begin;
+  const W* __restrict__ wtab = weights + weights_offsets[t];
+  const int64_t obase = (int64_t)t * B + b0;
+  for (int j = 0; j < nb; ++j) {
+    const int64_t s = load_index(offsets, obase + j, idx64);
+    const int64_t e = load_index(offsets, obase + j + 1, idx64);
+    const float* __restrict__ g = grad + (int64_t)(b0 + j) * grad_stride + D_begin;
+    for (int64_t p = s; p < e; ++p) {
+      const int64_t idx = load_index(indices, p, idx64);
+      const W* __restrict__ row = wtab + idx * D;
+      float acc = 0.f;
+      for (int d = EPV * lane; d < D; d += EPV * 32) {
+        float w[EPV];
+        load_vec<W, EPV, true>(row + d, w);
+#pragma unroll
+        for (int k = 0; k < EPV; ++k) acc = fmaf(g[d + k], w[k], acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) out[p] = acc;
+    }
+  }
+}
+
+// dim_cumsum[r] .. dim_cumsum[r+1] are the columns rank r contributes.
+// forward: src block r is [B_local, dims[r]] (contiguous), dst is [B_local, sumD].
+// backward: src is [B_local, sumD], dst block r is [B_local, dims[r]], scaled.
+__global__ void __launch_bounds__(256)
+pooled_a2a_recat_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                        const int32_t* __restrict__ dim_cumsum, int32_t W, int32_t B_local,
+                        bool forward, float scale) {
+  const int sumD4 = dim_cumsum[W] >> 2;
+  const int64_t total4 = (int64_t)B_local * sumD4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / sumD4;
+    const int c4 = (int)(i - b * sumD4);
+    const int col = c4 << 2;
+    int r = 0;
+    while (dim_cumsum[r + 1] <= col) ++r;
+    const int dr = dim_cumsum[r + 1] - dim_cumsum[r];
+    const int64_t blk = (int64_t)B_local * dim_cumsum[r] + b * dr + (col - dim_cumsum[r]);
+    const int64_t flat = b * ((int64_t)sumD4 << 2) + col;
+    if (forward) {
+      const uint4 v = ldg_stream_16(src + blk);
+      st_stream_16(dst + flat, v);
+    } else {
+      uint4 v = ldg_stream_16(src + flat);
+      float4 f = *reinterpret_cast<float4*>(&v);
+      f.x *= scale;
+      f.y *= scale;
+      f.z *= scale;
+      f.w *= scale;
+      *reinterpret_cast<float4*>(dst + blk) = f;
+    }
+  }
+}
+
+}  // namespace b200
+
+extern "C" const char* b200_error_string(int code) {
+  switch (code) {
+    case B200_OK:
+      return "ok";
+    case B200_EINVAL:
+      return "b200: invalid argument";
+    case B200_EUNSUPPORTED:
+      return "b200: configuration not supported by this build (see DESIGN.md)";
+    default:
+      return code > 0 ? cudaGetErrorString((cudaError_t)code) : "b200: unknown error";
+  }
+}
+
+extern "C" int b200_abi_version(void) { return 1; }
+
+extern "C" int b200_tbe_grad_indice_weights(const float* grad_output, int64_t grad_stride,
+                                            const void* weights, int weight_dtype,
+                                            const int64_t* weights_offsets,
+                                            const int32_t* D_offsets, int32_t T, int32_t B,
+                                            const void* indices, const void* offsets,
+                                            int index_dtype, float* grad_indice_weights,
+                                            void* stream) {
+  using namespace b200;
+  if (T == 0 || B == 0) return B200_OK;
+  if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
+  const int tiles = (B + 31) / 32;
+  const unsigned grid = (unsigned)ceil_div((int64_t)T * tiles, 4);
+  const bool idx64 = index_dtype == B200_I64;
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (weight_dtype) {
+    case B200_F32:
+      grad_indice_weights_kernel<float, 4><<<grid, 128, 0, s>>>(
+          grad_output, grad_stride, (const float*)weights, weights_offsets, D_offsets, T, B, tiles,
+          indices, offsets, idx64, grad_indice_weights);
+      break;
+    case B200_F16:
+      grad_indice_weights_kernel<__half, 4><<<grid, 128, 0, s>>>(
+          grad_output, grad_stride, (const __half*)weights, weights_offsets, D_offsets, T, B,
+          tiles, indices, offsets, idx64, grad_indice_weights);
+      break;
+    case B200_BF16:
+      grad_indice_weights_kernel<__nv_bfloat16, 4><<<grid, 128, 0, s>>>(
+          grad_output, grad_stride, (const __nv_bfloat16*)weights, weights_offsets, D_offsets, T,
+          B, tiles, indices, offsets, idx64, grad_indice_weights);
+      break;
+    default:
+      return B200_EUNSUPPORTED;
+  }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsum,
+                                     int32_t W, int32_t B_local, int forward, float scale,
+                                     void* stream) {
+  using namespace b200;
+  if (W <= 0 || B_local <= 0) return B200_OK;
+  pooled_a2a_recat_kernel<<<kNumSMs * 8, 256, 0, (cudaStream_t)stream>>>(
+      src, dst, dim_cumsum, W, B_local, forward != 0, scale);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -1,0 +1,663 @@
+// Fused backward + optimizer of the pooled lookup for sm_100a.
+//
+// Replaces transpose_embedding_input (fbgemm_gpu/src/split_embeddings_utils.cu:63-306) and
+// split_embedding_backward_codegen_<opt>_{un,}weighted_exact_cuda
+// (fbgemm_gpu/codegen/embedding_backward_split_template.cu:81-1138) with the optimizer bodies
+// of embedding_backward_code_generator.py:376-401 (rowwise Adagrad) and :629-632 (SGD).
+//
+// Contract kept: duplicate ids are coalesced BEFORE the optimizer, one update per unique
+// (table,row) per step, fp32 accumulation, weights updated in place, run-to-run
+// deterministic (no float atomics; the per-row sum is taken in stable sorted order).
+//
+// Design (not the reference's warp-per-row / CTA-per-row split):
+//  1. linearise keys (table row-offset + id) and radix-sort (key, b_t) pairs once — the sort
+//     only depends on the ids, so the host layer issues it at forward time on a side stream.
+//  2. ONE balanced pass over the sorted positions: each warp owns 32 consecutive sorted
+//     positions, keeps 4 gradient rows and the weight rows of the runs that end inside the
+//     batch in flight, sums runs in registers and applies the update as soon as a run ends.
+//     Work per warp is fixed (32 gradient rows) whatever the run-length distribution, so a
+//     3-row Criteo table (runs of ~21k) costs the same per position as a 40M-row one.
+//  3. runs that straddle warps are stitched through shared memory in fixed order; runs that
+//     straddle CTAs leave one partial row per CTA in scratch and a small second kernel
+//     finishes them, again in fixed order.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------ linearise
+template <typename K>
+__global__ void __launch_bounds__(128)
+tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ offsets, bool idx64,
+                     const int64_t* __restrict__ hash_size_cumsum, int32_t T, int32_t B,
+                     int32_t tiles_per_table, bool payload_is_position, K* __restrict__ keys,
+                     int32_t* __restrict__ payload, int32_t* __restrict__ bag_of_pos) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= (int64_t)T * tiles_per_table) return;
+  const int t = (int)(tile / tiles_per_table);
+  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
+  const int nb = min(32, B - b0);
+  const int64_t obase = (int64_t)t * B + b0;
+  const int64_t my_start = load_index(offsets, obase + min(lane, nb), idx64);
+  const int64_t S0 = __shfl_sync(kFull, my_start, 0);
+  const int32_t rel_start = (int32_t)(my_start - S0);
+  int32_t rel_end = __shfl_down_sync(kFull, rel_start, 1);
+  if (lane == 31) rel_end = (int32_t)(load_index(offsets, obase + nb, idx64) - S0);
+  const int32_t len = __shfl_sync(kFull, rel_end, 31);
+  const int64_t hash_base = hash_size_cumsum[t];
+  const int32_t iters = (len + 31) / 32;
+  for (int32_t it = 0; it < iters; ++it) {
+    const int32_t p = it * 32 + lane;
+    // bag of position p = number of bags whose end is <= p (ends are sorted)
+    int j = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const int probe = j + step - 1;
+      const int32_t e = __shfl_sync(kFull, rel_end, probe);
+      if (e <= p) j += step;
+    }
+    if (p < len) {
+      const int64_t idx = load_index(indices, S0 + p, idx64);
+      const int32_t bt = (int32_t)(obase + j);
+      keys[S0 + p] = (K)(hash_base + idx);
+      payload[S0 + p] = payload_is_position ? (int32_t)(S0 + p) : bt;
+      if (bag_of_pos) bag_of_pos[S0 + p] = bt;
+    }
+  }
+}
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+template <typename K>
+static size_t cub_sort_temp_bytes(int64_t N, int key_bits) {
+  size_t bytes = 0;
+  cub::DoubleBuffer<K> dk(nullptr, nullptr);
+  cub::DoubleBuffer<int32_t> dv(nullptr, nullptr);
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)N, 0, key_bits);
+  return bytes;
+}
+
+template <typename K>
+static int sort_impl(const void* indices, const void* offsets, bool idx64,
+                     const int64_t* hash_size_cumsum, int32_t T, int32_t B, int64_t N,
+                     int key_bits, bool payload_is_position, void* sorted_keys,
+                     int32_t* sorted_payload, int32_t* bag_of_pos, void* ws, size_t ws_bytes,
+                     cudaStream_t s) {
+  // ws = [alt keys | alt payload | cub temp]
+  char* p = (char*)ws;
+  K* keys_alt = (K*)p;
+  p += align256(sizeof(K) * (size_t)N);
+  int32_t* pay_alt = (int32_t*)p;
+  p += align256(sizeof(int32_t) * (size_t)N);
+  size_t temp_bytes = ws_bytes - (size_t)(p - (char*)ws);
+  const int tiles_per_table = (B + 31) / 32;
+  const int64_t tiles = (int64_t)T * tiles_per_table;
+  // linearise straight into the caller's output buffers, sort with a double buffer, and
+  // copy back only if CUB finished in the alternate one.
+  tbe_linearize_kernel<K><<<(unsigned)ceil_div(tiles, 4), 128, 0, s>>>(
+      indices, offsets, idx64, hash_size_cumsum, T, B, tiles_per_table, payload_is_position,
+      (K*)sorted_keys, sorted_payload, bag_of_pos);
+  B200_LAUNCH_CHECK();
+  cub::DoubleBuffer<K> dk((K*)sorted_keys, keys_alt);
+  cub::DoubleBuffer<int32_t> dv(sorted_payload, pay_alt);
+  B200_CUDA_TRY(cub::DeviceRadixSort::SortPairs(p, temp_bytes, dk, dv, (int)N, 0, key_bits, s));
+  if (dk.Current() != (K*)sorted_keys)
+    B200_CUDA_TRY(cudaMemcpyAsync(sorted_keys, dk.Current(), sizeof(K) * (size_t)N,
+                                  cudaMemcpyDeviceToDevice, s));
+  if (dv.Current() != sorted_payload)
+    B200_CUDA_TRY(cudaMemcpyAsync(sorted_payload, dv.Current(), sizeof(int32_t) * (size_t)N,
+                                  cudaMemcpyDeviceToDevice, s));
+  return B200_OK;
+}
+
+// ------------------------------------------------------------------ update
+constexpr int kBwdWarps = 8;
+constexpr int kBwdThreads = kBwdWarps * 32;
+constexpr int kBwdTile = kBwdThreads;  // sorted positions per CTA
+
+struct BwdMeta {  // per-CTA records in scratch, written unconditionally by every CTA
+  unsigned long long t_key;
+  int32_t t_feat;
+  int32_t t_flag;    // a run starts in this CTA and continues into the next
+  int32_t has_head;  // the run entering this CTA ends inside it (a head, or end of run/data)
+  int32_t pad;
+};
+
+__device__ __forceinline__ uint4 ld_na_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// fp32 gradient vector: EPV consecutive floats
+template <int EPV>
+__device__ __forceinline__ void load_grad(const float* p, float (&f)[EPV]) {
+#pragma unroll
+  for (int i = 0; i < EPV; i += 4) {
+    uint4 r = ldg_stream_16(p + i);
+    f[i] = __uint_as_float(r.x);
+    f[i + 1] = __uint_as_float(r.y);
+    f[i + 2] = __uint_as_float(r.z);
+    f[i + 3] = __uint_as_float(r.w);
+  }
+}
+
+template <typename W, int EPV>
+__device__ __forceinline__ void load_wrow(const W* p, float (&f)[EPV]) {
+  load_vec<W, EPV, false>(p, f);
+}
+
+// Optimizer step for one (table,row): acc holds the summed gradient, distributed over the
+// warp as element EPV*(lane+32*v)+e.  wv (optional) holds the prefetched weight row.
+template <typename W, int EPV, int NV, int OPT, bool PREFETCHED>
+__device__ __forceinline__ void apply_update(float (&acc)[NV][EPV], float (&wv)[NV][EPV],
+                                             float m_prefetched, W* __restrict__ wrow,
+                                             float* __restrict__ mom, int D, int lane, float lr,
+                                             float eps) {
+  float mult = lr;
+  if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+    float ss = 0.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) ss = fmaf(acc[v][e], acc[v][e], ss);  // lanes past D hold 0
+    ss = warp_sum(ss) / (float)D;
+    const float m_old = PREFETCHED ? m_prefetched : *mom;
+    const float m_new = m_old + ss;
+    if (lane == 0) *mom = m_new;
+    mult = lr / (sqrtf(m_new) + eps);
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const int d = EPV * (lane + 32 * v);
+    if (d < D) {
+      float w[EPV];
+      if constexpr (PREFETCHED) {
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) w[e] = wv[v][e];
+      } else {
+        load_wrow<W, EPV>(wrow + d, w);
+      }
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) w[e] = fmaf(acc[v][e], -mult, w[e]);
+      store_vec<W, EPV, false>(wrow + d, w);
+    }
+  }
+}
+
+// shared/global partial rows are stored so that lane accesses are 16-byte and conflict-free:
+// float4 chunk c of vector v of lane l sits at ((v*(EPV/4)+c)*32 + l)*4.
+template <int EPV, int NV>
+__device__ __forceinline__ void row_store(float* dst, const float (&acc)[NV][EPV], int lane) {
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int c = 0; c < EPV / 4; ++c)
+      *reinterpret_cast<float4*>(dst + ((v * (EPV / 4) + c) * 32 + lane) * 4) =
+          make_float4(acc[v][4 * c], acc[v][4 * c + 1], acc[v][4 * c + 2], acc[v][4 * c + 3]);
+}
+template <int EPV, int NV>
+__device__ __forceinline__ void row_add(float (&acc)[NV][EPV], const float* src, int lane) {
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int c = 0; c < EPV / 4; ++c) {
+      const float4 x = *reinterpret_cast<const float4*>(src + ((v * (EPV / 4) + c) * 32 + lane) * 4);
+      acc[v][4 * c] += x.x;
+      acc[v][4 * c + 1] += x.y;
+      acc[v][4 * c + 2] += x.z;
+      acc[v][4 * c + 3] += x.w;
+    }
+}
+
+template <typename K>
+struct BwdArgs {
+  const float* grad;
+  int64_t grad_stride;
+  const K* keys;
+  const int32_t* payload;
+  const int32_t* bag_of_pos;  // non-null => payload is the original position
+  int64_t N;
+  void* weights;
+  const int64_t* weights_offsets;
+  const int32_t* D_offsets;
+  const int64_t* hash_size_cumsum;
+  int32_t T, B;
+  const void* offsets;
+  bool idx64;
+  const float* psw;
+  bool mean;
+  float* momentum1;
+  const int64_t* momentum1_offsets;
+  float lr, eps;
+  float* part_rows;  // [numCTAs][2][ROW]  (0 = leading partial H, 1 = trailing partial T)
+  BwdMeta* meta;     // [numCTAs]
+  int32_t num_ctas;
+};
+
+template <typename W, typename K, int EPV, int NV, int OPT>
+__global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const BwdArgs<K> a) {
+  constexpr int ROW = NV * EPV * 32;
+  // gradient rows (and weight rows) in flight per warp: 16 floats per lane of each kind
+  constexpr int kBwdU = (16 / (NV * EPV)) > 0 ? (16 / (NV * EPV)) : 1;
+  extern __shared__ __align__(16) float smem[];
+  float* sH = smem;                    // [kBwdWarps][ROW]
+  __shared__ int s_first_head[kBwdWarps];
+  __shared__ int s_cont[kBwdWarps];
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int64_t i0 = (int64_t)blockIdx.x * kBwdTile + warp * 32;
+  const int nvalid = (int)max((int64_t)0, min((int64_t)32, a.N - i0));
+  const bool valid = lane < nvalid;
+  W* const weights = reinterpret_cast<W*>(a.weights);
+
+  // ---- per-position decode (lane k <-> sorted position i0+k)
+  K key = 0;
+  int32_t pay = 0;
+  if (valid) {
+    key = a.keys[i0 + lane];
+    pay = a.payload[i0 + lane];
+  }
+  K prev = __shfl_up_sync(kFull, key, 1);
+  if (lane == 0 && i0 > 0 && nvalid > 0) prev = a.keys[i0 - 1];
+  const bool head = valid && ((i0 + lane) == 0 || key != prev);
+  K nextkey = key;
+  if (lane == 31 && nvalid == 32 && i0 + 32 < a.N) nextkey = a.keys[i0 + 32];
+  const bool cont =
+      __shfl_sync(kFull, (int)(nvalid == 32 && i0 + 32 < a.N && nextkey == key), 31) != 0;
+  const unsigned Hm = __ballot_sync(kFull, head);
+  const unsigned Vm = nvalid == 32 ? kFull : ((1u << nvalid) - 1u);
+  const int fh = Hm ? (__ffs(Hm) - 1) : 32;
+  // run-end mask: position k ends a run if k+1 is a head, or k is the tile's last position
+  // and the run does not continue.  Complete (head inside the tile) only for k >= fh.
+  unsigned Em = (Hm >> 1);
+  if (nvalid > 0 && !cont) Em |= 1u << (nvalid - 1);
+  Em &= Vm;
+  const unsigned Cm = fh < 32 ? (Em & ~((1u << fh) - 1u)) : 0u;
+
+  int32_t pos = pay, bt = pay;
+  if (a.bag_of_pos && valid) bt = a.bag_of_pos[pos];
+  const int32_t t = valid ? bt / a.B : 0;
+  const int32_t b = bt - t * a.B;
+  int32_t Dbeg = 0, Dt = 0;
+  int64_t woff = 0, moff = 0;
+  float scale = 1.f;
+  if (valid) {
+    Dbeg = a.D_offsets[t];
+    Dt = a.D_offsets[t + 1] - Dbeg;
+    const int64_t row = (int64_t)key - a.hash_size_cumsum[t];
+    woff = a.weights_offsets[t] + row * Dt;
+    if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) moff = a.momentum1_offsets[t] + row;
+    if (a.mean) {
+      const int64_t L = load_index(a.offsets, (int64_t)bt + 1, a.idx64) -
+                        load_index(a.offsets, (int64_t)bt, a.idx64);
+      scale = 1.0f / (float)L;
+    }
+    if (a.psw) scale *= a.psw[pos];
+  }
+  const bool scaled = a.mean || a.psw != nullptr;
+  const uint32_t goff4 = (uint32_t)(((int64_t)b * a.grad_stride + Dbeg) >> 2);
+
+  float acc[NV][EPV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
+  int open_head = -1;  // head position of the open run inside this tile, -1 = carried in
+  float dummy_w[NV][EPV];
+
+  for (int base = 0; base < nvalid; base += kBwdU) {
+    float g[kBwdU][NV][EPV];
+    float wv[kBwdU][NV][EPV];
+    float mv[kBwdU];
+    int Du[kBwdU];
+    float su[kBwdU];
+    int64_t wo[kBwdU], mo[kBwdU];
+#pragma unroll
+    for (int u = 0; u < kBwdU; ++u) {
+      const int src = (base + u) & 31;
+      const bool live = base + u < nvalid;
+      const uint32_t g4 = __shfl_sync(kFull, goff4, src);
+      Du[u] = __shfl_sync(kFull, Dt, src);
+      su[u] = __shfl_sync(kFull, scale, src);
+      wo[u] = __shfl_sync(kFull, woff, src);
+      mo[u] = __shfl_sync(kFull, moff, src);
+      const float* grow = a.grad + ((int64_t)g4 << 2);
+      const bool fin = live && ((Cm >> src) & 1u);
+      mv[u] = 0.f;
+      if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+        if (fin) mv[u] = a.momentum1[mo[u]];
+      }
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        const int d = EPV * (lane + 32 * v);
+        if (live && d < Du[u]) {
+          load_grad<EPV>(grow + d, g[u][v]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) g[u][v][e] = 0.f;
+        }
+        if (fin && d < Du[u]) {
+          if constexpr (sizeof(W) == 4 || EPV == 8) {
+            // 16-byte coherent load that bypasses L1 (rows are written below by this warp)
+            uint4 r = ld_na_16(weights + wo[u] + d);
+            if constexpr (sizeof(W) == 4) {
+              wv[u][v][0] = __uint_as_float(r.x);
+              wv[u][v][1] = __uint_as_float(r.y);
+              wv[u][v][2] = __uint_as_float(r.z);
+              wv[u][v][3] = __uint_as_float(r.w);
+            } else {
+              ElemCvt<W>::unpack2(r.x, wv[u][v][0], wv[u][v][1]);
+              ElemCvt<W>::unpack2(r.y, wv[u][v][2], wv[u][v][3]);
+              ElemCvt<W>::unpack2(r.z, wv[u][v][4], wv[u][v][5]);
+              ElemCvt<W>::unpack2(r.w, wv[u][v][6], wv[u][v][7]);
+            }
+          } else {
+            load_wrow<W, EPV>(weights + wo[u] + d, wv[u][v]);
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) wv[u][v][e] = 0.f;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kBwdU; ++u) {
+      const int src = base + u;
+      if (src < nvalid) {
+        if ((Hm >> src) & 1u) open_head = src;
+        if (scaled) {
+#pragma unroll
+          for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) acc[v][e] = fmaf(su[u], g[u][v][e], acc[v][e]);
+        } else {
+#pragma unroll
+          for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) acc[v][e] += g[u][v][e];
+        }
+        if ((Em >> src) & 1u) {
+          if (open_head >= 0) {
+            apply_update<W, EPV, NV, OPT, true>(acc, wv[u], mv[u], weights + wo[u],
+                                                a.momentum1 + mo[u], Du[u], lane, a.lr, a.eps);
+          } else {
+            row_store<EPV, NV>(sH + warp * ROW, acc, lane);  // tail of a run from an earlier tile
+          }
+#pragma unroll
+          for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
+        }
+      }
+    }
+  }
+  // The run still open at the end of the tile continues into the next one.
+  // open_head < 0: the whole tile lies inside one run -> leading partial (H).
+  if (cont && open_head < 0) row_store<EPV, NV>(sH + warp * ROW, acc, lane);
+  if (lane == 0) {
+    s_first_head[warp] = nvalid > 0 ? fh : 0;
+    s_cont[warp] = cont ? 1 : 0;
+  }
+  __syncthreads();
+
+  // ---- stitch runs across the warps of this CTA (fixed order => deterministic)
+  float* my_part = a.part_rows + (int64_t)blockIdx.x * 2 * ROW;
+  if (cont && open_head >= 0) {
+    // this warp holds the first piece (T) of a run that continues; acc is still in registers
+    const K rk = __shfl_sync(kFull, key, open_head);
+    const int32_t rt = __shfl_sync(kFull, t, open_head);
+    const int rD = __shfl_sync(kFull, Dt, open_head);
+    const int64_t rwo = __shfl_sync(kFull, woff, open_head);
+    const int64_t rmo = __shfl_sync(kFull, moff, open_head);
+    bool finished = false;
+    for (int x = warp + 1; x < kBwdWarps; ++x) {
+      const int xfh = s_first_head[x];
+      if (xfh > 0) row_add<EPV, NV>(acc, sH + x * ROW, lane);
+      if (xfh < 32 || !s_cont[x]) {  // a head follows, or the run ends with tile x
+        finished = true;
+        break;
+      }
+    }
+    if (finished) {
+      apply_update<W, EPV, NV, OPT, false>(acc, dummy_w, 0.f, weights + rwo, a.momentum1 + rmo, rD,
+                                           lane, a.lr, a.eps);
+    } else {
+      row_store<EPV, NV>(my_part + ROW, acc, lane);
+      if (lane == 0) {
+        a.meta[blockIdx.x].t_key = (unsigned long long)rk;
+        a.meta[blockIdx.x].t_feat = rt;
+      }
+    }
+    if (lane == 0 && !finished) a.meta[blockIdx.x].t_flag = 1;
+  }
+  if (warp == 0) {
+    // leading partial of the CTA: pieces before the first head belong to a run that
+    // started in an earlier CTA.
+    float lead[NV][EPV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) lead[v][e] = 0.f;
+    int stop = 0;      // the run entering this CTA ends inside it
+    int any_head = 0;  // some run starts inside this CTA
+    for (int x = 0; x < kBwdWarps; ++x) {
+      const int xfh = s_first_head[x];
+      any_head |= (xfh < 32);
+      if (!stop) {
+        if (xfh > 0) row_add<EPV, NV>(lead, sH + x * ROW, lane);
+        if (xfh < 32 || !s_cont[x]) stop = 1;
+      }
+    }
+    // only the last run can leave the CTA: it does iff the last warp continues, and it
+    // started here iff the CTA holds a head.
+    const int any_t = s_cont[kBwdWarps - 1] && any_head;
+    row_store<EPV, NV>(my_part, lead, lane);
+    if (lane == 0) {
+      a.meta[blockIdx.x].has_head = stop;
+      if (!any_t) a.meta[blockIdx.x].t_flag = 0;
+    }
+  }
+}
+
+// Finish runs that straddle CTAs: T of CTA c + leading partials of following CTAs.
+template <typename W, typename K, int EPV, int NV, int OPT>
+__global__ void __launch_bounds__(128) tbe_backward_combine_kernel(const BwdArgs<K> a) {
+  constexpr int ROW = NV * EPV * 32;
+  const int lane = threadIdx.x & 31;
+  const int c = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (c >= a.num_ctas) return;
+  if (!a.meta[c].t_flag) return;
+  W* const weights = reinterpret_cast<W*>(a.weights);
+  float acc[NV][EPV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
+  row_add<EPV, NV>(acc, a.part_rows + ((int64_t)c * 2 + 1) * ROW, lane);
+  int x0 = c + 1;
+  while (x0 < a.num_ctas) {
+    const int x = x0 + lane;
+    const int flag = x < a.num_ctas ? a.meta[x].has_head : 1;
+    const unsigned m = __ballot_sync(kFull, flag != 0);
+    const int n = m ? (__ffs(m) - 1) : 32;  // CTAs x0 .. x0+n-1 lie wholly inside the run
+    const int last = m ? n : n - 1;         // inclusive index of the last partial to add
+    for (int k = 0; k <= last; ++k) {
+      if (x0 + k < a.num_ctas) row_add<EPV, NV>(acc, a.part_rows + (int64_t)(x0 + k) * 2 * ROW, lane);
+    }
+    if (m) break;
+    x0 += 32;
+  }
+  const K key = (K)a.meta[c].t_key;
+  const int32_t t = a.meta[c].t_feat;
+  const int Dbeg = a.D_offsets[t];
+  const int D = a.D_offsets[t + 1] - Dbeg;
+  const int64_t row = (int64_t)key - a.hash_size_cumsum[t];
+  float dummy_w[NV][EPV];
+  float* mom = a.momentum1;
+  if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) mom += a.momentum1_offsets[t] + row;
+  apply_update<W, EPV, NV, OPT, false>(acc, dummy_w, 0.f, weights + a.weights_offsets[t] + row * D,
+                                       mom, D, lane, a.lr, a.eps);
+}
+
+template <typename W, typename K, int EPV, int NV, int OPT>
+static int launch_backward(const BwdArgs<K>& a, cudaStream_t s) {
+  constexpr int ROW = NV * EPV * 32;
+  const size_t smem = sizeof(float) * kBwdWarps * ROW;
+  auto tile = tbe_backward_tile_kernel<W, K, EPV, NV, OPT>;
+  if (smem > 48 * 1024)
+    B200_CUDA_TRY(cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tile<<<a.num_ctas, kBwdThreads, smem, s>>>(a);
+  B200_LAUNCH_CHECK();
+  tbe_backward_combine_kernel<W, K, EPV, NV, OPT><<<(a.num_ctas + 3) / 4, 128, 0, s>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+template <typename W, typename K, int EPV, int OPT>
+static int dispatch_nv(const BwdArgs<K>& a, int max_D, cudaStream_t s) {
+  const int vecs = (int)ceil_div(max_D, EPV * 32);
+  if (vecs <= 1) return launch_backward<W, K, EPV, 1, OPT>(a, s);
+  if (vecs <= 2) return launch_backward<W, K, EPV, 2, OPT>(a, s);
+  if (vecs <= 4) return launch_backward<W, K, EPV, 4, OPT>(a, s);
+  if (vecs <= 8) return launch_backward<W, K, EPV, 8, OPT>(a, s);
+  return B200_EUNSUPPORTED;
+}
+
+template <typename W, typename K, int EPV>
+static int dispatch_opt(const BwdArgs<K>& a, int optimizer, int max_D, cudaStream_t s) {
+  if (optimizer == B200_OPT_SGD) return dispatch_nv<W, K, EPV, B200_OPT_SGD>(a, max_D, s);
+  if (optimizer == B200_OPT_ROWWISE_ADAGRAD)
+    return dispatch_nv<W, K, EPV, B200_OPT_ROWWISE_ADAGRAD>(a, max_D, s);
+  return B200_EUNSUPPORTED;
+}
+
+template <typename K>
+static int dispatch_w(const BwdArgs<K>& a, int weight_dtype, bool mult8, int optimizer, int max_D,
+                      cudaStream_t s) {
+  switch (weight_dtype) {
+    case B200_F32:
+      return dispatch_opt<float, K, 4>(a, optimizer, max_D, s);
+    case B200_F16:
+      return mult8 ? dispatch_opt<__half, K, 8>(a, optimizer, max_D, s)
+                   : dispatch_opt<__half, K, 4>(a, optimizer, max_D, s);
+    case B200_BF16:
+      return mult8 ? dispatch_opt<__nv_bfloat16, K, 8>(a, optimizer, max_D, s)
+                   : dispatch_opt<__nv_bfloat16, K, 4>(a, optimizer, max_D, s);
+    default:
+      return B200_EUNSUPPORTED;
+  }
+}
+
+static inline int64_t bwd_num_ctas(int64_t N) { return ceil_div(N, kBwdTile); }
+static inline size_t bwd_row_floats(int max_D) {
+  // the widest instantiation that can be chosen for this max_D (EPV=4 or 8, NV rounded up)
+  int vecs4 = (int)ceil_div(max_D, 4 * 32);
+  int nv = vecs4 <= 1 ? 1 : vecs4 <= 2 ? 2 : vecs4 <= 4 ? 4 : 8;
+  return (size_t)nv * 4 * 32 * 2;  // x2 covers the EPV=8 layouts as well
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits) {
+  using namespace b200;
+  if (N <= 0) return 256;
+  const bool k64 = key_bits > 32;
+  const size_t ksz = k64 ? 8 : 4;
+  size_t temp = k64 ? cub_sort_temp_bytes<uint64_t>(N, key_bits)
+                    : cub_sort_temp_bytes<uint32_t>(N, key_bits);
+  return align256(ksz * (size_t)N) + align256(4 * (size_t)N) + align256(temp) + 256;
+}
+
+extern "C" int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
+                                     const int64_t* hash_size_cumsum, int32_t T, int32_t B,
+                                     int64_t N, int key_bits, int payload_is_position,
+                                     void* sorted_keys, int32_t* sorted_payload,
+                                     int32_t* bag_of_pos, void* sort_ws, size_t sort_ws_bytes,
+                                     void* stream) {
+  using namespace b200;
+  if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
+  if (N >= 0x7fffffffLL || key_bits < 1 || key_bits > 64) return B200_EINVAL;
+  if (payload_is_position && !bag_of_pos) return B200_EINVAL;
+  if (N == 0 || T == 0 || B == 0) return B200_OK;
+  const bool idx64 = index_dtype == B200_I64;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (key_bits > 32)
+    return sort_impl<uint64_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
+                               payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                               sort_ws, sort_ws_bytes, s);
+  return sort_impl<uint32_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
+                             payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                             sort_ws, sort_ws_bytes, s);
+}
+
+extern "C" size_t b200_tbe_backward_scratch_bytes(int64_t N, int32_t max_D) {
+  using namespace b200;
+  const int64_t ctas = bwd_num_ctas(N > 0 ? N : 1);
+  return align256((size_t)ctas * 2 * bwd_row_floats(max_D) * sizeof(float)) +
+         align256((size_t)ctas * sizeof(BwdMeta)) + 256;
+}
+
+extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
+                                 const void* sorted_keys, const int32_t* sorted_payload,
+                                 const int32_t* bag_of_pos, int64_t N, int key_bits, void* weights,
+                                 int weight_dtype, const int64_t* weights_offsets,
+                                 const int32_t* D_offsets, const int64_t* hash_size_cumsum,
+                                 int32_t T, int32_t B, int32_t max_D, int32_t all_D_mult8,
+                                 const void* offsets, int index_dtype,
+                                 const float* per_sample_weights, int pooling_mode, int optimizer,
+                                 float* momentum1, const int64_t* momentum1_offsets,
+                                 float learning_rate, float eps, void* partial_scratch,
+                                 void* stream) {
+  using namespace b200;
+  if (N == 0 || T == 0 || B == 0) return B200_OK;
+  if ((grad_stride & 3) != 0) return B200_EINVAL;
+  if (((int64_t)B * grad_stride) >> 34) return B200_EINVAL;  // 32-bit float4 offsets
+  if (per_sample_weights && !bag_of_pos) return B200_EINVAL;
+  if (optimizer == B200_OPT_ROWWISE_ADAGRAD && (!momentum1 || !momentum1_offsets)) return B200_EINVAL;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t ctas = bwd_num_ctas(N);
+  char* p = (char*)partial_scratch;
+  float* part_rows = (float*)p;
+  p += align256((size_t)ctas * 2 * bwd_row_floats(max_D) * sizeof(float));
+  BwdMeta* meta = (BwdMeta*)p;
+#define B200_FILL(ARGS)                                    \
+  ARGS.grad = grad_output;                                 \
+  ARGS.grad_stride = grad_stride;                          \
+  ARGS.payload = sorted_payload;                           \
+  ARGS.bag_of_pos = bag_of_pos;                            \
+  ARGS.N = N;                                              \
+  ARGS.weights = weights;                                  \
+  ARGS.weights_offsets = weights_offsets;                  \
+  ARGS.D_offsets = D_offsets;                              \
+  ARGS.hash_size_cumsum = hash_size_cumsum;                \
+  ARGS.T = T;                                              \
+  ARGS.B = B;                                              \
+  ARGS.offsets = offsets;                                  \
+  ARGS.idx64 = index_dtype == B200_I64;                    \
+  ARGS.psw = per_sample_weights;                           \
+  ARGS.mean = pooling_mode == B200_POOL_MEAN;              \
+  ARGS.momentum1 = momentum1;                              \
+  ARGS.momentum1_offsets = momentum1_offsets;              \
+  ARGS.lr = learning_rate;                                 \
+  ARGS.eps = eps;                                          \
+  ARGS.part_rows = part_rows;                              \
+  ARGS.meta = meta;                                        \
+  ARGS.num_ctas = (int32_t)ctas;
+  if (key_bits > 32) {
+    BwdArgs<uint64_t> a;
+    a.keys = (const uint64_t*)sorted_keys;
+    B200_FILL(a);
+    return dispatch_w<uint64_t>(a, weight_dtype, all_D_mult8 != 0, optimizer, max_D, s);
+  }
+  BwdArgs<uint32_t> a;
+  a.keys = (const uint32_t*)sorted_keys;
+  B200_FILL(a);
+  return dispatch_w<uint32_t>(a, weight_dtype, all_D_mult8 != 0, optimizer, max_D, s);
+#undef B200_FILL
+}

@@ -1,0 +1,189 @@
+"""TEST INFRASTRUCTURE ONLY — CPU restatement (numpy) of the reference's pooled lookup,
+its fused backward+optimizer, the int8 rowwise path and the DLRM dot interaction.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this.
+Pinned against: the reference's own scalar C++ (third_party/fbgemm/src/RefImplementations.cc
+compiled unmodified into oracle/_ref/libfbgemm_ref.so, see oracle/Makefile), torch.nn.EmbeddingBag
+as the reference's tests do (fbgemm_gpu/test/split_table_batched_embeddings_test.py:322-415),
+and the InteractionArch golden tensor of torchrec/models/tests/test_dlrm.py:247-327.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def tbe_forward(weights, weights_offsets, D_offsets, indices, offsets, pooling_mean=False,
+                per_sample_weights=None, out_dtype=np.float32):
+    """fbgemm_gpu/codegen/embedding_forward_split_cpu.cpp:117-156 (scalar branch), same
+    arithmetic as EmbeddingSpMDM_ref (third_party/fbgemm/src/RefImplementations.cc:1186-1227):
+    acc = fma(w, row, acc) in fp32, MEAN scales by 1/L when L > 0; bag (t,b) at offsets[t*B+b]."""
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    total_D = int(D_offsets[-1])
+    out = np.zeros((B, total_D), dtype=np.float32)
+    for t in range(T):
+        d0, D = int(D_offsets[t]), int(D_offsets[t + 1] - D_offsets[t])
+        base = int(weights_offsets[t])
+        for b in range(B):
+            s, e = int(offsets[t * B + b]), int(offsets[t * B + b + 1])
+            acc = np.zeros(D, dtype=np.float32)
+            for p in range(s, e):
+                row = weights[base + int(indices[p]) * D: base + (int(indices[p]) + 1) * D].astype(np.float32)
+                if per_sample_weights is not None:
+                    acc = (np.float32(per_sample_weights[p]) * row + acc).astype(np.float32)
+                else:
+                    acc = acc + row
+            if pooling_mean and e > s:
+                acc = acc * np.float32(1.0 / (e - s))
+            out[b, d0:d0 + D] = acc
+    return out.astype(out_dtype)
+
+
+def tbe_backward(grad_output, weights, weights_offsets, D_offsets, hash_size_cumsum, indices, offsets,
+                 optimizer, lr, eps=0.0, momentum1=None, momentum1_offsets=None, pooling_mean=False,
+                 per_sample_weights=None):
+    """fbgemm_gpu/codegen/embedding_backward_split_cpu_template.cpp:193-224 (scalar branch) with
+    split_weight_update_cpu of rowwise_adagrad (embedding_backward_code_generator.py:402-415)
+    and sgd (:633-637); MEAN divides the bag gradient by L (grad_mean_kernel,
+    embedding_backward_split_template.cu:41-77).  Duplicates of one (table,row) are summed
+    first, then ONE update is applied.  Updates `weights` / `momentum1` in place (fp32 math,
+    result cast back to the weight dtype with round-to-nearest)."""
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    groups = {}
+    for t in range(T):
+        for b in range(B):
+            s, e = int(offsets[t * B + b]), int(offsets[t * B + b + 1])
+            for p in range(s, e):
+                key = int(hash_size_cumsum[t]) + int(indices[p])
+                groups.setdefault(key, []).append((t, b, p, e - s))
+    for key in sorted(groups):
+        occ = groups[key]
+        t0 = occ[0][0]
+        D = int(D_offsets[t0 + 1] - D_offsets[t0])
+        g = np.zeros(D, dtype=np.float32)
+        for (t, b, p, L) in occ:  # stable order: t-major, then b, then in-bag position
+            row = grad_output[b, int(D_offsets[t]): int(D_offsets[t]) + D].astype(np.float32)
+            sc = np.float32(1.0)
+            if pooling_mean:
+                sc = np.float32(1.0 / L)
+            if per_sample_weights is not None:
+                sc = np.float32(sc * np.float32(per_sample_weights[p]))
+            g = g + sc * row
+        idx = key - int(hash_size_cumsum[t0])
+        base = int(weights_offsets[t0]) + idx * D
+        w = weights[base: base + D].astype(np.float32)
+        if optimizer == "rowwise_adagrad":
+            g2 = np.float32(np.sum(g.astype(np.float64) ** 2) / D)
+            mi = int(momentum1_offsets[t0]) + idx
+            m = np.float32(momentum1[mi] + g2)
+            momentum1[mi] = m
+            mult = np.float32(lr) / (np.sqrt(m, dtype=np.float32) + np.float32(eps))
+            w = w - g * mult
+        elif optimizer == "sgd":
+            w = w - np.float32(lr) * g
+        else:
+            raise ValueError(optimizer)
+        weights[base: base + D] = w.astype(weights.dtype)
+
+
+def grad_indice_weights(grad_output, weights, weights_offsets, D_offsets, indices, offsets):
+    """fbgemm_gpu/codegen/embedding_forward_split_cpu.cpp:229-300
+    split_embedding_grad_indice_weights_cpu_kernel: g[p] = <grad_out[b, D_t], W_t[idx_p]>."""
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    out = np.zeros(len(indices), dtype=np.float32)
+    for t in range(T):
+        d0, D = int(D_offsets[t]), int(D_offsets[t + 1] - D_offsets[t])
+        base = int(weights_offsets[t])
+        for b in range(B):
+            for p in range(int(offsets[t * B + b]), int(offsets[t * B + b + 1])):
+                row = weights[base + int(indices[p]) * D: base + (int(indices[p]) + 1) * D].astype(np.float32)
+                out[p] = np.dot(grad_output[b, d0:d0 + D].astype(np.float32), row)
+    return out
+
+
+def quantize_rowwise_8bit_sbhalf(w):
+    """third_party/fbgemm/src/QuantUtils.cc:499-571 FloatOrHalfToFusedNBitRowwiseQuantizedSBHalfRef
+    with bit_rate 8: row = [ncols x uint8][fp16 scale][fp16 bias(min)]."""
+    w = np.asarray(w, dtype=np.float32)
+    nrows, ncols = w.shape
+    out = np.zeros((nrows, ncols + 4), dtype=np.uint8)
+    for r in range(nrows):
+        mn16 = np.float16(w[r].min())
+        mn = np.float32(mn16)
+        rng = np.float32(w[r].max()) - mn
+        scale = np.float32(1.0) if rng == 0 else np.float32(rng / np.float32(255))
+        scale = np.float32(np.float16(scale))
+        if scale == 0:
+            scale = np.float32(1.0)
+        with np.errstate(divide="ignore", over="ignore"):
+            inv = np.float32(1.0) / scale
+        if np.isinf(inv):
+            scale, inv = np.float32(1.0), np.float32(1.0)
+        q = np.rint((w[r] - mn) * inv)  # lrintf: round half to even
+        out[r, :ncols] = np.clip(q, 0, 255).astype(np.uint8)
+        out[r, ncols:ncols + 2] = np.frombuffer(np.float16(scale).tobytes(), dtype=np.uint8)
+        out[r, ncols + 2:] = np.frombuffer(mn16.tobytes(), dtype=np.uint8)
+    return out
+
+
+def int8_row_bytes(D, row_alignment=16):
+    """split_table_batched_embeddings_ops.py:1469-1485 rounded_row_size_in_bytes(INT8)."""
+    return (D + 4 + row_alignment - 1) // row_alignment * row_alignment
+
+
+def tbe_int8_forward(weights_u8, weights_offsets, D_offsets, indices, offsets, row_alignment=16,
+                     pooling_mean=False, per_sample_weights=None, out_dtype=np.float16):
+    """EmbeddingSpMDM_ref 8-bit branch with scale_bias_last=false
+    (third_party/fbgemm/src/RefImplementations.cc:1114-1179): row = [fp16 scale, fp16 bias, q...];
+    buf = fma(scale*w, q, buf + bias*w); idx == -1 is a pruned row (zeros,
+    embedding_forward_quantized_split_template.cu:276-278)."""
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    out = np.zeros((B, int(D_offsets[-1])), dtype=np.float32)
+    for t in range(T):
+        d0, D = int(D_offsets[t]), int(D_offsets[t + 1] - D_offsets[t])
+        rb = int8_row_bytes(D, row_alignment)
+        base = int(weights_offsets[t])
+        for b in range(B):
+            s, e = int(offsets[t * B + b]), int(offsets[t * B + b + 1])
+            acc = np.zeros(D, dtype=np.float32)
+            for p in range(s, e):
+                idx = int(indices[p])
+                if idx == -1:
+                    continue
+                row = weights_u8[base + idx * rb: base + idx * rb + 4 + D]
+                sb = np.frombuffer(row[:4].tobytes(), dtype=np.float16).astype(np.float32)
+                pw = np.float32(1.0) if per_sample_weights is None else np.float32(per_sample_weights[p])
+                sc, bi = np.float32(sb[0] * pw), np.float32(sb[1] * pw)
+                acc = (sc * row[4:4 + D].astype(np.float32) + (acc + bi)).astype(np.float32)
+            if pooling_mean and e > s:
+                acc = acc * np.float32(1.0 / (e - s))
+            out[b, d0:d0 + D] = acc
+    return out.astype(out_dtype)
+
+
+def interaction_forward(dense, sparse):
+    """torchrec/models/dlrm.py:193-219 InteractionArch.forward: X = cat(dense[:,None], sparse);
+    Z = bmm(X, X^T); out = cat(dense, Z[:, triu_indices(F+1, F+1, offset=1)]) (row-major)."""
+    B, D = dense.shape
+    X = np.concatenate([dense[:, None, :], sparse], axis=1).astype(np.float64)
+    Z = np.einsum("bid,bjd->bij", X, X)
+    iu = np.triu_indices(X.shape[1], k=1)
+    return np.concatenate([dense.astype(np.float64), Z[:, iu[0], iu[1]]], axis=1).astype(np.float32)
+
+
+def interaction_backward(dense, sparse, grad_out):
+    """Autograd of the above: dX = (G + G^T) X with G the strict upper triangle; the dense row
+    also receives grad_out[:, :D]."""
+    B, D = dense.shape
+    X = np.concatenate([dense[:, None, :], sparse], axis=1).astype(np.float64)
+    n = X.shape[1]
+    iu = np.triu_indices(n, k=1)
+    G = np.zeros((B, n, n), dtype=np.float64)
+    G[:, iu[0], iu[1]] = grad_out[:, D:]
+    Gs = G + G.transpose(0, 2, 1)
+    dX = np.einsum("bij,bjd->bid", Gs, X)
+    gd = dX[:, 0, :] + grad_out[:, :D]
+    return gd.astype(np.float32), dX[:, 1:, :].astype(np.float32)

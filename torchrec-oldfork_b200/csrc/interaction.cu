@@ -116,7 +116,8 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
   const int ldg = n + 1;
   const int grp = threadIdx.x / kIxGroup;
   const int tid = threadIdx.x % kIxGroup;
-  float* X = smem + (size_t)grp * (n * ld + n * ldg);
+  const int per_group = (n * ld + n * ldg + 3) & ~3;  // keep every group's X 16-byte aligned
+  float* X = smem + (size_t)grp * per_group;
   float* G = X + (size_t)n * ld;
   const int out_dim = D + n * (n - 1) / 2;
   const int D4 = D >> 2;
@@ -207,7 +208,7 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   const int n = F + 1;
-  const size_t smem = sizeof(float) * kIxSamplesPerCta * ((size_t)n * (D + 4) + (size_t)n * (n + 1));
+  const size_t smem = sizeof(float) * kIxSamplesPerCta * (((size_t)n * (D + 4) + (size_t)n * (n + 1) + 3) & ~(size_t)3);
   if (smem > 200 * 1024) return B200_EUNSUPPORTED;
   B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -1,0 +1,191 @@
+"""Sharded data movement modules (reference torchrec/distributed/dist_data.py: _get_recat :40,
+_split_lengths :121, KJTAllToAllIndicesAwaitable :137, KJTAllToAllLengthsAwaitable :276,
+KJTAllToAll :414, PooledEmbeddingsAllToAll :602, PooledEmbeddingsReduceScatter :745).
+
+Same two-phase protocol (lengths, then values/weights, NCCL all_to_all_single over NVLink) and
+the same rank-major -> feature-major recat through permute_2D_sparse_data.  One difference in
+host traffic: the single D2H read after the lengths exchange fetches the [W, F_local] table of
+per-(source rank, key) totals, which yields the receive split sizes AND the output KJT's
+length_per_key, so the second sync of the reference (from_lengths_sync, :266) disappears.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from torchrec.distributed.comm_ops import alltoall_pooled, reduce_scatter_pooled
+from torchrec.distributed.types import Awaitable, NoWait
+from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
+
+
+def _get_recat(local_split: int, num_splits: int, stagger: int = 1,
+               device: Optional[torch.device] = None) -> torch.Tensor:
+    """Permutation taking (source rank, local feature) order to (local feature, source rank):
+    _get_recat(2, 4, 1) == [0, 2, 4, 6, 1, 3, 5, 7]; _get_recat(2, 4, 2) == [0, 4, 2, 6, 1, 5, 3, 7]."""
+    if local_split == 0:
+        return torch.tensor([], device=device, dtype=torch.int32)
+    per = num_splits // stagger
+    rank_order = [x + per * y for x in range(per) for y in range(stagger)]
+    return torch.tensor([f + r * local_split for f in range(local_split) for r in rank_order],
+                        device=device, dtype=torch.int32)
+
+
+def _split_lengths(splits: List[int], keys: List[str], offset_per_key: List[int]) -> List[int]:
+    """Number of ids destined to each rank: keys are ordered by destination, `splits` keys per rank."""
+    out, k = [], 0
+    for s in splits:
+        out.append(offset_per_key[k + s] - offset_per_key[k])
+        k += s
+    return out
+
+
+class KJTAllToAllIndicesAwaitable(Awaitable[KeyedJaggedTensor]):
+    """Phase 2: values (+weights) exchange, then recat to feature-major."""
+
+    def __init__(self, pg, input: KeyedJaggedTensor, lengths: torch.Tensor, splits: List[int], keys: List[str],
+                 recat: torch.Tensor, in_lengths_per_worker: List[int], out_lengths_per_worker: List[int],
+                 batch_size_per_rank: List[int], length_per_key: Optional[List[int]] = None) -> None:
+        super().__init__()
+        self._pg, self._input, self._lengths, self._splits = pg, input, lengths, splits
+        self._keys, self._recat = keys, recat
+        self._workers = dist.get_world_size(pg)
+        self._batch_size_per_rank = batch_size_per_rank
+        self._length_per_key = length_per_key
+        self._works: List = []
+        self._values: Optional[torch.Tensor] = None
+        self._weights: Optional[torch.Tensor] = None
+        if self._workers == 1:
+            return
+        total = sum(out_lengths_per_worker)
+
+        def exchange(t: torch.Tensor) -> torch.Tensor:
+            src = t.contiguous().view(-1)
+            dst = src.new_empty(total)
+            self._works.append(dist.all_to_all_single(dst, src, output_split_sizes=out_lengths_per_worker,
+                                                      input_split_sizes=in_lengths_per_worker, group=pg,
+                                                      async_op=True))
+            return dst
+
+        self._values = exchange(input.values())
+        if input.weights_or_none() is not None:
+            self._weights = exchange(input.weights())
+
+    def _wait_impl(self) -> KeyedJaggedTensor:
+        if self._workers == 1:
+            return self._input.sync()
+        for w in self._works:
+            w.wait()
+        lengths, values, weights = self._lengths, self._values, self._weights
+        if self._recat.numel() > 0:
+            rows = self._workers * self._splits[dist.get_rank(self._pg)]
+            lengths, values, weights = torch.ops.fbgemm.permute_2D_sparse_data(
+                self._recat, lengths.view(rows, -1), values, weights, values.numel())
+            lengths = lengths.view(-1)
+        return KeyedJaggedTensor(keys=self._keys, values=values, weights=weights, lengths=lengths,
+                                 stride=sum(self._batch_size_per_rank), length_per_key=self._length_per_key)
+
+
+class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
+    """Phase 1: lengths exchange; wait() reads the receive sizes and starts phase 2."""
+
+    def __init__(self, pg, input: KeyedJaggedTensor, splits: List[int], keys: List[str], recat: torch.Tensor) -> None:
+        super().__init__()
+        self._pg, self._input, self._splits, self._keys, self._recat = pg, input, splits, keys, recat
+        self._workers = dist.get_world_size(pg)
+        self._local_split = splits[dist.get_rank(pg)]
+        B = input.stride()
+        self._batch_size_per_rank = [B] * self._workers
+        self._lengths = input.lengths()
+        self._in_lengths_per_worker: List[int] = []
+        self._work = None
+        if self._workers == 1:
+            return
+        src = input.lengths().contiguous().view(-1)
+        self._lengths = src.new_empty(self._local_split * B * self._workers)
+        self._in_lengths_per_worker = _split_lengths(splits, input.keys(), input.offset_per_key())
+        self._work = dist.all_to_all_single(
+            self._lengths, src, output_split_sizes=[self._local_split * B] * self._workers,
+            input_split_sizes=[s * B for s in splits], group=pg, async_op=True)
+
+    def _wait_impl(self) -> KJTAllToAllIndicesAwaitable:
+        out_lengths_per_worker: List[int] = []
+        length_per_key: Optional[List[int]] = None
+        if self._workers > 1:
+            self._work.wait()
+            if self._local_split > 0:
+                # one D2H read: [W, F_local] totals -> receive splits and per-key totals
+                table = self._lengths.view(self._workers, self._local_split, -1).sum(dim=2).cpu()
+                out_lengths_per_worker = table.sum(dim=1).tolist()
+                length_per_key = table.sum(dim=0).tolist()
+            else:
+                out_lengths_per_worker = [0] * self._workers
+                length_per_key = []
+        return KJTAllToAllIndicesAwaitable(
+            self._pg, self._input, self._lengths, self._splits, self._keys, self._recat,
+            self._in_lengths_per_worker, out_lengths_per_worker, self._batch_size_per_rank, length_per_key)
+
+
+class KJTAllToAll(nn.Module):
+    """Redistributes a KJT whose keys are ordered by destination rank (`splits[r]` keys to rank r)."""
+
+    def __init__(self, pg: dist.ProcessGroup, splits: List[int], device: Optional[torch.device] = None,
+                 stagger: int = 1, variable_batch_size: bool = False) -> None:
+        super().__init__()
+        assert len(splits) == dist.get_world_size(pg)
+        if variable_batch_size:
+            raise NotImplementedError("variable batch size per rank is out of scope (SURVEY.md §8 f3)")
+        self._pg, self._splits = pg, splits
+        self._no_dist = all(s == 0 for s in splits)
+        self._splits_cumsum = [0]
+        for s in splits:
+            self._splits_cumsum.append(self._splits_cumsum[-1] + s)
+        self.register_buffer("_recat", _get_recat(splits[dist.get_rank(pg)], len(splits), stagger, device),
+                             persistent=False)
+
+    def forward(self, input: KeyedJaggedTensor) -> Awaitable[KJTAllToAllIndicesAwaitable]:
+        rank = dist.get_rank(self._pg)
+        keys = input.keys()[self._splits_cumsum[rank]:self._splits_cumsum[rank + 1]]
+        return KJTAllToAllLengthsAwaitable(self._pg, input, self._splits, keys, self._recat)
+
+
+class PooledEmbeddingsAwaitable(Awaitable[torch.Tensor]):
+    def __init__(self, tensor_awaitable: Awaitable[torch.Tensor]) -> None:
+        super().__init__()
+        self._tensor_awaitable = tensor_awaitable
+
+    def _wait_impl(self) -> torch.Tensor:
+        return self._tensor_awaitable.wait()
+
+
+class PooledEmbeddingsAllToAll(nn.Module):
+    """[B_global, D_local_sum] -> [B_local, sum_r dim_sum_per_rank[r]] (table-wise output dist)."""
+
+    def __init__(self, pg: dist.ProcessGroup, dim_sum_per_rank: List[int],
+                 device: Optional[torch.device] = None, callbacks=None) -> None:
+        super().__init__()
+        self._pg, self._dim_sum_per_rank = pg, dim_sum_per_rank
+        self._callbacks = callbacks or []
+
+    def forward(self, local_embs: torch.Tensor, batch_size_per_rank: Optional[List[int]] = None
+                ) -> PooledEmbeddingsAwaitable:
+        aw = PooledEmbeddingsAwaitable(alltoall_pooled(local_embs, self._dim_sum_per_rank, group=self._pg))
+        aw.callbacks.extend(self._callbacks)
+        return aw
+
+    @property
+    def callbacks(self):
+        return self._callbacks
+
+
+class PooledEmbeddingsReduceScatter(nn.Module):
+    """Sum over ranks of [B_global, D], scattered along the batch (row-wise output dist)."""
+
+    def __init__(self, pg: dist.ProcessGroup) -> None:
+        super().__init__()
+        self._pg = pg
+
+    def forward(self, local_embs: torch.Tensor) -> PooledEmbeddingsAwaitable:
+        return PooledEmbeddingsAwaitable(reduce_scatter_pooled(local_embs, self._pg))

@@ -1,0 +1,80 @@
+"""Grouped pooled lookups (reference torchrec/distributed/embedding_lookup.py:
+GroupedPooledEmbeddingsLookup :209, forward :287-337): the local KJT is split per kernel group,
+each group runs ONE table-batched lookup, outputs are concatenated along the embedding dim."""
+from __future__ import annotations
+
+from typing import Any, Dict, Iterator, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from torchrec.distributed.batched_embedding_kernel import BatchedFusedEmbeddingBag
+from torchrec.distributed.embedding_sharding import BaseEmbeddingLookup
+from torchrec.distributed.embedding_types import (
+    EmbeddingComputeKernel, GroupedEmbeddingConfig, SparseFeatures)
+from torchrec.optim.fused import FusedOptimizerModule
+from torchrec.optim.keyed import CombinedOptimizer, KeyedOptimizer
+
+
+class GroupedPooledEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Tensor], FusedOptimizerModule):
+    def __init__(self, grouped_configs: List[GroupedEmbeddingConfig],
+                 grouped_score_configs: List[GroupedEmbeddingConfig],
+                 device: Optional[torch.device] = None, pg: Optional[dist.ProcessGroup] = None,
+                 fused_params: Optional[Dict[str, Any]] = None, feature_processor=None) -> None:
+        super().__init__()
+        if feature_processor is not None:
+            raise NotImplementedError("feature processors are out of scope")
+
+        def make(cfg: GroupedEmbeddingConfig) -> nn.Module:
+            if cfg.compute_kernel != EmbeddingComputeKernel.BATCHED_FUSED:
+                raise NotImplementedError(
+                    f"compute kernel {cfg.compute_kernel} is not built; only BATCHED_FUSED (SURVEY.md §8 a11)")
+            return BatchedFusedEmbeddingBag(cfg, pg=pg, device=device, fused_params=fused_params)
+
+        self._emb_modules = nn.ModuleList([make(c) for c in grouped_configs])
+        self._score_emb_modules = nn.ModuleList([make(c) for c in grouped_score_configs])
+        self._id_list_feature_splits = [c.num_features() for c in grouped_configs]
+        self._id_score_list_feature_splits = [c.num_features() for c in grouped_score_configs]
+        self.grouped_configs = grouped_configs
+        self.grouped_score_configs = grouped_score_configs
+        self._device = device
+        self._dim_sum = sum(c.dim_sum() for c in grouped_configs) + sum(c.dim_sum() for c in grouped_score_configs)
+
+    def forward(self, sparse_features: SparseFeatures) -> torch.Tensor:
+        outs: List[torch.Tensor] = []
+        if self._emb_modules:
+            assert sparse_features.id_list_features is not None
+            parts = sparse_features.id_list_features.split(self._id_list_feature_splits)
+            outs.extend(m(f) for m, f in zip(self._emb_modules, parts))
+        if self._score_emb_modules:
+            assert sparse_features.id_score_list_features is not None
+            parts = sparse_features.id_score_list_features.split(self._id_score_list_feature_splits)
+            outs.extend(m(f) for m, f in zip(self._score_emb_modules, parts))
+        if len(outs) == 0:
+            kjt = sparse_features.id_list_features or sparse_features.id_score_list_features
+            B = kjt.stride() if kjt is not None else 0
+            return torch.empty((B, 0), device=self._device)
+        return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
+
+    def _all_modules(self) -> List[nn.Module]:
+        return list(self._emb_modules) + list(self._score_emb_modules)
+
+    def state_dict(self, destination=None, prefix: str = "", keep_vars: bool = False) -> Dict[str, Any]:
+        if destination is None:
+            destination = {}
+        for m in self._all_modules():
+            m.state_dict(destination, prefix, keep_vars)
+        return destination
+
+    def named_parameters(self, prefix: str = "", recurse: bool = True):
+        yield from ()
+
+    def named_buffers(self, prefix: str = "", recurse: bool = True):
+        for m in self._all_modules():
+            yield from m.named_buffers(prefix, recurse)
+
+    @property
+    def fused_optimizer(self) -> KeyedOptimizer:
+        return CombinedOptimizer([m.fused_optimizer for m in self._all_modules()
+                                  if isinstance(m, FusedOptimizerModule)])

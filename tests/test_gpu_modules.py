@@ -1,0 +1,171 @@
+"""GPU parity at the module boundary: TBE module vs nn.EmbeddingBag + closed-form optimizer (the
+reference's own oracle pattern, fbgemm_gpu/test/split_table_batched_embeddings_test.py:322-415,
+1756-1785), KJT ops, sharded-vs-unsharded one-step parity
+(torchrec/distributed/test_utils/test_model_parallel_base.py:144-290), quantized EBC, DLRM."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pg():
+    import torch.distributed as dist
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1)
+    yield dist.group.WORLD
+
+
+def _tbe(rows, dims, opt, **kw):
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from fbgemm_gpu.split_table_batched_embeddings_ops import (
+        ComputeDevice, EmbeddingLocation, SplitTableBatchedEmbeddingBagsCodegen)
+    return SplitTableBatchedEmbeddingBagsCodegen(
+        [(r, d, EmbeddingLocation.DEVICE, ComputeDevice.CUDA) for r, d in zip(rows, dims)],
+        optimizer=getattr(EmbOptimType, opt), device=torch.device("cuda"), **kw)
+
+
+@pytest.mark.parametrize("opt", ["EXACT_SGD", "EXACT_ROWWISE_ADAGRAD"])
+@pytest.mark.parametrize("pooling", ["SUM", "MEAN"])
+@pytest.mark.parametrize("weighted", [False, True])
+def test_tbe_module_vs_embedding_bag(opt, pooling, weighted):
+    from fbgemm_gpu.split_table_batched_embeddings_ops import PoolingMode
+    if weighted and pooling == "MEAN":
+        pytest.skip("MEAN pooling ignores per-sample weights in nn.EmbeddingBag")
+    torch.manual_seed(1)
+    rows, dims, B, L = [40, 9, 300], [16, 32, 8], 50, 4
+    lr, eps = 0.1, 1e-4
+    m = _tbe(rows, dims, opt, learning_rate=lr, eps=eps, pooling_mode=getattr(PoolingMode, pooling))
+    m.init_embedding_weights_uniform(-1.0, 1.0)
+    bags = [torch.nn.EmbeddingBag(r, d, mode=pooling.lower(), sparse=False, include_last_offset=True).cuda()
+            for r, d in zip(rows, dims)]
+    for b, w in zip(bags, m.split_embedding_weights()):
+        b.weight.data.copy_(w)
+    lengths = torch.randint(0, L + 1, (len(rows), B))
+    idx = [torch.randint(0, r, (int(lengths[t].sum()),)) for t, r in enumerate(rows)]
+    offs = [torch.cat([torch.zeros(1, dtype=torch.long), lengths[t].cumsum(0)]) for t in range(len(rows))]
+    psw = [torch.rand(i.numel()) for i in idx] if weighted else None
+    indices = torch.cat(idx).cuda()
+    offsets = torch.cat([torch.zeros(1, dtype=torch.long), lengths.view(-1).cumsum(0)]).cuda()
+    psw_all = torch.cat(psw).cuda().requires_grad_(True) if weighted else None
+    out = m(indices, offsets, psw_all)
+    ref_psw = [p.cuda().requires_grad_(True) for p in psw] if weighted else [None] * len(rows)
+    ref = torch.cat([b(i.cuda(), o.cuda(), per_sample_weights=p) for b, i, o, p in zip(bags, idx, offs, ref_psw)], 1)
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+    go = torch.randn_like(out)
+    out.backward(go)
+    ref.backward(go)
+    for t, (b, w) in enumerate(zip(bags, m.split_embedding_weights())):
+        g = b.weight.grad
+        if opt == "EXACT_SGD":
+            exp = b.weight.data - lr * g
+        else:
+            state = g.pow(2).mean(dim=1)
+            exp = torch.addcdiv(b.weight.data, g, (state.sqrt() + eps).unsqueeze(1), value=-lr)
+            touched = torch.unique(idx[t]).cuda()
+            torch.testing.assert_close(m.split_optimizer_states()[t][0][touched], state[touched],
+                                       rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(w, exp, rtol=1e-4, atol=1e-4)
+    if weighted:
+        torch.testing.assert_close(psw_all.grad, torch.cat([p.grad for p in ref_psw]), rtol=1e-4, atol=1e-4)
+
+
+def test_kjt_reference_vectors():
+    # torchrec/sparse/tests/test_jagged_tensor.py: test_permute :671, test_split :577, test_to_dict :549
+    from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
+    values = torch.tensor([1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0]).cuda()
+    lengths = torch.tensor([0, 2, 0, 1, 1, 1, 0, 3, 0], dtype=torch.int32).cuda()
+    kjt = KeyedJaggedTensor.from_lengths_sync(keys=["index_0", "index_1", "index_2"], values=values, lengths=lengths)
+    p = kjt.permute([1, 0, 2])
+    assert p.keys() == ["index_1", "index_0", "index_2"]
+    assert p.values().tolist() == [3, 4, 5, 1, 2, 6, 7, 8]
+    assert p.lengths().tolist() == [1, 1, 1, 0, 2, 0, 0, 3, 0]
+    assert kjt.offsets().tolist() == [0, 0, 2, 2, 3, 4, 5, 5, 8, 8]
+    d = kjt.to_dict()
+    assert d["index_1"].values().tolist() == [3, 4, 5] and d["index_1"].offsets().tolist() == [0, 1, 2, 3]
+    a, b = kjt.split([1, 2])
+    assert a.keys() == ["index_0"] and a.values().tolist() == [1, 2] and b.lengths().tolist() == [1, 1, 1, 0, 3, 0]
+    dup = kjt.permute([2, 0, 0])  # test_permute_duplicates :704
+    assert dup.values().tolist() == [6, 7, 8, 1, 2, 1, 2]
+
+
+def _make_dlrm(tables, dense_in, dev, meta=True):
+    from torchrec import EmbeddingBagCollection
+    from torchrec.models.dlrm import DLRM
+    ebc = EmbeddingBagCollection(tables, device=torch.device("meta") if meta else dev)
+    return DLRM(ebc, dense_in, [32, tables[0].embedding_dim], [32, 16, 1], dense_device=dev)
+
+
+@pytest.mark.parametrize("sharding", ["table_wise", "row_wise"])
+def test_sharded_vs_unsharded_one_step(pg, sharding):
+    """global (unsharded nn.EmbeddingBag, SGD) vs local (DMP + fused EXACT_SGD) after ONE step."""
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from torchrec import EmbeddingBagConfig
+    from torchrec.datasets.random import RandomRecDataset
+    from torchrec.distributed import DistributedModelParallel, ShardingEnv
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.planner import EmbeddingShardingPlanner, ParameterConstraints, Topology
+    torch.manual_seed(0)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda")
+    rows = [50, 7, 1000, 3]
+    D, B, lr = 16, 64, 0.1
+    keys = [f"f{i}" for i in range(len(rows))]
+    mk = lambda: [EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r, feature_names=[keys[i]])  # noqa
+                  for i, r in enumerate(rows)]
+    glob = _make_dlrm(mk(), 13, dev, meta=False)
+    local = _make_dlrm(mk(), 13, dev, meta=True)
+    sharders = [EmbeddingBagCollectionSharder(fused_params={"learning_rate": lr, "optimizer": EmbOptimType.EXACT_SGD})]
+    plan = EmbeddingShardingPlanner(Topology(1), {f"t{i}": ParameterConstraints(sharding_types=[sharding])
+                                                  for i in range(len(rows))}).plan(local, sharders)
+    dmp = DistributedModelParallel(local, env=ShardingEnv.from_process_group(pg), device=dev, plan=plan,
+                                   sharders=sharders)
+    # copy weights global -> local
+    gsd = glob.state_dict()
+    lsd = dmp.state_dict()
+    for k, v in lsd.items():
+        v.data.copy_(gsd[k])
+    batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=3, num_dense=13,
+                                       manual_seed=3))).to(dev)
+    dense_opt_g = torch.optim.SGD(glob.parameters(), lr=lr)
+    dense_opt_l = torch.optim.SGD([p for p in dmp.parameters()], lr=lr)
+    for model, opt in ((glob, dense_opt_g), (dmp, dense_opt_l)):
+        opt.zero_grad()
+        out = model(batch.dense_features, batch.sparse_features)
+        out.sum().backward()
+        opt.step()
+    with torch.no_grad():
+        pg_, pl_ = glob(batch.dense_features, batch.sparse_features), dmp(batch.dense_features, batch.sparse_features)
+    torch.testing.assert_close(pl_, pg_, rtol=1e-4, atol=1e-4)
+    for k, v in dmp.state_dict().items():
+        torch.testing.assert_close(v, glob.state_dict()[k], rtol=1e-4, atol=1e-5, msg=k)
+
+
+def test_quantized_ebc():
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig, KeyedJaggedTensor
+    from torchrec.quant.embedding_modules import EmbeddingBagCollection as QuantEBC
+    torch.manual_seed(2)
+    dev = torch.device("cuda")
+    rows, D, B = [100, 30, 500], 128, 33
+    keys = ["a", "b", "c"]
+    ebc = EmbeddingBagCollection([EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r,
+                                                     feature_names=[keys[i]]) for i, r in enumerate(rows)], device=dev)
+    ebc.qconfig = torch.quantization.QConfig(activation=torch.quantization.PlaceholderObserver,
+                                             weight=torch.quantization.PlaceholderObserver.with_args(dtype=torch.qint8))
+    q = QuantEBC.from_float(ebc)
+    lengths = torch.randint(0, 4, (len(rows) * B,), dtype=torch.int32)
+    vals = torch.cat([torch.randint(0, r, (int(lengths[i * B:(i + 1) * B].sum()),)) for i, r in enumerate(rows)])
+    kjt = KeyedJaggedTensor.from_lengths_sync(keys=keys, values=vals.cuda(), lengths=lengths.cuda())
+    ref = ebc(kjt).values()
+    got = q(kjt)
+    assert got.keys() == keys
+    # int8 rowwise error: |x - deq(x)| <= scale/2 = range/510 per element, times L <= 3 ids
+    torch.testing.assert_close(got.values(), ref, rtol=0.0, atol=3 * 2.0 / 510 * 4 + 2e-2)
+    # state_dict layout: [rows, 16-byte-aligned 4 + D] uint8 per table
+    sd = q.state_dict()
+    assert sd["embedding_bags.t0.weight"].shape == (100, 144)

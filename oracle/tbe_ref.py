@@ -30,11 +30,13 @@ def tbe_forward(weights, weights_offsets, D_offsets, indices, offsets, pooling_m
             for p in range(s, e):
                 row = weights[base + int(indices[p]) * D: base + (int(indices[p]) + 1) * D].astype(np.float32)
                 if per_sample_weights is not None:
-                    acc = (np.float32(per_sample_weights[p]) * row + acc).astype(np.float32)
+                    # std::fma(w, x, acc): the float64 product of two float32 is exact
+                    acc = (np.float64(np.float32(per_sample_weights[p])) * row.astype(np.float64)
+                           + acc.astype(np.float64)).astype(np.float32)
                 else:
                     acc = acc + row
             if pooling_mean and e > s:
-                acc = acc * np.float32(1.0 / (e - s))
+                acc = acc * (np.float32(1.0) / np.float32(e - s))
             out[b, d0:d0 + D] = acc
     return out.astype(out_dtype)
 
@@ -157,9 +159,10 @@ def tbe_int8_forward(weights_u8, weights_offsets, D_offsets, indices, offsets, r
                 sb = np.frombuffer(row[:4].tobytes(), dtype=np.float16).astype(np.float32)
                 pw = np.float32(1.0) if per_sample_weights is None else np.float32(per_sample_weights[p])
                 sc, bi = np.float32(sb[0] * pw), np.float32(sb[1] * pw)
-                acc = (sc * row[4:4 + D].astype(np.float32) + (acc + bi)).astype(np.float32)
+                acc = (np.float64(sc) * row[4:4 + D].astype(np.float64)
+                       + (acc + bi).astype(np.float64)).astype(np.float32)  # fma(scale, q, buf + bias)
             if pooling_mean and e > s:
-                acc = acc * np.float32(1.0 / (e - s))
+                acc = acc * (np.float32(1.0) / np.float32(e - s))
             out[b, d0:d0 + D] = acc
     return out.astype(out_dtype)
 

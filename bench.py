@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py — DLRM (Criteo-1TB / MLPerf shape) training throughput on the B200 sparse path.
+
+  python bench.py --gpus N --steps K --warmup W            (N = 1; N > 1 under torchrun)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+One "step" = one full training step (dense MLPs on cuBLAS via PyTorch, pooled lookup, dot
+interaction, loss, backward with the fused rowwise-Adagrad update, dense SGD) over one batch of
+Criteo-shaped synthetic data (RandomRecDataset shape): 26 tables capped at 40 M rows, dim 128,
+fp32, local batch 65536 per GPU (weak scaling), table-wise sharding at N = 1 and table-wise +
+row-wise at N > 1.  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "torchrec-oldfork_b200"))
+sys.path.insert(0, ROOT)
+
+CRITEO_ROWS = [40000000, 39060, 17295, 7424, 20265, 3, 7122, 1543, 63, 40000000, 3067956, 405282, 10, 2209,
+               11938, 155, 4, 976, 14, 40000000, 40000000, 40000000, 590152, 12973, 108, 36]
+DENSE_IN = 13
+DENSE_ARCH = [512, 256, 128]
+OVER_ARCH = [1024, 1024, 512, 256, 1]
+EMB_DIM = 128
+LR, EPS = 0.01, 1e-8
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=65536, help="local batch per GPU")
+    ap.add_argument("--row-cap", type=int, default=40000000)
+    ap.add_argument("--cpu-batch", type=int, default=8192, help="batch of the bounded CPU sample")
+    ap.add_argument("--cpu-row-cap", type=int, default=1000000, help="row cap of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+def algorithmic_bytes(N_ids: int, B: int, T: int, D: int, U: int, wbytes: int = 4) -> dict:
+    """SURVEY.md §8(d) / BASELINE.md §3."""
+    fwd = N_ids * D * wbytes + B * T * D * 4 + N_ids * 8 + (T * B + 1) * 8
+    bwd = N_ids * D * 4 + 2 * U * D * wbytes + 2 * U * 4 + N_ids * 8 + (T * B + 1) * 8
+    return {"fwd": fwd, "bwd": bwd}
+
+
+def table_configs(rows):
+    from torchrec import EmbeddingBagConfig
+    from torchrec.datasets.criteo import DEFAULT_CAT_NAMES
+    return [EmbeddingBagConfig(name=f"t_{n}", embedding_dim=EMB_DIM, num_embeddings=r, feature_names=[n])
+            for n, r in zip(DEFAULT_CAT_NAMES, rows)]
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the reference algorithm on the host cores (oracle port; bounded sample)
+class CpuDLRM:
+    """DLRM train step on the CPU: torch MLPs + the oracle's C restatement of the reference's CPU
+    pooled lookup / fused rowwise-Adagrad backward (oracle/tbe_ref.c) + the reference's bmm/triu
+    interaction formulation (torchrec/models/dlrm.py:193-219)."""
+
+    def __init__(self, rows, batch: int, seed: int = 0) -> None:
+        from oracle import c_oracle
+        self.c = c_oracle
+        self.c.lib()
+        torch.manual_seed(seed)
+        self.rows, self.B, self.T, self.D = rows, batch, len(rows), EMB_DIM
+        rng = np.random.default_rng(seed)
+        self.hsc = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
+        self.wo = (self.hsc[:-1] * self.D).astype(np.int64)
+        self.Do = np.arange(0, (self.T + 1) * self.D, self.D, dtype=np.int32)
+        self.weights = (rng.random(int(self.hsc[-1]) * self.D, dtype=np.float32) - 0.5) * 0.02
+        self.mom = np.zeros(int(self.hsc[-1]), dtype=np.float32)
+        from torchrec.modules.mlp import MLP
+        n = self.T + 1
+        self.dense = MLP(DENSE_IN, DENSE_ARCH)
+        self.over = torch.nn.Sequential(MLP(self.D + n * (n - 1) // 2, OVER_ARCH[:-1]),
+                                        torch.nn.Linear(OVER_ARCH[-2], OVER_ARCH[-1]))
+        self.opt = torch.optim.SGD(list(self.dense.parameters()) + list(self.over.parameters()), lr=0.1)
+        self.triu = torch.triu_indices(n, n, offset=1)
+        self.loss_fn = torch.nn.BCEWithLogitsLoss()
+        self.batches = []
+        for s in range(2):
+            g = np.random.default_rng(100 + s)
+            idx = np.concatenate([g.integers(0, r, size=batch) for r in rows]).astype(np.int64)
+            self.batches.append((idx, np.arange(self.T * batch + 1, dtype=np.int64),
+                                 torch.randn(batch, DENSE_IN), torch.randint(0, 2, (batch,)).float()))
+
+    def step(self, i: int) -> float:
+        idx, off, dense_in, labels = self.batches[i % len(self.batches)]
+        pooled = self.c.tbe_forward(self.weights, self.wo, self.Do, idx, off)
+        sparse = torch.from_numpy(pooled).view(self.B, self.T, self.D).requires_grad_(True)
+        self.opt.zero_grad(set_to_none=True)
+        d = self.dense(dense_in)
+        x = torch.cat([d.unsqueeze(1), sparse], dim=1)
+        z = torch.bmm(x, x.transpose(1, 2))
+        inter = torch.cat([d, z[:, self.triu[0], self.triu[1]]], dim=1)
+        loss = self.loss_fn(self.over(inter).squeeze(), labels)
+        loss.backward()
+        self.opt.step()
+        self.c.tbe_backward(sparse.grad.view(self.B, self.T * self.D).numpy(), self.weights, self.wo, self.Do,
+                            self.hsc, idx, off, "rowwise_adagrad", LR, EPS, self.mom, self.hsc[:-1])
+        return float(loss.detach())
+
+
+def time_cpu_arm(args, steps: int, warmup: int) -> dict:
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    rows = [min(r, args.cpu_row_cap) for r in CRITEO_ROWS]
+    model = CpuDLRM(rows, args.cpu_batch)
+    for i in range(warmup):
+        model.step(i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        model.step(i)
+    dt = time.perf_counter() - t0
+    return {"value": args.cpu_batch * steps / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+            "ms_per_step": dt / steps * 1e3,
+            "sample": f"same DLRM step, batch {args.cpu_batch}, tables row-capped at {args.cpu_row_cap}, "
+                      f"{steps} steps after {warmup} warm-up, oracle/tbe_ref.c (OpenMP) + torch CPU MLPs"}
+
+
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = min(args.steps, 10)
+    r = time_cpu_arm(args, steps, max(2, min(args.warmup, 3)))
+    line = {
+        "impl": "reference", "metric": "dlrm_train_samples_per_sec", "value": r["value"], "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": max(2, min(args.warmup, 3)), "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "DLRM Criteo-1TB (MLPerf) shape, 26 tables dim 128 fp32, fused rowwise Adagrad; "
+                               "reference CPU algorithm on host cores over a bounded sample", "sample": r["sample"]},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+def build_gpu_model(args, rank: int, world: int, dev: torch.device, pg):
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from torchrec import EmbeddingBagCollection
+    from torchrec.distributed import DistributedModelParallel, ShardingEnv
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.planner import EmbeddingShardingPlanner, ParameterConstraints, Topology
+    from torchrec.models.dlrm import DLRMTrain
+    rows = [min(r, args.row_cap) for r in CRITEO_ROWS]
+    tables = table_configs(rows)
+    model = DLRMTrain(EmbeddingBagCollection(tables, device=torch.device("meta")), DENSE_IN, DENSE_ARCH, OVER_ARCH,
+                      dense_device=dev)
+    sharders = [EmbeddingBagCollectionSharder(fused_params={
+        "optimizer": EmbOptimType.EXACT_ROWWISE_ADAGRAD, "learning_rate": LR, "eps": EPS})]
+    constraints = {}
+    for cfg in tables:
+        rw = world > 1 and cfg.num_embeddings >= 3_000_000
+        constraints[cfg.name] = ParameterConstraints(sharding_types=["row_wise" if rw else "table_wise"],
+                                                     compute_kernels=["batched_fused"])
+    plan = EmbeddingShardingPlanner(Topology(world, "cuda"), constraints).plan(model, sharders)
+    dmp = DistributedModelParallel(model, env=ShardingEnv.from_process_group(pg), device=dev, plan=plan,
+                                   sharders=sharders)
+    dense_opt = torch.optim.SGD([p for p in dmp.parameters() if p.requires_grad], lr=0.1)
+    return dmp, dense_opt, rows
+
+
+def make_batches(rows, B: int, rank: int, n: int):
+    from torchrec.datasets.criteo import DEFAULT_CAT_NAMES
+    from torchrec.datasets.random import RandomRecDataset
+    out = []
+    for s in range(n):
+        ds = RandomRecDataset(keys=DEFAULT_CAT_NAMES, batch_size=B, hash_sizes=rows, ids_per_feature=1,
+                              num_dense=DENSE_IN, manual_seed=1000 * rank + s + 1, num_generated_batches=1)
+        out.append(next(iter(ds)).pin_memory())
+    return out
+
+
+def batch_bytes(b) -> int:
+    kjt = b.sparse_features
+    n = b.dense_features.numel() * b.dense_features.element_size() + b.labels.numel() * b.labels.element_size()
+    n += kjt.values().numel() * kjt.values().element_size() + kjt.lengths().numel() * kjt.lengths().element_size()
+    return n
+
+
+def lookup_shapes(dmp, batch):
+    """(N_ids, B, T, U) of every table-batched lookup this rank runs for `batch` (rank-local)."""
+    from torchrec.distributed.types import ShardedModule
+    shapes = []
+    for m in dmp.module.modules():
+        if isinstance(m, ShardedModule):
+            with torch.no_grad():
+                dist_in = m.input_dist(m.create_context(), batch.sparse_features).wait()
+            for sf in dist_in:
+                kjt = sf.id_list_features
+                if kjt is None or len(kjt.keys()) == 0:
+                    continue
+                U = sum(int(torch.unique(jt.values()).numel()) for jt in kjt.to_dict().values())
+                shapes.append((int(kjt.values().numel()), int(kjt.stride()), len(kjt.keys()), U))
+    return shapes
+
+
+def run_ours(args) -> None:
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for "
+                         "the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29571")
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    pg = dist.group.WORLD
+    torch.backends.cuda.matmul.allow_tf32 = True  # reference-era PyTorch default for the MLP GEMMs
+    torch.backends.cudnn.allow_tf32 = True
+    from b200_sparse.ops import KernelProfile
+
+    dmp, dense_opt, rows = build_gpu_model(args, rank, world, dev, pg)
+    host_batches = make_batches(rows, args.batch, rank, 4)
+    dev_batches = [b.to(dev) for b in host_batches]
+    torch.cuda.synchronize()
+
+    def train_step(batch):
+        dense_opt.zero_grad(set_to_none=True)
+        loss, _ = dmp(batch)
+        loss.backward()
+        dense_opt.step()
+        return loss
+
+    def timed(fn, steps):
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for i in range(max(args.warmup, 3)):
+        train_step(dev_batches[i % len(dev_batches)])
+    torch.cuda.synchronize()
+    shapes = lookup_shapes(dmp, dev_batches[0]) if rank == 0 else []
+
+    # ---- value: inputs resident in HBM
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    KernelProfile.reset(enabled=True)
+    ms_total = timed(lambda i: train_step(dev_batches[i % len(dev_batches)]), args.steps)
+    launches = KernelProfile.launches
+    kern = KernelProfile.summary_ms()
+    KernelProfile.reset(enabled=False)
+    clocks = sampler.stop() if rank == 0 else {}
+
+    # ---- e2e: pinned host batch -> H2D every step, loss read back every step
+    def e2e_step(i):
+        b = host_batches[i % len(host_batches)].to(dev, non_blocking=True)
+        return float(train_step(b).item())
+
+    for i in range(2):
+        e2e_step(i)
+    ms_e2e = timed(e2e_step, args.steps)
+
+    if rank != 0:
+        dist.destroy_process_group()
+        return
+    global_batch = args.batch * world
+    value = global_batch * args.steps / (ms_total / 1e3)
+    e2e_value = global_batch * args.steps / (ms_e2e / 1e3)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
+    alg = [algorithmic_bytes(n, b, t, EMB_DIM, u) for (n, b, t, u) in shapes]
+    calls_per_step = max(1, len(shapes))
+    roof = {}
+    kernels = {}
+    for name, key in (("tbe_backward", "bwd"), ("tbe_forward", "fwd")):
+        if name in kern and alg:
+            cnt, mean_ms = kern[name]
+            per_step_bytes = sum(a[key] for a in alg)
+            per_step_ms = mean_ms * calls_per_step
+            kernels[name] = {"launch_groups_per_step": calls_per_step, "mean_ms_per_call": mean_ms,
+                             "algorithmic_bytes_per_step": per_step_bytes,
+                             "achieved_gbs": per_step_bytes / per_step_ms / 1e6}
+    for name in ("tbe_sort", "interaction_forward", "interaction_backward"):
+        if name in kern:
+            kernels[name] = {"mean_ms_per_call": kern[name][1]}
+    if "tbe_backward" in kernels:
+        k = kernels["tbe_backward"]
+        roof = {"kernel": "tbe_backward_tile_kernel (+combine) — fused segment-reduce + rowwise Adagrad",
+                "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                "frac": k["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_step"] // calls_per_step}
+    line = {
+        "metric": "dlrm_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {
+            "workload": "DLRM Criteo-1TB (MLPerf) shape: 26 tables capped at %d rows, dim 128, fp32 tables, fused "
+                        "rowwise Adagrad, dense 512-256-128 / over 1024-1024-512-256-1 (TF32 cuBLAS), local batch %d "
+                        "per GPU, RandomRecDataset-shaped ids (1 id per feature)" % (args.row_cap, args.batch),
+            "global_batch": global_batch,
+            "parallelism": "table_wise" if world == 1 else f"table_wise+row_wise(>=3M rows) x{world}, DDP dense",
+            "l2": "4 distinct batches cycled; per-step working set (1.7 GB pooled output + random rows of 104 GB "
+                  "tables) exceeds the 126 MB L2",
+        },
+        "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": batch_bytes(host_batches[0]) * 1, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roof, "kernels": kernels,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            r = time_cpu_arm(args, 4, 2)
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as e:  # the baseline is a reported number, never a reason to lose the bench line
+            line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"failed: {e}"}
+    print(json.dumps(line))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -19,6 +19,43 @@ _DT = {torch.int32: cabi.I32, torch.int64: cabi.I64, torch.float32: cabi.F32,
 _WS: Dict[Tuple[int, int], torch.Tensor] = {}
 
 
+class KernelProfile:
+    """Launch accounting and optional CUDA-event timing of the hot kernels (used by bench.py:
+    events are recorded on the launching stream around the C-ABI call, so the elapsed time is
+    the kernel's own duration)."""
+    launches = 0
+    enabled = False
+    events: Dict[str, List[Tuple["torch.cuda.Event", "torch.cuda.Event"]]] = {}
+
+    @classmethod
+    def reset(cls, enabled: bool = False) -> None:
+        cls.launches, cls.enabled, cls.events = 0, enabled, {}
+
+    @classmethod
+    def summary_ms(cls) -> Dict[str, Tuple[int, float]]:
+        """name -> (count, mean milliseconds); call after a device synchronize."""
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v) / max(1, len(v))) for k, v in cls.events.items()}
+
+
+class _timed:
+    def __init__(self, name: str, dev: torch.device, launches: int) -> None:
+        self.name, self.dev, self.n = name, dev, launches
+
+    def __enter__(self):
+        KernelProfile.launches += self.n
+        if KernelProfile.enabled:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record(torch.cuda.current_stream(self.dev))
+        return self
+
+    def __exit__(self, *exc):
+        if KernelProfile.enabled:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record(torch.cuda.current_stream(self.dev))
+            KernelProfile.events.setdefault(self.name, []).append((self.e0, e1))
+        return False
+
+
 def _need_cuda(*ts: Optional[torch.Tensor]) -> torch.device:
     dev = None
     for t in ts:
@@ -76,6 +113,7 @@ def cumsum(t_in: torch.Tensor, mode: int) -> torch.Tensor:
     shape = (n + 1,) if mode == cabi.CUMSUM_COMPLETE else x.shape
     out = torch.empty(shape, dtype=x.dtype, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_cumsum(_p(x), _p(out), n, dt, mode, _p(_ws(dev)), _stream(dev)), "b200_cumsum")
     return out
 
@@ -111,6 +149,7 @@ def permute_sparse_data(
     out_off = torch.empty(Tp * B + 1, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
         st = _stream(dev)
+        KernelProfile.launches += 1
         check(lib.b200_permute_lengths(_p(permute), _p(lengths_c), ldt, T, Tp, B, _p(out_lengths),
                                        _p(in_off), _p(out_off), _p(_ws(dev)), st),
               "b200_permute_lengths")
@@ -123,6 +162,7 @@ def permute_sparse_data(
         out_weights = None
         if weights_c is not None:
             out_weights = torch.empty(total, dtype=weights_c.dtype, device=dev)
+        KernelProfile.launches += 1
         check(lib.b200_permute_data(_p(permute), Tp, B, _p(in_off), _p(out_off), _p(values_c),
                                     _p(out_values), values_c.element_size(), _p(weights_c),
                                     _p(out_weights),
@@ -145,6 +185,7 @@ def expand_into_jagged_permute(permute: torch.Tensor, input_offsets: torch.Tenso
     dt = _idx_dt(input_offsets, "offsets")
     out = torch.empty(int(output_size), dtype=input_offsets.dtype, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_expand_into_jagged_permute(_p(permute.contiguous()), _p(input_offsets.contiguous()),
                                                   _p(output_offsets.contiguous()), dt, n, _p(out),
                                                   int(output_size), _stream(dev)),
@@ -157,6 +198,7 @@ def offsets_range(offsets: torch.Tensor, range_size: int) -> torch.Tensor:
     dt = _idx_dt(offsets, "offsets")
     out = torch.empty(int(range_size), dtype=offsets.dtype, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_offsets_range(_p(offsets.contiguous()), dt, offsets.numel(), _p(out),
                                      int(range_size), _stream(dev)), "b200_offsets_range")
     return out
@@ -192,6 +234,7 @@ def block_bucketize_sparse_features(
     off = torch.empty(TB + 1, dtype=torch.int64, device=dev)
     noff = torch.empty(TB * W + 1, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_block_bucketize(_p(lengths), odt, _p(indices), idt, _p(block_sizes), T, B, W, N,
                                        _p(weights.contiguous() if weights is not None else None),
                                        _p(new_lengths), _p(new_indices), _p(new_weights), _p(new_pos),
@@ -213,6 +256,7 @@ def bounds_check_indices(rows_per_table: torch.Tensor, indices: torch.Tensor, of
         return
     B = (offsets.numel() - 1) // T
     with torch.cuda.device(dev):
+        KernelProfile.launches += 2
         check(lib.b200_bounds_check(_p(rows_per_table), _p(indices), _p(offsets), dt, T, B,
                                     indices.numel(), int(mode), _p(warning), _p(_ws(dev)), _stream(dev)),
               "b200_bounds_check")
@@ -238,7 +282,7 @@ def tbe_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets:
             per_sample_weights = per_sample_weights.float()
         per_sample_weights = per_sample_weights.contiguous()
     out = torch.empty((B, total_D), dtype=output_dtype, device=dev)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _timed("tbe_forward", dev, 1):
         check(lib.b200_tbe_forward(_p(weights), _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
                                    T, B, total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
                                    _p(offsets.contiguous()), idt, _p(per_sample_weights),
@@ -270,7 +314,7 @@ def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cum
     bag_of_pos = torch.empty(N, dtype=torch.int32, device=dev) if weighted else None
     ws_bytes = lib.b200_tbe_sort_workspace_bytes(N, key_bits)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _timed("tbe_sort", dev, 7):  # linearize + CUB histogram/scan/4 passes
         check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
                                         key_bits, int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
                                         _p(ws), ws_bytes, _stream(dev)), "b200_tbe_sort_indices")
@@ -295,7 +339,7 @@ def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.T
     scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):  # tile kernel + cross-CTA combine
         check(lib.b200_tbe_backward(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
                                     _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),
                                     _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
@@ -315,6 +359,7 @@ def tbe_grad_indice_weights(grad_output: torch.Tensor, weights: torch.Tensor,
     B = (offsets.numel() - 1) // T
     out = torch.empty(indices.numel(), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_tbe_grad_indice_weights(_p(grad_output), grad_output.stride(0), _p(weights),
                                                _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
                                                T, B, _p(indices), _p(offsets),
@@ -331,6 +376,7 @@ def quantize_rowwise_8bit_sbhalf(w: torch.Tensor) -> torch.Tensor:
     w = w.float().contiguous()
     out = torch.empty((w.shape[0], w.shape[1] + 4), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_quantize_rowwise_8bit_sbhalf(_p(w), w.shape[0], w.shape[1], _p(out), _stream(dev)),
               "b200_quantize_rowwise_8bit_sbhalf")
     return out
@@ -349,6 +395,7 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_tbe_int8_forward(_p(weights), _p(weights_offsets), _p(D_offsets), T, B, total_D,
                                         max_D, int(row_alignment), _p(indices.contiguous()),
                                         _p(offsets.contiguous()), _idx_dt(indices, "indices"),
@@ -365,7 +412,7 @@ def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor) -> torch.Tens
     dense = dense.float().contiguous()
     sparse = sparse.float().contiguous()
     out = torch.empty((B, D + (F + 1) * F // 2), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _timed("interaction_forward", dev, 1):
         check(lib.b200_interaction_forward(_p(dense), _p(sparse), B, F, D, _p(out), _stream(dev)),
               "b200_interaction_forward")
     return out
@@ -379,7 +426,7 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     grad_out = grad_out.float().contiguous()
     gd = torch.empty_like(dense)
     gs = torch.empty_like(sparse)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
         check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), B, F, D, _p(gd), _p(gs),
                                             _stream(dev)), "b200_interaction_backward")
     return gd, gs
@@ -393,6 +440,7 @@ def pooled_a2a_recat(src: torch.Tensor, dim_cumsum: torch.Tensor, B_local: int, 
     src = src.contiguous()
     dst = torch.empty_like(src)
     with torch.cuda.device(dev):
+        KernelProfile.launches += 1
         check(lib.b200_pooled_a2a_recat(_p(src), _p(dst), _p(dim_cumsum), W, int(B_local), int(forward),
                                         float(scale), _stream(dev)), "b200_pooled_a2a_recat")
     return dst

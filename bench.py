@@ -13,6 +13,7 @@ row-wise at N > 1.  Prints ONE JSON line (rank 0).
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
 import subprocess
@@ -39,7 +40,7 @@ LR, EPS = 0.01, 1e-8
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=65536, help="local batch per GPU")
@@ -63,7 +64,7 @@ class ClockSampler:
     def start(self) -> None:
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i",
                  str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -276,7 +277,8 @@ def run_ours(args) -> None:
     dev = torch.device("cuda", local_rank)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29571")
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev,
+                            timeout=datetime.timedelta(seconds=180))
     pg = dist.group.WORLD
     torch.backends.cuda.matmul.allow_tf32 = True  # reference-era PyTorch default for the MLP GEMMs
     torch.backends.cudnn.allow_tf32 = True
@@ -311,7 +313,7 @@ def run_ours(args) -> None:
     for i in range(max(args.warmup, 3)):
         train_step(dev_batches[i % len(dev_batches)])
     torch.cuda.synchronize()
-    shapes = lookup_shapes(dmp, dev_batches[0]) if rank == 0 else []
+    shapes = lookup_shapes(dmp, dev_batches[0])  # runs the input collectives: every rank must call it
 
     # ---- value: inputs resident in HBM
     sampler = ClockSampler(local_rank)
@@ -381,7 +383,7 @@ def run_ours(args) -> None:
                   "tables) exceeds the 126 MB L2",
         },
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": batch_bytes(host_batches[0]) * 1, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": batch_bytes(host_batches[0]) * world, "d2h_bytes_per_step": 4 * world},
         "gpu_launches": launches, "clocks": clocks, "roofline": roof, "kernels": kernels,
     }
     if world == 1 and not args.no_cpu_baseline:

@@ -1,0 +1,105 @@
+"""Multi-rank worker (torchrun): sharded-vs-unsharded one-step parity on real GPUs, the pattern of
+torchrec/distributed/test_utils/test_model_parallel_base.py:144-290.  Every rank builds the same
+unsharded DLRM (nn.EmbeddingBag tables, plain SGD) and a DistributedModelParallel DLRM with a mix of
+table-wise and row-wise tables and the fused EXACT_SGD; after ONE step on per-rank batches the
+sharded predictions must equal the unsharded model's predictions on the same samples, and every
+local weight shard must equal the corresponding slice of the unsharded weights."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "torchrec-oldfork_b200"))
+
+
+def main() -> None:
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=dev)
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig, KeyedJaggedTensor
+    from torchrec.datasets.random import RandomRecDataset
+    from torchrec.distributed import DistributedModelParallel, ShardingEnv
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.planner import EmbeddingShardingPlanner, ParameterConstraints, Topology
+    from torchrec.distributed.sharding.rw_sharding import row_wise_shard_sizes
+    from torchrec.models.dlrm import DLRM
+    torch.backends.cuda.matmul.allow_tf32 = False
+    rows = [50, 7, 1001, 3, 5, 300]          # 5 rows over W ranks exercises short / empty row shards
+    sharding = ["table_wise", "row_wise", "row_wise", "table_wise", "row_wise", "table_wise"]
+    D, B, lr = 16, 32, 0.1
+    keys = [f"f{i}" for i in range(len(rows))]
+
+    def tables():
+        return [EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r, feature_names=[keys[i]])
+                for i, r in enumerate(rows)]
+
+    torch.manual_seed(7)  # identical on every rank
+    glob = DLRM(EmbeddingBagCollection(tables(), device=dev), 13, [32, D], [32, 16, 1], dense_device=dev)
+    torch.manual_seed(7)
+    local = DLRM(EmbeddingBagCollection(tables(), device=torch.device("meta")), 13, [32, D], [32, 16, 1],
+                 dense_device=dev)
+    sharders = [EmbeddingBagCollectionSharder(fused_params={"learning_rate": lr, "optimizer": EmbOptimType.EXACT_SGD})]
+    plan = EmbeddingShardingPlanner(Topology(world), {f"t{i}": ParameterConstraints(sharding_types=[s])
+                                                      for i, s in enumerate(sharding)}).plan(local, sharders)
+    dmp = DistributedModelParallel(local, env=ShardingEnv.from_process_group(dist.group.WORLD), device=dev,
+                                   plan=plan, sharders=sharders)
+    ebc_plan = plan.plan["sparse_arch.embedding_bag_collection"]
+
+    def shard_of(name: str, full: torch.Tensor):
+        ps = ebc_plan[name]
+        if ps.sharding_type == "table_wise":
+            return full if ps.ranks[0] == rank else None
+        sizes = row_wise_shard_sizes(full.shape[0], world)
+        o = sum(sizes[:rank])
+        return full[o:o + sizes[rank]]
+
+    gsd = glob.state_dict()
+    for k, v in dmp.state_dict().items():
+        if "embedding_bags" in k:
+            v.copy_(shard_of(k.split(".")[-2], gsd[k]))
+        else:
+            v.copy_(gsd[k])
+    batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
+                                       manual_seed=100 + rank))).to(dev)
+    # global batch = concatenation of the per-rank batches along the batch dim
+    dense_all = [torch.empty_like(batch.dense_features) for _ in range(world)]
+    dist.all_gather(dense_all, batch.dense_features)
+    vals_all = [torch.empty_like(batch.sparse_features.values()) for _ in range(world)]
+    dist.all_gather(vals_all, batch.sparse_features.values())
+    F = len(keys)
+    per_rank = [v.view(F, B * 2) for v in vals_all]
+    gvalues = torch.cat(per_rank, dim=1).reshape(-1)
+    gkjt = KeyedJaggedTensor(keys=keys, values=gvalues,
+                             lengths=torch.full((F * B * world,), 2, dtype=torch.int32, device=dev), stride=B * world)
+    gdense = torch.cat(dense_all, dim=0)
+
+    opt_g = torch.optim.SGD(glob.parameters(), lr=lr)
+    opt_l = torch.optim.SGD(list(dmp.parameters()), lr=lr)
+    opt_g.zero_grad()
+    # DDP averages dense grads over ranks and the pooled collectives divide by W (GRADIENT_DIVISION):
+    # the equivalent unsharded objective is the mean over ranks of the per-rank sums.
+    (glob(gdense, gkjt).sum() / world).backward()
+    opt_g.step()
+    opt_l.zero_grad()
+    dmp(batch.dense_features, batch.sparse_features).sum().backward()
+    opt_l.step()
+    with torch.no_grad():
+        pred_g = glob(gdense, gkjt)[rank * B:(rank + 1) * B]
+        pred_l = dmp(batch.dense_features, batch.sparse_features)
+    torch.testing.assert_close(pred_l, pred_g, rtol=1e-4, atol=1e-4)
+    gsd = glob.state_dict()
+    for k, v in dmp.state_dict().items():
+        exp = shard_of(k.split(".")[-2], gsd[k]) if "embedding_bags" in k else gsd[k]
+        torch.testing.assert_close(v, exp, rtol=1e-4, atol=1e-5, msg=f"rank {rank}: {k}")
+    dist.barrier()
+    if rank == 0:
+        print(f"DIST PARITY OK world={world}")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

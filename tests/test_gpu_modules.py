@@ -169,3 +169,17 @@ def test_quantized_ebc():
     # state_dict layout: [rows, 16-byte-aligned 4 + D] uint8 per table
     sd = q.state_dict()
     assert sd["embedding_bags.t0.weight"].shape == (100, 144)
+
+
+@pytest.mark.parametrize("world", [2])
+def test_multi_gpu_sharded_vs_unsharded(world):
+    """TW + RW over `world` GPUs (torchrun, NCCL); skipped on a single-GPU box."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29611",
+                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "DIST PARITY OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

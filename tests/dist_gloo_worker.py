@@ -1,0 +1,141 @@
+"""World-size-2 gloo worker (CPU): the N>1 host logic of the sharded data movement —
+KJTAllToAll, bucketize + row-wise redistribution, pooled all-to-all and reduce-scatter with their
+backward collectives — checked against what a single global view predicts.  Patterned on
+torchrec/distributed/tests/test_dist_data.py (KJTAllToAllTest / PooledEmbeddingsAllToAllTest).
+The jagged ops run on the test-only CPU kernels of tests/cpu_ops.py."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path[:0] = [os.path.join(ROOT, "torchrec-oldfork_b200"), ROOT, HERE]
+
+
+def make_kjt(rank: int, keys, B: int, hash_size: int, weighted: bool = False):
+    """Deterministic per-rank input every rank can regenerate."""
+    from torchrec import KeyedJaggedTensor
+    rng = np.random.default_rng(1000 + rank)
+    lengths = rng.integers(0, 4, size=len(keys) * B).astype(np.int32)
+    values = rng.integers(0, hash_size, size=int(lengths.sum())).astype(np.int64)
+    w = torch.from_numpy(rng.random(int(lengths.sum())).astype(np.float32)) if weighted else None
+    return KeyedJaggedTensor(keys=list(keys), values=torch.from_numpy(values), weights=w,
+                             lengths=torch.from_numpy(lengths), stride=B)
+
+
+def check_kjt_all2all(rank: int, world: int) -> None:
+    from torchrec.distributed.dist_data import KJTAllToAll
+    keys, splits, B = ["f0", "f1", "f2"], [2, 1], 3
+    for weighted in (False, True):
+        mine = make_kjt(rank, keys, B, 100, weighted)
+        got = KJTAllToAll(dist.group.WORLD, splits)(mine).wait().wait()
+        lo = sum(splits[:rank])
+        my_keys = keys[lo:lo + splits[rank]]
+        assert got.keys() == my_keys and got.stride() == B * world
+        inputs = [make_kjt(r, keys, B, 100, weighted) for r in range(world)]
+        for k in my_keys:
+            exp_l = torch.cat([i[k].lengths() for i in inputs])
+            exp_v = torch.cat([i[k].values() for i in inputs])
+            assert torch.equal(got[k].lengths(), exp_l), (k, got[k].lengths(), exp_l)
+            assert torch.equal(got[k].values(), exp_v)
+            if weighted:
+                assert torch.equal(got[k].weights(), torch.cat([i[k].weights() for i in inputs]))
+
+
+def check_row_wise_input_dist(rank: int, world: int) -> None:
+    from torchrec.distributed.dist_data import KJTAllToAll
+    from torchrec.distributed.embedding_sharding import bucketize_kjt_before_all2all
+    keys, B, rows = ["a", "b"], 4, [10, 7]
+    block = torch.tensor([(r + world - 1) // world for r in rows])
+    mine = make_kjt(rank, keys, B, 7)
+    bucketized, _ = bucketize_kjt_before_all2all(mine, world, block)
+    got = KJTAllToAll(dist.group.WORLD, [len(keys)] * world)(bucketized).wait().wait()
+    assert got.keys() == keys and got.stride() == B * world
+    inputs = [make_kjt(r, keys, B, 7) for r in range(world)]
+    for f, k in enumerate(keys):
+        bs = int(block[f])
+        exp_v, exp_l = [], []
+        for src in inputs:
+            jt = src[k]
+            off = jt.offsets().tolist()
+            vals = jt.values().tolist()
+            for b in range(B):
+                sel = [v - rank * bs for v in vals[off[b]:off[b + 1]] if v // bs == rank]
+                exp_v += sel
+                exp_l.append(len(sel))
+        assert got[k].lengths().tolist() == exp_l, (k, got[k].lengths().tolist(), exp_l)
+        assert got[k].values().tolist() == exp_v
+
+
+def check_pooled_all2all(rank: int, world: int) -> None:
+    from torchrec.distributed import comm_ops
+    from torchrec.distributed.dist_data import PooledEmbeddingsAllToAll
+    dims, B_local = [8, 4], 3
+    B_global = B_local * world
+
+    def inp(r):
+        g = torch.Generator().manual_seed(50 + r)
+        return torch.randn(B_global, dims[r], generator=g)
+
+    x = inp(rank).requires_grad_(True)
+    out = PooledEmbeddingsAllToAll(dist.group.WORLD, dims)(x).wait()
+    exp = torch.cat([inp(r)[rank * B_local:(rank + 1) * B_local] for r in range(world)], dim=1)
+    torch.testing.assert_close(out, exp, rtol=0, atol=0)
+
+    def wgt(r):  # the upstream gradient rank r applies to its output
+        g = torch.Generator().manual_seed(70 + r)
+        return torch.randn(B_local, sum(dims), generator=g)
+
+    (out * wgt(rank)).sum().backward()
+    lo = sum(dims[:rank])
+    exp_g = torch.cat([wgt(r)[:, lo:lo + dims[rank]] for r in range(world)], dim=0)
+    if comm_ops.GRADIENT_DIVISION:
+        exp_g = exp_g / world
+    torch.testing.assert_close(x.grad, exp_g, rtol=1e-6, atol=1e-7)
+
+
+def check_reduce_scatter(rank: int, world: int) -> None:
+    from torchrec.distributed import comm_ops
+    from torchrec.distributed.dist_data import PooledEmbeddingsReduceScatter
+    B_local, D = 2, 8
+
+    def inp(r):
+        g = torch.Generator().manual_seed(90 + r)
+        return torch.randn(B_local * world, D, generator=g)
+
+    x = inp(rank).requires_grad_(True)
+    out = PooledEmbeddingsReduceScatter(dist.group.WORLD)(x).wait()
+    exp = sum(inp(r)[rank * B_local:(rank + 1) * B_local] for r in range(world))
+    torch.testing.assert_close(out, exp, rtol=1e-6, atol=1e-6)
+
+    def wgt(r):
+        g = torch.Generator().manual_seed(110 + r)
+        return torch.randn(B_local, D, generator=g)
+
+    (out * wgt(rank)).sum().backward()
+    exp_g = torch.cat([wgt(r) for r in range(world)], dim=0)
+    if comm_ops.GRADIENT_DIVISION:
+        exp_g = exp_g / world
+    torch.testing.assert_close(x.grad, exp_g, rtol=1e-6, atol=1e-7)
+
+
+def main() -> None:
+    import cpu_ops
+    cpu_ops.register()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    check_kjt_all2all(rank, world)
+    check_row_wise_input_dist(rank, world)
+    check_pooled_all2all(rank, world)
+    check_reduce_scatter(rank, world)
+    dist.barrier()
+    if rank == 0:
+        print(f"GLOO DIST OK world={world}")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -160,3 +160,58 @@ def test_bounds_check(ops, dt, mode, L):
     ops.bounds_check_indices(dev(rows), gi, go, 2, warn)
     np.testing.assert_array_equal(go.cpu().numpy(), eo)
     np.testing.assert_array_equal(gi.cpu().numpy(), ei)
+
+
+# ---------------------------------------------------------------------------------------------
+# CUDA path vs fixtures produced by the reference's own CPU kernels (tests/golden/make_golden.py)
+# ---------------------------------------------------------------------------------------------
+class _CudaBackend:
+    @staticmethod
+    def _d(x):
+        return None if x is None else torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+    @staticmethod
+    def _h(x):
+        return None if x is None else x.cpu().numpy()
+
+    @classmethod
+    def cumsum(cls, x, mode):
+        from b200_sparse import cabi, ops
+        m = {"complete": cabi.CUMSUM_COMPLETE, "inclusive": cabi.CUMSUM_INCLUSIVE, "exclusive": cabi.CUMSUM_EXCLUSIVE}
+        return cls._h(ops.cumsum(cls._d(x), m[mode]))
+
+    @classmethod
+    def permute(cls, perm, lengths, values, weights, two_d):
+        from b200_sparse import ops
+        r = ops.permute_sparse_data(cls._d(perm), cls._d(lengths), cls._d(values), cls._d(weights), None, two_d)
+        return tuple(cls._h(t) for t in r)
+
+    @classmethod
+    def expand(cls, perm, in_off, out_off, n):
+        from b200_sparse import ops
+        return cls._h(ops.expand_into_jagged_permute(cls._d(perm), cls._d(in_off), cls._d(out_off), n))
+
+    @classmethod
+    def offsets_range(cls, off, n):
+        from b200_sparse import ops
+        return cls._h(ops.offsets_range(cls._d(off), n))
+
+    @classmethod
+    def bucketize(cls, lengths, indices, pos, seq, block, W, weights):
+        from b200_sparse import ops
+        r = ops.block_bucketize_sparse_features(cls._d(lengths), cls._d(indices), pos, seq, cls._d(block), W,
+                                                cls._d(weights))
+        return tuple(cls._h(t) for t in r)
+
+    @classmethod
+    def bounds_check(cls, rows, indices, offsets, mode):
+        from b200_sparse import ops
+        i, o = cls._d(indices.copy()), cls._d(offsets.copy())
+        warn = torch.zeros(1, dtype=torch.int64, device="cuda")
+        ops.bounds_check_indices(cls._d(rows), i, o, mode, warn)
+        return cls._h(i), cls._h(o), int(warn.item())
+
+
+def test_cuda_matches_reference_cpu_kernel_fixtures():
+    import golden_cases
+    assert golden_cases.run_all(_CudaBackend) == 38

@@ -191,7 +191,8 @@ def test_interaction_golden(ops):
     assert abs(float(out[0, 0]) - 0.4963) < 1e-4  # first element of the reference's expected tensor
 
 
-@pytest.mark.parametrize("B,F,D", [(3, 4, 4), (65, 26, 128), (130, 8, 64), (7, 1, 16)])
+@pytest.mark.parametrize("B,F,D", [(3, 4, 4), (65, 26, 128), (130, 8, 64), (7, 1, 16), (3001, 26, 128), (1250, 31, 64), (200, 15, 192),
+                                   (500, 7, 256), (40, 32, 64), (9, 0, 64)])
 def test_interaction_fwd_bwd(ops, B, F, D):
     rng = np.random.default_rng(B)
     dense = rng.standard_normal((B, D)).astype(np.float32)

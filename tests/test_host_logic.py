@@ -1,0 +1,167 @@
+"""CPU tests of the host layer that mirrors the reference API: KeyedJaggedTensor bookkeeping
+(torchrec/sparse/tests/test_jagged_tensor.py vectors), KJTAllToAll index helpers
+(torchrec/distributed/tests/test_dist_data.py), row-wise shard geometry, the planner, the TBE module's
+bookkeeping, and the world-size-2 gloo run of the sharded data movement.
+Jagged ops run on tests/cpu_ops.py (oracle-backed, test-only); the product registers CUDA only."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+import cpu_ops
+
+cpu_ops.register()
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def test_get_recat_reference_vectors():
+    from torchrec.distributed.dist_data import _get_recat
+    assert _get_recat(2, 4, 1).tolist() == [0, 2, 4, 6, 1, 3, 5, 7]
+    assert _get_recat(2, 4, 2).tolist() == [0, 4, 2, 6, 1, 5, 3, 7]
+    assert _get_recat(0, 4, 1).numel() == 0
+    from oracle.jagged_ref import get_recat
+    for ls, ns, st in [(1, 2, 1), (3, 8, 4), (5, 4, 2)]:
+        assert _get_recat(ls, ns, st).tolist() == list(get_recat(ls, ns, st))
+
+
+def test_split_lengths():
+    from torchrec.distributed.dist_data import _split_lengths
+    assert _split_lengths([2, 1, 0], ["a", "b", "c"], [0, 3, 5, 9]) == [5, 4, 0]
+
+
+def test_row_wise_shard_sizes():
+    from torchrec.distributed.sharding.rw_sharding import row_wise_shard_sizes
+    assert row_wise_shard_sizes(5, 4) == [2, 2, 1, 0]
+    assert row_wise_shard_sizes(8, 4) == [2, 2, 2, 2]
+    assert row_wise_shard_sizes(1, 2) == [1, 0]
+    for rows in (1, 7, 100, 40_000_000):
+        for w in (1, 2, 8):
+            s = row_wise_shard_sizes(rows, w)
+            assert sum(s) == rows and len(s) == w and all(a >= b for a, b in zip(s, s[1:]))
+
+
+def _kjt():
+    from torchrec import KeyedJaggedTensor
+    # the tensor of torchrec/sparse/tests/test_jagged_tensor.py:394-415
+    return KeyedJaggedTensor(keys=["index_0", "index_1"],
+                             values=torch.tensor([1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0]),
+                             weights=torch.tensor([1.0, 0.5, 1.5, 1.0, 0.5, 1.0, 1.0, 1.5]),
+                             lengths=torch.tensor([2, 0, 1, 1, 1, 3], dtype=torch.int32))
+
+
+def test_kjt_metadata_and_views():
+    k = _kjt()
+    assert k.stride() == 3 and k.keys() == ["index_0", "index_1"]
+    assert k.offsets().tolist() == [0, 2, 2, 3, 4, 5, 8]
+    assert k.length_per_key() == [3, 5] and k.offset_per_key() == [0, 3, 8]
+    j0, j1 = k["index_0"], k["index_1"]
+    assert j0.values().tolist() == [1.0, 2.0, 3.0] and j0.lengths().tolist() == [2, 0, 1]
+    assert j1.values().tolist() == [4.0, 5.0, 6.0, 7.0, 8.0] and j1.offsets().tolist() == [0, 1, 2, 5]
+    assert j1.weights().tolist() == [1.0, 0.5, 1.0, 1.0, 1.5]
+    d = k.to_dict()
+    assert list(d) == ["index_0", "index_1"] and d["index_1"].values().tolist() == j1.values().tolist()
+
+
+def test_kjt_split_and_permute():
+    k = _kjt()
+    a, b = k.split([1, 1])
+    assert a.keys() == ["index_0"] and b.keys() == ["index_1"]
+    assert a.values().tolist() == [1.0, 2.0, 3.0] and b.lengths().tolist() == [1, 1, 3]
+    p = k.permute([1, 0])
+    assert p.keys() == ["index_1", "index_0"]
+    assert p.values().tolist() == [4.0, 5.0, 6.0, 7.0, 8.0, 1.0, 2.0, 3.0]
+    assert p.lengths().tolist() == [1, 1, 3, 2, 0, 1]
+    assert p.weights().tolist() == [1.0, 0.5, 1.0, 1.0, 1.5, 1.0, 0.5, 1.5]
+    # duplicates are allowed in permute (test_jagged_tensor.py:560-600)
+    q = k.permute([1, 0, 1])
+    assert q.keys() == ["index_1", "index_0", "index_1"] and q.values().numel() == 13
+
+
+def test_kjt_empty_and_from_offsets():
+    from torchrec import KeyedJaggedTensor
+    e = KeyedJaggedTensor(keys=[], values=torch.tensor([], dtype=torch.int64),
+                          lengths=torch.tensor([], dtype=torch.int32), stride=0)
+    assert e.keys() == [] and e.values().numel() == 0
+    k = KeyedJaggedTensor.from_offsets_sync(keys=["a", "b"], values=torch.arange(5),
+                                            offsets=torch.tensor([0, 2, 2, 3, 5]))
+    assert k.lengths().tolist() == [2, 0, 1, 2] and k.stride() == 2
+    z = KeyedJaggedTensor.from_lengths_sync(keys=["a"], values=torch.tensor([], dtype=torch.int64),
+                                            lengths=torch.zeros(4, dtype=torch.int32))
+    assert z["a"].values().numel() == 0 and z.offsets().tolist() == [0, 0, 0, 0, 0]
+
+
+def test_keyed_tensor_regroup():
+    from torchrec import KeyedTensor
+    kt = KeyedTensor(keys=["a", "b", "c"], length_per_key=[2, 3, 1], values=torch.arange(12.0).view(2, 6))
+    d = kt.to_dict()
+    assert d["b"].tolist() == [[2.0, 3.0, 4.0], [8.0, 9.0, 10.0]] and kt.offset_per_key() == [0, 2, 5, 6]
+    assert kt["c"].tolist() == [[5.0], [11.0]]
+
+
+def test_unsharded_ebc_matches_embedding_bag():
+    """EmbeddingBagCollection on CPU tensors (torchrec/modules/tests/test_embedding_modules.py:20-80)."""
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig, KeyedJaggedTensor
+    torch.manual_seed(0)
+    ebc = EmbeddingBagCollection([
+        EmbeddingBagConfig(name="t1", embedding_dim=4, num_embeddings=10, feature_names=["f1"]),
+        EmbeddingBagConfig(name="t2", embedding_dim=8, num_embeddings=10, feature_names=["f2", "f3"])])
+    kjt = KeyedJaggedTensor.from_offsets_sync(keys=["f1", "f2", "f3"], values=torch.tensor([1, 2, 4, 5, 4, 3, 2, 9, 0]),
+                                              offsets=torch.tensor([0, 2, 4, 6, 8, 9, 9]))
+    out = ebc(kjt)
+    assert out.keys() == ["f1", "f2", "f3"] and out.values().shape == (2, 20)
+    w1, w2 = ebc.embedding_bags["t1"].weight, ebc.embedding_bags["t2"].weight
+    torch.testing.assert_close(out["f1"][0], w1[1] + w1[2])
+    torch.testing.assert_close(out["f2"][1], w2[2] + w2[9])
+    torch.testing.assert_close(out["f3"][1], torch.zeros(8))
+
+
+def test_planner_is_deterministic_and_honours_constraints():
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.planner import EmbeddingShardingPlanner, ParameterConstraints, Topology
+    rows = [1000, 10, 500, 20_000, 7]
+    ebc = EmbeddingBagCollection([EmbeddingBagConfig(name=f"t{i}", embedding_dim=16, num_embeddings=r,
+                                                     feature_names=[f"f{i}"]) for i, r in enumerate(rows)],
+                                 device=torch.device("meta"))
+    cons = {"t3": ParameterConstraints(sharding_types=["row_wise"])}
+    plans = [EmbeddingShardingPlanner(Topology(4), cons).plan(ebc, [EmbeddingBagCollectionSharder()])
+             for _ in range(2)]
+    p0, p1 = (next(iter(p.plan.values())) for p in plans)
+    assert set(p0) == {f"t{i}" for i in range(5)}
+    for name in p0:
+        assert p0[name].sharding_type == p1[name].sharding_type and p0[name].ranks == p1[name].ranks
+    assert p0["t3"].sharding_type == "row_wise" and sorted(p0["t3"].ranks) == [0, 1, 2, 3]
+    tw = [n for n in p0 if p0[n].sharding_type == "table_wise"]
+    assert all(len(p0[n].ranks) == 1 and 0 <= p0[n].ranks[0] < 4 for n in tw)
+    # greedy balance: the two biggest table-wise tables land on different ranks
+    assert p0["t0"].ranks != p0["t2"].ranks
+
+
+def test_tbe_module_requires_cuda():
+    """No CPU path: the fused module refuses a CPU device instead of computing on the host."""
+    from fbgemm_gpu.split_table_batched_embeddings_ops import (ComputeDevice, EmbeddingLocation,
+                                                               SplitTableBatchedEmbeddingBagsCodegen)
+    with pytest.raises((NotImplementedError, RuntimeError, AssertionError, ValueError)):
+        SplitTableBatchedEmbeddingBagsCodegen([(10, 4, EmbeddingLocation.HOST, ComputeDevice.CPU)])
+
+
+def test_row_size_helpers():
+    from fbgemm_gpu.split_embedding_configs import SparseType
+    from fbgemm_gpu.split_table_batched_embeddings_ops import rounded_row_size_in_bytes, unpadded_row_size_in_bytes
+    # split_table_batched_embeddings_ops.py:1469-1485: int8 rows carry a 4-byte fp16 scale/bias header
+    assert unpadded_row_size_in_bytes(128, SparseType.INT8) == 132
+    assert rounded_row_size_in_bytes(128, SparseType.INT8, 16) == 144
+    assert rounded_row_size_in_bytes(12, SparseType.INT8, 16) == 16
+
+
+def test_world2_gloo_sharded_data_movement():
+    """KJTAllToAll, bucketize + row-wise input dist, pooled all-to-all and reduce-scatter (fwd + bwd)
+    at world_size 2 over gloo."""
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29741",
+                        os.path.join(HERE, "dist_gloo_worker.py")], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "GLOO DIST OK world=2" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -188,3 +188,43 @@ def test_rowwise_adagrad_vs_reference_code():
                    offsets, "rowwise_adagrad", lr, eps, h, np.array([0], np.int64))
     np.testing.assert_allclose(w.reshape(rows, D), w_ref, rtol=1e-6, atol=1e-7)
     np.testing.assert_allclose(h, h_ref, rtol=1e-6, atol=1e-7)
+
+
+# ---------------------------------------------------------------------------------------------
+# Fixtures produced by the reference's own CPU kernels (tests/golden/make_golden.py)
+# ---------------------------------------------------------------------------------------------
+class _OracleBackend:
+    @staticmethod
+    def cumsum(x, mode):
+        from oracle import jagged_ref as J
+        return getattr(J, mode + "_cumsum")(x)
+
+    @staticmethod
+    def permute(perm, lengths, values, weights, two_d):
+        from oracle import jagged_ref as J
+        return (J.permute_2D_sparse_data if two_d else J.permute_1D_sparse_data)(perm, lengths, values, weights)
+
+    @staticmethod
+    def expand(perm, in_off, out_off, n):
+        from oracle import jagged_ref as J
+        return J.expand_into_jagged_permute(perm, in_off, out_off, n)
+
+    @staticmethod
+    def offsets_range(off, n):
+        from oracle import jagged_ref as J
+        return J.offsets_range(off, n)
+
+    @staticmethod
+    def bucketize(lengths, indices, pos, seq, block, W, weights):
+        from oracle import jagged_ref as J
+        return J.block_bucketize_sparse_features(lengths, indices, pos, seq, block, W, weights)
+
+    @staticmethod
+    def bounds_check(rows, indices, offsets, mode):
+        from oracle import jagged_ref as J
+        return J.bounds_check_indices(rows, indices, offsets, mode)
+
+
+def test_oracle_matches_reference_cpu_kernel_fixtures():
+    import golden_cases
+    assert golden_cases.run_all(_OracleBackend) == 38

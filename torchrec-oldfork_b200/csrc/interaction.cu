@@ -181,6 +181,288 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core path (n = F+1 <= 32, D % 64 == 0): one warp per sample, mma.sync m16n8k8 with the
+// 3xTF32 split (x = hi + lo, products lo*hi + hi*lo + hi*hi accumulated in fp32), which keeps the
+// result within a few ulp of the fp32 FFMA chain.  X X^T is symmetric, so the A fragment of row
+// tile i IS the pair of B fragments of column tiles 2i, 2i+1: each k-step loads 8 floats per lane
+// and issues 18 MMAs (6 upper-triangular 16x8 tiles x 3 passes).
+// Samples stream through warp-private cp.async rings of 64-column half-sample stages (row stride
+// 68 floats: fragment loads are bank-conflict free), so no CTA-wide barrier sits on the path and
+// 8 warps x 2 stages (~115 KB) stay in flight per SM.  The [D + n(n-1)/2] output row is assembled
+// in shared memory and written with coalesced stores (rows are only 4-byte aligned).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMmaWarps = 8;
+constexpr int kKC = 64;  // columns per pipeline stage
+
+__device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                         uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};\n"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  const float r = x - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+
+__device__ __forceinline__ void cp_async_16(float* dst_smem, const float* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(float* dst_smem, const float* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(kMmaWarps * 32, 1)
+interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
+                               int32_t B, int32_t F, int32_t D, float* __restrict__ out) {
+  extern __shared__ __align__(16) float smem[];
+  const int n = F + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  constexpr int ld = kKC + 4;
+  const int stage_floats = n * ld;
+  const int out_dim = D + n * (n - 1) / 2;
+  const int outs_floats = (out_dim + 3) & ~3;
+  float* wbase = smem + (size_t)warp * (3 * stage_floats + outs_floats);
+  float* outs = wbase + 3 * stage_floats;
+  const int nch = D / kKC;
+  const int ntiles = (n + 7) >> 3;  // live 8-row tiles
+  const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
+  const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
+
+  auto issue = [&](int64_t q) {
+    if (q < Q) {
+      const int64_t it = q / nch;
+      const int h = (int)(q - it * nch);
+      const int64_t s = gw + it * tw;
+      float* st = wbase + (q % 3) * stage_floats;
+      const float* dsrc = dense + s * D + h * kKC;
+      const float* ssrc = sparse + s * (int64_t)F * D + h * kKC;
+      for (int c = lane; c < n * (kKC / 4); c += 32) {
+        const int r = c >> 4, cc = c & 15;
+        cp_async_16(st + r * ld + 4 * cc, (r == 0 ? dsrc : ssrc + (int64_t)(r - 1) * D) + 4 * cc);
+      }
+    }
+    cp_async_commit();  // always: keeps the group count uniform
+  };
+  issue(0);
+  issue(1);
+
+  constexpr int kTM[6] = {0, 0, 0, 0, 1, 1};
+  constexpr int kTN[6] = {0, 1, 2, 3, 2, 3};
+  float acc[6][4];
+  int rowoff[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) rowoff[j] = min(8 * j + g, n - 1) * ld + t;
+
+  for (int64_t q = 0; q < Q; ++q) {
+    cp_async_wait<1>();
+    __syncwarp();
+    issue(q + 2);
+    const int64_t it = q / nch;
+    const int h = (int)(q - it * nch);
+    const float* st = wbase + (q % 3) * stage_floats;
+    if (h == 0) {
+#pragma unroll
+      for (int x = 0; x < 6; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[x][y] = 0.f;
+    }
+    outs[h * kKC + lane] = st[lane];  // dense passthrough
+    outs[h * kKC + 32 + lane] = st[32 + lane];
+#pragma unroll 2
+    for (int k0 = 0; k0 < kKC; k0 += 8) {
+      uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        split_tf32(st[rowoff[j] + k0], bh[j][0], bl[j][0]);
+        split_tf32(st[rowoff[j] + k0 + 4], bh[j][1], bl[j][1]);
+      }
+#pragma unroll
+      for (int x = 0; x < 6; ++x) {
+        const int mi = kTM[x], nj = kTN[x];
+        if (nj < ntiles && 2 * mi < ntiles) {
+          mma_tf32(acc[x], bl[2 * mi][0], bl[2 * mi + 1][0], bl[2 * mi][1], bl[2 * mi + 1][1], bh[nj][0], bh[nj][1]);
+          mma_tf32(acc[x], bh[2 * mi][0], bh[2 * mi + 1][0], bh[2 * mi][1], bh[2 * mi + 1][1], bl[nj][0], bl[nj][1]);
+          mma_tf32(acc[x], bh[2 * mi][0], bh[2 * mi + 1][0], bh[2 * mi][1], bh[2 * mi + 1][1], bh[nj][0], bh[nj][1]);
+        }
+      }
+    }
+    if (h == nch - 1) {
+      float* o = outs + D;
+#pragma unroll
+      for (int x = 0; x < 6; ++x) {
+#pragma unroll
+        for (int y = 0; y < 4; ++y) {
+          const int i = 16 * kTM[x] + g + ((y & 2) ? 8 : 0);
+          const int j = 8 * kTN[x] + 2 * t + (y & 1);
+          if (i < j && j < n) o[tri_index(i, j, n)] = acc[x][y];
+        }
+      }
+      __syncwarp();
+      float* dst = out + (gw + it * tw) * out_dim;
+      for (int c = lane; c < out_dim; c += 32) dst[c] = outs[c];
+    }
+  }
+}
+
+
+// Backward on the same machinery: grad_X = Gs X, Gs (n x n, symmetric, zero diagonal) scattered
+// from grad_out's triangle into a warp-private 32x36 tile (A operand, split once per sample and
+// kept in registers), X streamed in 64-column stages with row stride 72 (B-fragment loads are
+// conflict free).  grad_out rows ride in the same cp.async groups (4-byte copies: rows are only
+// 4-byte aligned).  Results leave as 8-byte stores that fill whole 32-byte sectors.
+__global__ void __launch_bounds__(kMmaWarps * 32, 1)
+interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
+                                const float* __restrict__ grad_out, int32_t B, int32_t F, int32_t D,
+                                float* __restrict__ grad_dense, float* __restrict__ grad_sparse) {
+  extern __shared__ __align__(16) float smem[];
+  const int n = F + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  constexpr int ld = kKC + 8;
+  constexpr int ldG = 36;
+  const int stage_floats = n * ld;
+  const int n_tri = n * (n - 1) / 2;
+  const int out_dim = D + n_tri;
+  const int gs_floats = (out_dim + 3) & ~3;
+  const int per_warp = 2 * stage_floats + 32 * ldG + 2 * gs_floats;
+  uint16_t* ij = reinterpret_cast<uint16_t*>(smem + (size_t)kMmaWarps * per_warp);  // [n_tri] (i | j << 8)
+  float* wbase = smem + (size_t)warp * per_warp;
+  float* Gs = wbase + 2 * stage_floats;
+  float* gst = Gs + 32 * ldG;
+  const int nch = D / kKC;
+  const int ksteps = (n + 7) >> 3;
+  const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
+  const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
+
+  for (int p = threadIdx.x; p < n_tri; p += blockDim.x) {
+    int i = 0, rem = p;
+    while (rem >= n - 1 - i) {
+      rem -= n - 1 - i;
+      ++i;
+    }
+    ij[p] = (uint16_t)(i | ((i + 1 + rem) << 8));
+  }
+  for (int c = lane; c < 32 * ldG; c += 32) Gs[c] = 0.f;  // diagonal and padding stay zero
+  __syncthreads();
+
+  auto issue = [&](int64_t q) {
+    if (q < Q) {
+      const int64_t it = q / nch;
+      const int h = (int)(q - it * nch);
+      const int64_t s = gw + it * tw;
+      float* st = wbase + (q & 1) * stage_floats;
+      const float* dsrc = dense + s * D + h * kKC;
+      const float* ssrc = sparse + s * (int64_t)F * D + h * kKC;
+      for (int c = lane; c < n * (kKC / 4); c += 32) {
+        const int r = c >> 4, cc = c & 15;
+        cp_async_16(st + r * ld + 4 * cc, (r == 0 ? dsrc : ssrc + (int64_t)(r - 1) * D) + 4 * cc);
+      }
+      if (h == 0) {
+        float* gd = gst + (it & 1) * gs_floats;
+        const float* gsrc = grad_out + s * out_dim;
+        for (int c = lane; c < out_dim; c += 32) cp_async_4(gd + c, gsrc + c);
+      }
+    }
+    cp_async_commit();
+  };
+  issue(0);
+
+  uint32_t ah[2][4][4], al[2][4][4];  // [row tile][k-step][fragment]
+  int rowoff[4][2];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    rowoff[k][0] = min(8 * k + t, n - 1) * ld + g;
+    rowoff[k][1] = min(8 * k + t + 4, n - 1) * ld + g;
+  }
+
+  for (int64_t q = 0; q < Q; ++q) {
+    cp_async_wait<0>();
+    __syncwarp();
+    issue(q + 1);
+    const int64_t it = q / nch;
+    const int h = (int)(q - it * nch);
+    const int64_t s = gw + it * tw;
+    const float* st = wbase + (q & 1) * stage_floats;
+    const float* gcur = gst + (it & 1) * gs_floats;
+    if (h == 0) {
+      for (int p = lane; p < n_tri; p += 32) {
+        const int i = ij[p] & 0xff, j = ij[p] >> 8;
+        const float v = gcur[D + p];
+        Gs[i * ldG + j] = v;
+        Gs[j * ldG + i] = v;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float* a = Gs + (16 * mi + g) * ldG + 8 * k + t;
+          split_tf32(a[0], ah[mi][k][0], al[mi][k][0]);
+          split_tf32(a[8 * ldG], ah[mi][k][1], al[mi][k][1]);
+          split_tf32(a[4], ah[mi][k][2], al[mi][k][2]);
+          split_tf32(a[8 * ldG + 4], ah[mi][k][3], al[mi][k][3]);
+        }
+      __syncwarp();  // Gs is rewritten by the next sample only after every lane has its fragments
+    }
+#pragma unroll 1
+    for (int nt = 0; nt < kKC / 8; ++nt) {
+      float acc[2][4];
+#pragma unroll
+      for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[mi][y] = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (k < ksteps) {
+          uint32_t bh0, bl0, bh1, bl1;
+          split_tf32(st[rowoff[k][0] + 8 * nt], bh0, bl0);
+          split_tf32(st[rowoff[k][1] + 8 * nt], bh1, bl1);
+#pragma unroll
+          for (int mi = 0; mi < 2; ++mi) {
+            if (16 * mi < n) {
+              mma_tf32(acc[mi], al[mi][k][0], al[mi][k][1], al[mi][k][2], al[mi][k][3], bh0, bh1);
+              mma_tf32(acc[mi], ah[mi][k][0], ah[mi][k][1], ah[mi][k][2], ah[mi][k][3], bl0, bl1);
+              mma_tf32(acc[mi], ah[mi][k][0], ah[mi][k][1], ah[mi][k][2], ah[mi][k][3], bh0, bh1);
+            }
+          }
+        }
+      }
+      const int d = h * kKC + 8 * nt + 2 * t;
+#pragma unroll
+      for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int i = 16 * mi + g + 8 * half;
+          if (i < n) {
+            float2 v = make_float2(acc[mi][2 * half], acc[mi][2 * half + 1]);
+            if (i == 0) {
+              v.x += gcur[d];
+              v.y += gcur[d + 1];
+              *reinterpret_cast<float2*>(grad_dense + s * D + d) = v;
+            } else {
+              *reinterpret_cast<float2*>(grad_sparse + (s * F + (i - 1)) * (int64_t)D + d) = v;
+            }
+          }
+        }
+    }
+  }
+}
+
 }  // namespace b200
 
 extern "C" int b200_interaction_forward(const float* dense, const float* sparse, int32_t B,
@@ -189,6 +471,20 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   const int n = F + 1;
+  if (n <= 32 && D % kKC == 0) {
+    const int out_dim = D + n * (n - 1) / 2;
+    const size_t msmem = sizeof(float) * kMmaWarps * (3 * (size_t)n * (kKC + 4) + ((out_dim + 3) & ~3));
+    if (msmem <= 227 * 1024) {
+      B200_CUDA_TRY(cudaFuncSetAttribute(interaction_forward_mma_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+      int64_t mgrid = ceil_div(B, kMmaWarps);
+      if (mgrid > kNumSMs) mgrid = kNumSMs;
+      interaction_forward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+          dense, sparse, B, F, D, out);
+      B200_LAUNCH_CHECK();
+      return B200_OK;
+    }
+  }
   const size_t smem = sizeof(float) * kIxSamplesPerCta * (size_t)n * (D + 4);
   if (smem > 200 * 1024) return B200_EUNSUPPORTED;
   B200_CUDA_TRY(cudaFuncSetAttribute(interaction_forward_kernel,
@@ -208,6 +504,21 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   const int n = F + 1;
+  if (n <= 32 && D % kKC == 0) {
+    const int n_tri = n * (n - 1) / 2;
+    const size_t per_warp = 2 * (size_t)n * (kKC + 8) + 32 * 36 + 2 * (size_t)((D + n_tri + 3) & ~3);
+    const size_t msmem = sizeof(float) * kMmaWarps * per_warp + ((sizeof(uint16_t) * n_tri + 15) & ~(size_t)15);
+    if (msmem <= 227 * 1024) {
+      B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_mma_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+      int64_t mgrid = ceil_div(B, kMmaWarps);
+      if (mgrid > kNumSMs) mgrid = kNumSMs;
+      interaction_backward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+          dense, sparse, grad_out, B, F, D, grad_dense, grad_sparse);
+      B200_LAUNCH_CHECK();
+      return B200_OK;
+    }
+  }
   const size_t smem = sizeof(float) * kIxSamplesPerCta * (((size_t)n * (D + 4) + (size_t)n * (n + 1) + 3) & ~(size_t)3);
   if (smem > 200 * 1024) return B200_EUNSUPPORTED;
   B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_kernel,

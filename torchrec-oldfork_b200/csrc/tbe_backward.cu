@@ -214,6 +214,60 @@ __device__ __forceinline__ void row_add(float (&acc)[NV][EPV], const float* src,
     }
 }
 
+
+// cp.async ring geometry of the tile kernel: per sorted position one fp32 gradient row, one weight
+// row slot (16 bytes per lane and vector) and 16 bytes for the momentum word.
+template <int EPV, int NV>
+struct BwdRing {
+  static constexpr int kGradBytes = NV * EPV * 32 * 4;
+  static constexpr int kWrowBytes = NV * 32 * 16;
+  static constexpr int kStageBytes = kGradBytes + kWrowBytes + 16;
+  static constexpr int kChunks = NV * (EPV / 4);
+  static constexpr int kStages = kChunks >= 4 ? 2 : (8 / kChunks);
+};
+
+__device__ __forceinline__ void cp_async_cg16(void* dst_smem, const void* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_ca8(void* dst_smem, const void* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_ca4(void* dst_smem, const void* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_group() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// one lane's staged piece of a weight row (EPV elements of W) -> fp32
+template <typename W, int EPV>
+__device__ __forceinline__ void load_wslot(const unsigned char* p, float (&f)[EPV]) {
+  if constexpr (sizeof(W) == 4) {
+    const float4 x = *reinterpret_cast<const float4*>(p);
+    f[0] = x.x;
+    f[1] = x.y;
+    f[2] = x.z;
+    f[3] = x.w;
+  } else if constexpr (EPV == 8) {
+    const uint4 r = *reinterpret_cast<const uint4*>(p);
+    ElemCvt<W>::unpack2(r.x, f[0], f[1]);
+    ElemCvt<W>::unpack2(r.y, f[2], f[3]);
+    ElemCvt<W>::unpack2(r.z, f[4], f[5]);
+    ElemCvt<W>::unpack2(r.w, f[6], f[7]);
+  } else {
+    const uint2 r = *reinterpret_cast<const uint2*>(p);
+    ElemCvt<W>::unpack2(r.x, f[0], f[1]);
+    ElemCvt<W>::unpack2(r.y, f[2], f[3]);
+  }
+}
+
 template <typename K>
 struct BwdArgs {
   const float* grad;
@@ -242,8 +296,10 @@ struct BwdArgs {
 template <typename W, typename K, int EPV, int NV, int OPT>
 __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const BwdArgs<K> a) {
   constexpr int ROW = NV * EPV * 32;
-  // gradient rows (and weight rows) in flight per warp: 16 floats per lane of each kind
-  constexpr int kBwdU = (16 / (NV * EPV)) > 0 ? (16 / (NV * EPV)) : 1;
+  constexpr int kStages = BwdRing<EPV, NV>::kStages;
+  constexpr int kGradBytes = BwdRing<EPV, NV>::kGradBytes;
+  constexpr int kWrowBytes = BwdRing<EPV, NV>::kWrowBytes;
+  constexpr int kStageBytes = BwdRing<EPV, NV>::kStageBytes;
   extern __shared__ __align__(16) float smem[];
   float* sH = smem;                    // [kBwdWarps][ROW]
   __shared__ int s_first_head[kBwdWarps];
@@ -311,92 +367,101 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
   int open_head = -1;  // head position of the open run inside this tile, -1 = carried in
   float dummy_w[NV][EPV];
 
-  for (int base = 0; base < nvalid; base += kBwdU) {
-    float g[kBwdU][NV][EPV];
-    float wv[kBwdU][NV][EPV];
-    float mv[kBwdU];
-    int Du[kBwdU];
-    float su[kBwdU];
-    int64_t wo[kBwdU], mo[kBwdU];
-#pragma unroll
-    for (int u = 0; u < kBwdU; ++u) {
-      const int src = (base + u) & 31;
-      const bool live = base + u < nvalid;
-      const uint32_t g4 = __shfl_sync(kFull, goff4, src);
-      Du[u] = __shfl_sync(kFull, Dt, src);
-      su[u] = __shfl_sync(kFull, scale, src);
-      wo[u] = __shfl_sync(kFull, woff, src);
-      mo[u] = __shfl_sync(kFull, moff, src);
+  // ---- stream the tile's rows through a warp-private cp.async ring.  One group per sorted
+  // position: its gradient row and, when a run that started in this tile ends there, the weight
+  // row (+ momentum) the optimizer will rewrite.  Every lane copies and later consumes its own
+  // 16-byte pieces, so no warp barrier is needed and the registers hold only the accumulator:
+  // kStages-1 positions (~0.7 KB each at D=128) stay in flight per warp.
+  unsigned char* ring = reinterpret_cast<unsigned char*>(smem + kBwdWarps * ROW) +
+                        (size_t)warp * kStages * kStageBytes;
+  auto issue = [&](int p) {
+    if (p < nvalid) {
+      unsigned char* st = ring + (p % kStages) * kStageBytes;
+      const uint32_t g4 = __shfl_sync(kFull, goff4, p);
+      const int Dp = __shfl_sync(kFull, Dt, p);
       const float* grow = a.grad + ((int64_t)g4 << 2);
-      const bool fin = live && ((Cm >> src) & 1u);
-      mv[u] = 0.f;
-      if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
-        if (fin) mv[u] = a.momentum1[mo[u]];
+      const bool fin = (Cm >> p) & 1u;
+      int64_t wo = 0, mo = 0;
+      if (fin) {  // warp-uniform
+        wo = __shfl_sync(kFull, woff, p);
+        if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) mo = __shfl_sync(kFull, moff, p);
       }
 #pragma unroll
       for (int v = 0; v < NV; ++v) {
         const int d = EPV * (lane + 32 * v);
-        if (live && d < Du[u]) {
-          load_grad<EPV>(grow + d, g[u][v]);
-        } else {
+        if (d < Dp) {
 #pragma unroll
-          for (int e = 0; e < EPV; ++e) g[u][v][e] = 0.f;
-        }
-        if (fin && d < Du[u]) {
-          if constexpr (sizeof(W) == 4 || EPV == 8) {
-            // 16-byte coherent load that bypasses L1 (rows are written below by this warp)
-            uint4 r = ld_na_16(weights + wo[u] + d);
-            if constexpr (sizeof(W) == 4) {
-              wv[u][v][0] = __uint_as_float(r.x);
-              wv[u][v][1] = __uint_as_float(r.y);
-              wv[u][v][2] = __uint_as_float(r.z);
-              wv[u][v][3] = __uint_as_float(r.w);
-            } else {
-              ElemCvt<W>::unpack2(r.x, wv[u][v][0], wv[u][v][1]);
-              ElemCvt<W>::unpack2(r.y, wv[u][v][2], wv[u][v][3]);
-              ElemCvt<W>::unpack2(r.z, wv[u][v][4], wv[u][v][5]);
-              ElemCvt<W>::unpack2(r.w, wv[u][v][6], wv[u][v][7]);
-            }
-          } else {
-            load_wrow<W, EPV>(weights + wo[u] + d, wv[u][v]);
+          for (int c = 0; c < EPV / 4; ++c)
+            cp_async_cg16(st + ((v * (EPV / 4) + c) * 32 + lane) * 16, grow + d + 4 * c);
+          if (fin) {
+            if constexpr (EPV * sizeof(W) == 16)
+              cp_async_cg16(st + kGradBytes + (v * 32 + lane) * 16, weights + wo + d);
+            else
+              cp_async_ca8(st + kGradBytes + (v * 32 + lane) * 16, weights + wo + d);
           }
-        } else {
+        }
+      }
+      if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+        if (fin && lane == 0) cp_async_ca4(st + kGradBytes + kWrowBytes, a.momentum1 + mo);
+      }
+    }
+    cp_async_commit_group();  // always: keeps the group count uniform
+  };
 #pragma unroll
-          for (int e = 0; e < EPV; ++e) wv[u][v][e] = 0.f;
+  for (int p = 0; p < kStages - 1; ++p) issue(p);
+
+  for (int p = 0; p < nvalid; ++p) {
+    issue(p + kStages - 1);
+    cp_async_wait_group<kStages - 1>();
+    const unsigned char* st = ring + (p % kStages) * kStageBytes;
+    const int Dp = __shfl_sync(kFull, Dt, p);
+    if ((Hm >> p) & 1u) open_head = p;
+    const float sp = scaled ? __shfl_sync(kFull, scale, p) : 1.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      if (EPV * (lane + 32 * v) < Dp) {
+#pragma unroll
+        for (int c = 0; c < EPV / 4; ++c) {
+          const float4 x = *reinterpret_cast<const float4*>(st + ((v * (EPV / 4) + c) * 32 + lane) * 16);
+          acc[v][4 * c] = fmaf(sp, x.x, acc[v][4 * c]);
+          acc[v][4 * c + 1] = fmaf(sp, x.y, acc[v][4 * c + 1]);
+          acc[v][4 * c + 2] = fmaf(sp, x.z, acc[v][4 * c + 2]);
+          acc[v][4 * c + 3] = fmaf(sp, x.w, acc[v][4 * c + 3]);
         }
       }
     }
-#pragma unroll
-    for (int u = 0; u < kBwdU; ++u) {
-      const int src = base + u;
-      if (src < nvalid) {
-        if ((Hm >> src) & 1u) open_head = src;
-        if (scaled) {
-#pragma unroll
-          for (int v = 0; v < NV; ++v)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] = fmaf(su[u], g[u][v][e], acc[v][e]);
-        } else {
-#pragma unroll
-          for (int v = 0; v < NV; ++v)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] += g[u][v][e];
+    if ((Em >> p) & 1u) {
+      if (open_head >= 0) {
+        const int64_t wo = __shfl_sync(kFull, woff, p);
+        int64_t mo = 0;
+        float m_old = 0.f;
+        if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+          mo = __shfl_sync(kFull, moff, p);
+          if (lane == 0) m_old = *reinterpret_cast<const float*>(st + kGradBytes + kWrowBytes);
+          m_old = __shfl_sync(kFull, m_old, 0);
         }
-        if ((Em >> src) & 1u) {
-          if (open_head >= 0) {
-            apply_update<W, EPV, NV, OPT, true>(acc, wv[u], mv[u], weights + wo[u],
-                                                a.momentum1 + mo[u], Du[u], lane, a.lr, a.eps);
+        float wv[NV][EPV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          if (EPV * (lane + 32 * v) < Dp) {
+            load_wslot<W, EPV>(st + kGradBytes + (v * 32 + lane) * 16, wv[v]);
           } else {
-            row_store<EPV, NV>(sH + warp * ROW, acc, lane);  // tail of a run from an earlier tile
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) wv[v][e] = 0.f;
           }
-#pragma unroll
-          for (int v = 0; v < NV; ++v)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
         }
+        apply_update<W, EPV, NV, OPT, true>(acc, wv, m_old, weights + wo, a.momentum1 + mo, Dp, lane,
+                                            a.lr, a.eps);
+      } else {
+        row_store<EPV, NV>(sH + warp * ROW, acc, lane);  // tail of a run from an earlier tile
       }
+#pragma unroll
+      for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
     }
   }
+  cp_async_wait_group<0>();
   // The run still open at the end of the tile continues into the next one.
   // open_head < 0: the whole tile lies inside one run -> leading partial (H).
   if (cont && open_head < 0) row_store<EPV, NV>(sH + warp * ROW, acc, lane);
@@ -508,7 +573,8 @@ __global__ void __launch_bounds__(128) tbe_backward_combine_kernel(const BwdArgs
 template <typename W, typename K, int EPV, int NV, int OPT>
 static int launch_backward(const BwdArgs<K>& a, cudaStream_t s) {
   constexpr int ROW = NV * EPV * 32;
-  const size_t smem = sizeof(float) * kBwdWarps * ROW;
+  const size_t smem = sizeof(float) * kBwdWarps * ROW +
+                      (size_t)kBwdWarps * BwdRing<EPV, NV>::kStages * BwdRing<EPV, NV>::kStageBytes;
   auto tile = tbe_backward_tile_kernel<W, K, EPV, NV, OPT>;
   if (smem > 48 * 1024)
     B200_CUDA_TRY(cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -24,6 +24,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
     "-I", INCLUDE,
+    *os.environ.get("B200_NVCC_EXTRA", "").split(),  # tuning sweeps only (e.g. -DB200_BWD_STAGES=6)
 ]
 
 

@@ -172,12 +172,17 @@ int b200_tbe_int8_forward(const uint8_t* weights, const int64_t* weights_offsets
 /* InteractionArch.forward (torchrec/models/dlrm.py:193-219):
  * dense [B, D], sparse [B, F, D] -> out [B, D + (F+1)F/2] = [dense | triu(X X^T, 1)],
  * X = [dense; sparse]; row-major upper triangle, fp32. */
+/* out rows start every out_stride floats (>= the row width); columns past the row width are
+ * written as zeros, so with out_stride = round_up(width, 4) the consumer may run an aligned
+ * out_stride-wide GEMM over the buffer (the 479-wide row of Criteo DLRM otherwise forces
+ * cuBLAS onto its unaligned kernels). */
 int b200_interaction_forward(const float* dense, const float* sparse, int32_t B, int32_t F,
-                             int32_t D, float* out, void* stream);
-/* Backward of the same: grad_out [B, D + (F+1)F/2] -> grad_dense [B, D], grad_sparse [B,F,D]. */
+                             int32_t D, float* out, int64_t out_stride, void* stream);
+/* Backward of the same: grad_out [B, D + (F+1)F/2] at a pitch of grad_stride floats
+ * -> grad_dense [B, D], grad_sparse [B,F,D]. */
 int b200_interaction_backward(const float* dense, const float* sparse, const float* grad_out,
-                              int32_t B, int32_t F, int32_t D, float* grad_dense,
-                              float* grad_sparse, void* stream);
+                              int64_t grad_stride, int32_t B, int32_t F, int32_t D,
+                              float* grad_dense, float* grad_sparse, void* stream);
 
 /* ---------------------------------------------------------------- sharded data movement */
 

@@ -183,3 +183,51 @@ def test_multi_gpu_sharded_vs_unsharded(world):
                         "--master-addr", "127.0.0.1", "--master-port", "29611",
                         os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "DIST PARITY OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_interaction_row_pitch_and_pitched_linear():
+    """InteractionArch output sits at a 16-byte row pitch with zero padding, and RowPitchedLinear consumes
+    it with the same results/gradients as nn.Linear on a dense copy (fan-in 479 -> 480-wide GEMM)."""
+    from b200_sparse import ops
+    from torchrec.models.dlrm import InteractionArch
+    from torchrec.modules.mlp import RowPitchedLinear
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(3)
+    B, F, D, N = 70, 26, 128, 96
+    dense = torch.randn(B, D, device="cuda", requires_grad=True)
+    sparse = torch.randn(B, F, D, device="cuda", requires_grad=True)
+    out = InteractionArch(F)(dense, sparse)
+    width = D + (F + 1) * F // 2
+    assert out.shape == (B, width) and out.stride() == (480, 1)
+    full = out.detach().as_strided((B, 480), (480, 1), out.storage_offset())
+    assert torch.count_nonzero(full[:, width:]) == 0
+    lin = RowPitchedLinear(width, N, device=torch.device("cuda"))
+    assert lin.weight.shape == (N, width) and lin.weight.stride() == (480, 1)
+    assert lin.state_dict()["weight"].shape == (N, width)
+    ref = torch.nn.Linear(width, N, device="cuda")
+    with torch.no_grad():
+        ref.weight.copy_(lin.weight)
+        ref.bias.copy_(lin.bias)
+    y = lin(out)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    d2 = dense.detach().clone().requires_grad_(True)
+    s2 = sparse.detach().clone().requires_grad_(True)
+    out2 = ops.interaction_forward(d2.detach(), s2.detach())  # dense layout
+    assert out2.is_contiguous()
+    torch.testing.assert_close(out.detach(), out2, rtol=0, atol=0)
+    x2 = out2.clone().requires_grad_(True)
+    y2 = ref(x2)
+    y2.backward(gy)
+    torch.testing.assert_close(y, y2, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(lin.weight.grad, ref.weight.grad, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(lin.bias.grad, ref.bias.grad, rtol=1e-5, atol=1e-4)
+    gd, gs = ops.interaction_backward(d2.detach(), s2.detach(), x2.grad)
+    torch.testing.assert_close(dense.grad, gd, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(sparse.grad, gs, rtol=1e-5, atol=1e-4)
+    # an unmarked / dense input takes the plain path
+    torch.testing.assert_close(lin(out2), ref(out2), rtol=1e-5, atol=1e-4)
+    # an SGD step keeps the pad column at zero and the parameter a view of the pitched buffer
+    torch.optim.SGD(lin.parameters(), lr=0.1).step()
+    wf = lin.weight.detach().as_strided((N, 480), (480, 1), lin.weight.storage_offset())
+    assert torch.count_nonzero(wf[:, width:]) == 0 and lin.weight.stride() == (480, 1)

@@ -46,8 +46,8 @@ SIGNATURES = {
     "b200_quantize_rowwise_8bit_sbhalf": (_int, [_p, _i64, _i32, _p, _p]),
     "b200_tbe_int8_forward": (_int, [_p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _int, _p,
                                      _int, _p, _int, _p]),
-    "b200_interaction_forward": (_int, [_p, _p, _i32, _i32, _i32, _p, _p]),
-    "b200_interaction_backward": (_int, [_p, _p, _p, _i32, _i32, _i32, _p, _p, _p]),
+    "b200_interaction_forward": (_int, [_p, _p, _i32, _i32, _i32, _p, _i64, _p]),
+    "b200_interaction_backward": (_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p]),
     "b200_pooled_a2a_recat": (_int, [_p, _p, _p, _i32, _i32, _int, _f32, _p]),
 }
 

@@ -405,17 +405,21 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
 
 
 # ------------------------------------------------------------------------ dot interaction
-def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor) -> torch.Tensor:
+def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
+    """[B, D + (F+1)F/2].  pad_rows=True returns a view of a buffer whose rows sit at a 16-byte
+    pitch with zeros in the pad columns (see b200_sparse.h); the view's stride(0) is the pitch."""
     dev = _need_cuda(dense, sparse)
     B, D = dense.shape
     F = sparse.shape[1]
     dense = dense.float().contiguous()
     sparse = sparse.float().contiguous()
-    out = torch.empty((B, D + (F + 1) * F // 2), dtype=torch.float32, device=dev)
+    width = D + (F + 1) * F // 2
+    pitch = (width + 3) // 4 * 4 if pad_rows else width
+    buf = torch.empty((B, pitch), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _timed("interaction_forward", dev, 1):
-        check(lib.b200_interaction_forward(_p(dense), _p(sparse), B, F, D, _p(out), _stream(dev)),
+        check(lib.b200_interaction_forward(_p(dense), _p(sparse), B, F, D, _p(buf), pitch, _stream(dev)),
               "b200_interaction_forward")
-    return out
+    return buf[:, :width] if pitch != width else buf
 
 
 def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
@@ -423,12 +427,14 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     dev = _need_cuda(dense, sparse, grad_out)
     B, D = dense.shape
     F = sparse.shape[1]
-    grad_out = grad_out.float().contiguous()
+    grad_out = grad_out.float()
+    if grad_out.dim() != 2 or grad_out.stride(1) != 1 or grad_out.stride(0) < grad_out.shape[1]:
+        grad_out = grad_out.contiguous()  # a row-pitched view is consumed in place
     gd = torch.empty_like(dense)
     gs = torch.empty_like(sparse)
     with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
-        check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), B, F, D, _p(gd), _p(gs),
-                                            _stream(dev)), "b200_interaction_backward")
+        check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D,
+                                            _p(gd), _p(gs), _stream(dev)), "b200_interaction_backward")
     return gd, gs
 
 

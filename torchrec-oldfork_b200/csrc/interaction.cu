@@ -22,7 +22,7 @@ __device__ __forceinline__ int tri_index(int i, int j, int n) {  // i < j
 // smem row stride D + 4 floats keeps 16-byte alignment and staggers banks between rows.
 __global__ void __launch_bounds__(kIxThreads)
 interaction_forward_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
-                           int32_t B, int32_t F, int32_t D, float* __restrict__ out) {
+                           int32_t B, int32_t F, int32_t D, float* __restrict__ out, int64_t out_stride) {
   extern __shared__ __align__(16) float smem[];
   const int n = F + 1;
   const int ld = D + 4;
@@ -52,8 +52,9 @@ interaction_forward_kernel(const float* __restrict__ dense, const float* __restr
     __syncthreads();
     if (live) {
       // dense passthrough; output rows are only 4-byte aligned (out_dim = 479 at F=26, D=128)
-      for (int c = tid; c < D; c += kIxGroup) out[s * out_dim + c] = X[c];
-      float* o = out + s * out_dim + D;
+      for (int c = tid; c < D; c += kIxGroup) out[s * out_stride + c] = X[c];
+      for (int c = out_dim + tid; c < out_stride; c += kIxGroup) out[s * out_stride + c] = 0.f;  // row padding
+      float* o = out + s * out_stride + D;
       for (int blk = tid; blk < n_blocks; blk += kIxGroup) {
         // decode block pair (bi <= bj) from the linear index
         int bi = 0, rem = blk;
@@ -108,8 +109,8 @@ interaction_forward_kernel(const float* __restrict__ dense, const float* __restr
 // triangle; grad_dense additionally receives the passthrough part grad_out[:, :D].
 __global__ void __launch_bounds__(kIxThreads)
 interaction_backward_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
-                            const float* __restrict__ grad_out, int32_t B, int32_t F, int32_t D,
-                            float* __restrict__ grad_dense, float* __restrict__ grad_sparse) {
+                            const float* __restrict__ grad_out, int64_t grad_stride, int32_t B, int32_t F,
+                            int32_t D, float* __restrict__ grad_dense, float* __restrict__ grad_sparse) {
   extern __shared__ __align__(16) float smem[];
   const int n = F + 1;
   const int ld = D + 4;
@@ -137,7 +138,7 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
         const int r = c / D4, cc = c - r * D4;
         *reinterpret_cast<uint4*>(X + (size_t)(r + 1) * ld + 4 * cc) = ldg_stream_16(s4 + c);
       }
-      const float* g = grad_out + s * out_dim + D;
+      const float* g = grad_out + s * grad_stride + D;
       for (int i = tid; i < n; i += kIxGroup) G[i * ldg + i] = 0.f;
       // walk the triangle row by row
       for (int p = tid; p < n_tri; p += kIxGroup) {
@@ -154,7 +155,7 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
     }
     __syncthreads();
     if (live) {
-      const float* gpass = grad_out + s * out_dim;
+      const float* gpass = grad_out + s * grad_stride;
       // work item = (row i, float4 column c)
       for (int w = tid; w < n * D4; w += kIxGroup) {
         const int i = w / D4, c = w - i * D4;
@@ -227,7 +228,8 @@ __device__ __forceinline__ void cp_async_wait() {
 
 __global__ void __launch_bounds__(kMmaWarps * 32, 1)
 interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
-                               int32_t B, int32_t F, int32_t D, float* __restrict__ out) {
+                               int32_t B, int32_t F, int32_t D, float* __restrict__ out,
+                               int64_t out_stride) {
   extern __shared__ __align__(16) float smem[];
   const int n = F + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -242,6 +244,10 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
   const int ntiles = (n + 7) >> 3;  // live 8-row tiles
   const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
   const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
+  // rows at a 16-byte pitch (out_stride == round_up(out_dim, 4)) leave with 128-bit stores; the pad
+  // columns carry zeros so a consumer may treat the row as out_stride wide
+  const bool vec_out = out_stride == outs_floats && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  for (int c = out_dim + lane; c < outs_floats; c += 32) outs[c] = 0.f;
 
   auto issue = [&](int64_t q) {
     if (q < Q) {
@@ -313,8 +319,14 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
         }
       }
       __syncwarp();
-      float* dst = out + (gw + it * tw) * out_dim;
-      for (int c = lane; c < out_dim; c += 32) dst[c] = outs[c];
+      float* dst = out + (gw + it * tw) * out_stride;
+      if (vec_out) {
+        for (int c = lane; c < (outs_floats >> 2); c += 32)
+          reinterpret_cast<float4*>(dst)[c] = reinterpret_cast<const float4*>(outs)[c];
+      } else {
+        for (int c = lane; c < out_dim; c += 32) dst[c] = outs[c];
+        for (int c = out_dim + lane; c < out_stride; c += 32) dst[c] = 0.f;
+      }
     }
   }
 }
@@ -327,8 +339,9 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 // 4-byte aligned).  Results leave as 8-byte stores that fill whole 32-byte sectors.
 __global__ void __launch_bounds__(kMmaWarps * 32, 1)
 interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
-                                const float* __restrict__ grad_out, int32_t B, int32_t F, int32_t D,
-                                float* __restrict__ grad_dense, float* __restrict__ grad_sparse) {
+                                const float* __restrict__ grad_out, int64_t grad_stride, int32_t B,
+                                int32_t F, int32_t D, float* __restrict__ grad_dense,
+                                float* __restrict__ grad_sparse) {
   extern __shared__ __align__(16) float smem[];
   const int n = F + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -348,6 +361,9 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
   const int ksteps = (n + 7) >> 3;
   const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
   const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
+  // 16-byte copies of grad_out rows when their pitch allows it (the pad floats are read, never used)
+  const bool vec_g = (grad_stride & 3) == 0 && grad_stride >= gs_floats &&
+                     (reinterpret_cast<uintptr_t>(grad_out) & 15) == 0;
 
   for (int p = threadIdx.x; p < n_tri; p += blockDim.x) {
     int i = 0, rem = p;
@@ -374,8 +390,12 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
       }
       if (h == 0) {
         float* gd = gst + (it & 1) * gs_floats;
-        const float* gsrc = grad_out + s * out_dim;
-        for (int c = lane; c < out_dim; c += 32) cp_async_4(gd + c, gsrc + c);
+        const float* gsrc = grad_out + s * grad_stride;
+        if (vec_g) {
+          for (int c = lane; c < (gs_floats >> 2); c += 32) cp_async_16(gd + 4 * c, gsrc + 4 * c);
+        } else {
+          for (int c = lane; c < out_dim; c += 32) cp_async_4(gd + c, gsrc + c);
+        }
       }
     }
     cp_async_commit();
@@ -466,10 +486,12 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
 }  // namespace b200
 
 extern "C" int b200_interaction_forward(const float* dense, const float* sparse, int32_t B,
-                                        int32_t F, int32_t D, float* out, void* stream) {
+                                        int32_t F, int32_t D, float* out, int64_t out_stride,
+                                        void* stream) {
   using namespace b200;
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
+  if (out_stride < D + (int64_t)(F + 1) * F / 2) return B200_EINVAL;
   const int n = F + 1;
   if (n <= 32 && D % kKC == 0) {
     const int out_dim = D + n * (n - 1) / 2;
@@ -480,7 +502,7 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
       int64_t mgrid = ceil_div(B, kMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
       interaction_forward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
-          dense, sparse, B, F, D, out);
+          dense, sparse, B, F, D, out, out_stride);
       B200_LAUNCH_CHECK();
       return B200_OK;
     }
@@ -492,17 +514,19 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
   int64_t grid = ceil_div(B, kIxSamplesPerCta);
   if (grid > (int64_t)kNumSMs * 8) grid = (int64_t)kNumSMs * 8;
   interaction_forward_kernel<<<(unsigned)grid, kIxThreads, smem, (cudaStream_t)stream>>>(
-      dense, sparse, B, F, D, out);
+      dense, sparse, B, F, D, out, out_stride);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
 extern "C" int b200_interaction_backward(const float* dense, const float* sparse,
-                                         const float* grad_out, int32_t B, int32_t F, int32_t D,
-                                         float* grad_dense, float* grad_sparse, void* stream) {
+                                         const float* grad_out, int64_t grad_stride, int32_t B,
+                                         int32_t F, int32_t D, float* grad_dense,
+                                         float* grad_sparse, void* stream) {
   using namespace b200;
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
+  if (grad_stride < D + (int64_t)(F + 1) * F / 2) return B200_EINVAL;
   const int n = F + 1;
   if (n <= 32 && D % kKC == 0) {
     const int n_tri = n * (n - 1) / 2;
@@ -514,7 +538,7 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
       int64_t mgrid = ceil_div(B, kMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
       interaction_backward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
-          dense, sparse, grad_out, B, F, D, grad_dense, grad_sparse);
+          dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
       B200_LAUNCH_CHECK();
       return B200_OK;
     }
@@ -526,7 +550,7 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
   int64_t grid = ceil_div(B, kIxSamplesPerCta);
   if (grid > (int64_t)kNumSMs * 8) grid = (int64_t)kNumSMs * 8;
   interaction_backward_kernel<<<(unsigned)grid, kIxThreads, smem, (cudaStream_t)stream>>>(
-      dense, sparse, grad_out, B, F, D, grad_dense, grad_sparse);
+      dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

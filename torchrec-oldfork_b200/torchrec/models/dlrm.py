@@ -13,7 +13,7 @@ from torch import nn
 from b200_sparse import ops as _b200
 from torchrec.datasets.utils import Batch
 from torchrec.modules.embedding_modules import EmbeddingBagCollection
-from torchrec.modules.mlp import MLP
+from torchrec.modules.mlp import MLP, mark_zero_padded
 from torchrec.sparse.jagged_tensor import KeyedJaggedTensor, KeyedTensor
 
 
@@ -68,7 +68,8 @@ class _DotInteraction(torch.autograd.Function):
     def forward(ctx, dense: torch.Tensor, sparse: torch.Tensor) -> torch.Tensor:
         dense_c, sparse_c = dense.float().contiguous(), sparse.float().contiguous()
         ctx.save_for_backward(dense_c, sparse_c)
-        return _b200.interaction_forward(dense_c, sparse_c)
+        # rows at a 16-byte pitch, zeros in the pad: the next Linear can run an aligned GEMM on it
+        return _b200.interaction_forward(dense_c, sparse_c, pad_rows=True)
 
     @staticmethod
     def backward(ctx, grad_out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -90,7 +91,7 @@ class InteractionArch(nn.Module):
         if self.F <= 0:
             return dense_features
         if dense_features.is_cuda and dense_features.shape[1] % 4 == 0:
-            return _DotInteraction.apply(dense_features, sparse_features)
+            return mark_zero_padded(_DotInteraction.apply(dense_features, sparse_features))
         # shapes the kernel does not cover (D % 4 != 0): reference formulation in plain torch
         combined = torch.cat((dense_features.unsqueeze(1), sparse_features), dim=1)
         inter = torch.bmm(combined, combined.transpose(1, 2))

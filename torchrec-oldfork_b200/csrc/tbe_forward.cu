@@ -11,15 +11,62 @@
 //    are detected on the fly from the 33 offsets held in registers.  The number of row
 //    gathers in flight is therefore independent of the pooling factor: at L = 1 the warp
 //    still keeps 8 x 16-byte loads per lane outstanding (the reference has one).
-//  * ids of the next batch are fetched while the rows of the current batch are in flight
-//    (two dependent DRAM latencies overlapped by software pipelining).
-//  * rows are read with ld.global.nc.L1::no_allocate 128-bit loads and the output row is
-//    written once with streaming 128-bit stores.
+//  * ids travel as one coalesced load per 32 positions (next chunk in flight while the current
+//    one is used) and are broadcast through a 64-entry shared-memory ring.
+//  * rows stream through a warp-private cp.async ring (8 stages of one row): every lane copies
+//    and later consumes its own 16-byte slot, so there are no barriers, the kernel needs ~34
+//    registers and 12+ CTAs/SM keep >100 KB of row reads in flight per SM.
+//  * the pooled row is written once with streaming 128-bit stores.
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int kFwdThreads = 128;
+constexpr int kFwdWarps = kFwdThreads / 32;
+
+// Ring geometry: one stage = one table row laid out as 16-byte lane slots ([v][lane]).
+template <int NV>
+struct FwdRing {
+  static constexpr int kStageBytes = NV * 512;
+  static constexpr int kStages = NV >= 4 ? 2 : (NV == 2 ? 4 : 8);  // power of two
+  static constexpr int kWarpBytes = kStages * kStageBytes + 64 * 8 + 64 * 4;  // + id ring + weight ring
+};
+
+__device__ __forceinline__ void fwd_cp16(void* dst_smem, const void* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void fwd_cp8(void* dst_smem, const void* src) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void fwd_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void fwd_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// one lane's staged piece of a row (EPV elements of W) -> fp32
+template <typename W, int EPV>
+__device__ __forceinline__ void fwd_load_slot(const unsigned char* p, float (&f)[EPV]) {
+  if constexpr (sizeof(W) == 4) {
+    const float4 x = *reinterpret_cast<const float4*>(p);
+    f[0] = x.x;
+    f[1] = x.y;
+    f[2] = x.z;
+    f[3] = x.w;
+  } else if constexpr (EPV == 8) {
+    const uint4 r = *reinterpret_cast<const uint4*>(p);
+    ElemCvt<W>::unpack2(r.x, f[0], f[1]);
+    ElemCvt<W>::unpack2(r.y, f[2], f[3]);
+    ElemCvt<W>::unpack2(r.z, f[4], f[5]);
+    ElemCvt<W>::unpack2(r.w, f[6], f[7]);
+  } else {
+    const uint2 r = *reinterpret_cast<const uint2*>(p);
+    ElemCvt<W>::unpack2(r.x, f[0], f[1]);
+    ElemCvt<W>::unpack2(r.y, f[2], f[3]);
+  }
+}
 
 template <typename W, typename O, int EPV, int NV>
 __global__ void __launch_bounds__(kFwdThreads)
@@ -28,9 +75,13 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
                    int32_t tiles_per_table, const void* __restrict__ indices,
                    const void* __restrict__ offsets, bool idx64,
                    const float* __restrict__ psw, bool mean, O* __restrict__ out) {
-  constexpr int U = (32 / (NV * EPV)) > 0 ? (32 / (NV * EPV)) : 1;  // rows in flight per warp
+  constexpr int kStages = FwdRing<NV>::kStages;
+  constexpr int kStageBytes = FwdRing<NV>::kStageBytes;
+  constexpr int kAhead = kStages - 1;
+  extern __shared__ __align__(16) unsigned char fwd_smem[];
   const int lane = threadIdx.x & 31;
-  const int64_t tile = (int64_t)blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5);
+  const int warp = threadIdx.x >> 5;
+  const int64_t tile = (int64_t)blockIdx.x * kFwdWarps + warp;
   if (tile >= (int64_t)T * tiles_per_table) return;
   const int t = (int)(tile / tiles_per_table);
   const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
@@ -51,7 +102,10 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
   unsigned remaining = __ballot_sync(kFull, in_tile && rel_end > rel_start);
   const unsigned empty = __ballot_sync(kFull, in_tile && rel_end <= rel_start);
 
-  O* __restrict__ out_tile = out + (int64_t)b0 * total_D + D_begin;
+  O* __restrict__ out_tile = out + (int64_t)b0 * total_D + D_begin + EPV * lane;
+  bool act[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) act[v] = EPV * (lane + 32 * v) < D;
 
   // Empty bags pool to zeros.
   for (unsigned m = empty; m; m &= m - 1) {
@@ -60,108 +114,119 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
 #pragma unroll
     for (int e = 0; e < EPV; ++e) z[e] = 0.f;
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      const int d = EPV * (lane + 32 * v);
-      if (d < D) store_vec<O, EPV, true>(out_tile + (int64_t)j * total_D + d, z);
-    }
+    for (int v = 0; v < NV; ++v)
+      if (act[v]) store_vec<O, EPV, true>(out_tile + (int64_t)j * total_D + EPV * 32 * v, z);
   }
   if (len <= 0) return;
+
+  unsigned char* const wsm = fwd_smem + (size_t)warp * FwdRing<NV>::kWarpBytes;
+  unsigned char* const lring = wsm + lane * 16;
+  int64_t* const sid = reinterpret_cast<int64_t*>(wsm + kStages * kStageBytes);  // [64] ids, 2 chunks
+  float* const sw = reinterpret_cast<float*>(sid + 64);                           // [64] weights
+  const bool weighted = psw != nullptr;
+  const W* const lrow = wtab + EPV * lane;
+
+  // ids travel one coalesced load per 32 positions; chunk c+1 is in flight while chunk c is used
+  const int nchunks = (len + 31) >> 5;
+  auto load_chunk = [&](int c, int64_t& id, float& w) {
+    const int32_t p = 32 * c + lane;
+    id = 0;
+    w = 1.f;
+    if (p < len) {
+      id = load_index(indices, S0 + p, idx64);
+      if (weighted) w = psw[S0 + p];
+    }
+  };
+  int64_t id_nxt;
+  float w_nxt;
+  load_chunk(0, id_nxt, w_nxt);
+  sid[lane] = id_nxt;
+  sw[lane] = w_nxt;
+  __syncwarp();
+  if (nchunks > 1) load_chunk(1, id_nxt, w_nxt);
+
+  auto issue = [&](int32_t p, int stage) {
+    const W* row = lrow + sid[p & 63] * D;
+    unsigned char* st = lring + stage * kStageBytes;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+      if (act[v]) {
+        if constexpr (EPV * sizeof(W) == 16) {
+          fwd_cp16(st + v * 512, row + EPV * 32 * v);
+        } else {
+          fwd_cp8(st + v * 512, row + EPV * 32 * v);
+        }
+      }
+  };
 
   float acc[NV][EPV];
 #pragma unroll
   for (int v = 0; v < NV; ++v)
 #pragma unroll
     for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
-
-  int cur_bag = remaining ? (__ffs(remaining) - 1) : 0;
+  int cur_bag = __ffs(remaining) - 1;  // len > 0 => some bag is non-empty
   int32_t cur_end = __shfl_sync(kFull, rel_end, cur_bag);
   int32_t prev_end = 0;
-  const bool weighted = psw != nullptr;
 
-  int64_t idx_cur[U];
-  float w_cur[U];
 #pragma unroll
-  for (int u = 0; u < U; ++u) {
-    idx_cur[u] = 0;
-    w_cur[u] = 1.f;
-    if (u < len) {
-      idx_cur[u] = load_index(indices, S0 + u, idx64);
-      if (weighted) w_cur[u] = psw[S0 + u];
-    }
+  for (int q = 0; q < kAhead; ++q) {
+    if (q < len) issue(q, q);
+    fwd_commit();
   }
-
-  for (int32_t q = 0; q < len; q += U) {
-    // ids of the next batch (independent of the row loads below)
-    int64_t idx_nxt[U];
-    float w_nxt[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int32_t p = q + U + u;
-      idx_nxt[u] = 0;
-      w_nxt[u] = 1.f;
-      if (p < len) {
-        idx_nxt[u] = load_index(indices, S0 + p, idx64);
-        if (weighted) w_nxt[u] = psw[S0 + p];
-      }
+  for (int c = 0; c < nchunks; ++c) {
+    __syncwarp();
+    if (c + 1 < nchunks) {  // publish the ids of the next chunk (its slot was last read a chunk ago)
+      sid[((c + 1) & 1) * 32 + lane] = id_nxt;
+      sw[((c + 1) & 1) * 32 + lane] = w_nxt;
     }
-    // gather U rows
-    float rows[U][NV][EPV];
+    __syncwarp();
+    if (c + 2 < nchunks) load_chunk(c + 2, id_nxt, w_nxt);
+#pragma unroll 1
+    for (int p0 = 32 * c; p0 < 32 * c + 32 && p0 < len; p0 += 8) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const W* __restrict__ row = wtab + idx_cur[u] * D;
-      const bool live = q + u < len;
-#pragma unroll
-      for (int v = 0; v < NV; ++v) {
-        const int d = EPV * (lane + 32 * v);
-        if (live && d < D) {
-          load_vec<W, EPV, true>(row + d, rows[u][v]);
-        } else {
-#pragma unroll
-          for (int e = 0; e < EPV; ++e) rows[u][v][e] = 0.f;
-        }
-      }
-    }
-    // accumulate in stream order, flushing at bag boundaries
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (q + u < len) {
-        if (weighted) {
+      for (int q = 0; q < 8; ++q) {
+        const int32_t p = p0 + q;
+        if (p + kAhead < len) issue(p + kAhead, (q + kAhead) & (kStages - 1));
+        fwd_commit();
+        if (p < len) {
+          fwd_wait<kAhead>();
+          const unsigned char* st = lring + (q & (kStages - 1)) * kStageBytes;
+          const float wp = weighted ? sw[p & 63] : 1.f;
 #pragma unroll
           for (int v = 0; v < NV; ++v)
+            if (act[v]) {
+              float x[EPV];
+              fwd_load_slot<W, EPV>(st + v * 512, x);
+              if (weighted) {
 #pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] = fmaf(w_cur[u], rows[u][v][e], acc[v][e]);
-        } else {
+                for (int e = 0; e < EPV; ++e) acc[v][e] = fmaf(wp, x[e], acc[v][e]);
+              } else {
 #pragma unroll
-          for (int v = 0; v < NV; ++v)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] += rows[u][v][e];
-        }
-        if (q + u + 1 == cur_end) {
-          const float scale = mean ? 1.0f / (float)(cur_end - prev_end) : 1.0f;
-#pragma unroll
-          for (int v = 0; v < NV; ++v) {
-            const int d = EPV * (lane + 32 * v);
-            if (mean) {
-#pragma unroll
-              for (int e = 0; e < EPV; ++e) acc[v][e] *= scale;
+                for (int e = 0; e < EPV; ++e) acc[v][e] += x[e];
+              }
             }
-            if (d < D) store_vec<O, EPV, true>(out_tile + (int64_t)cur_bag * total_D + d, acc[v]);
+          if (p + 1 == cur_end) {  // bag boundary: write the pooled row once
+            const float scale = mean ? 1.0f / (float)(cur_end - prev_end) : 1.0f;
 #pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
+            for (int v = 0; v < NV; ++v) {
+              if (mean) {
+#pragma unroll
+                for (int e = 0; e < EPV; ++e) acc[v][e] *= scale;
+              }
+              if (act[v]) store_vec<O, EPV, true>(out_tile + (int64_t)cur_bag * total_D + EPV * 32 * v, acc[v]);
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
+            }
+            prev_end = cur_end;
+            remaining &= remaining - 1;
+            cur_bag = remaining ? (__ffs(remaining) - 1) : 0;
+            cur_end = remaining ? __shfl_sync(kFull, rel_end, cur_bag) : 0x7fffffff;
           }
-          prev_end = cur_end;
-          remaining &= remaining - 1;
-          cur_bag = remaining ? (__ffs(remaining) - 1) : 0;
-          cur_end = remaining ? __shfl_sync(kFull, rel_end, cur_bag) : 0x7fffffff;
         }
       }
     }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      idx_cur[u] = idx_nxt[u];
-      w_cur[u] = w_nxt[u];
-    }
   }
+  fwd_wait<0>();
 }
 
 template <typename W, typename O, int EPV>
@@ -176,7 +241,7 @@ static int launch_forward_nv(const void* weights, const int64_t* weights_offsets
   if (grid > 0x7fffffffLL) return B200_EINVAL;
   const int vecs = (int)ceil_div(max_D, EPV * 32);
 #define B200_FWD_LAUNCH(NV)                                                                     \
-  tbe_forward_kernel<W, O, EPV, NV><<<(unsigned)grid, kFwdThreads, 0, s>>>(                      \
+  tbe_forward_kernel<W, O, EPV, NV><<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>( \
       (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table, indices,    \
       offsets, idx64, psw, mean, (O*)output)
   if (vecs <= 1)

@@ -194,8 +194,12 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
 // 8 warps x 2 stages (~115 KB) stay in flight per SM.  The [D + n(n-1)/2] output row is assembled
 // in shared memory and written with coalesced stores (rows are only 4-byte aligned).
 // ---------------------------------------------------------------------------------------------
-constexpr int kMmaWarps = 8;
-constexpr int kKC = 64;  // columns per pipeline stage
+// 12 warps per SM: the kernels are latency-bound per warp (LDS -> split -> dependent MMAs), the
+// tensor pipe is ~1/3 busy at 8 warps (ncu), so residency is what shared memory is spent on.
+constexpr int kFwdMmaWarps = 12;
+constexpr int kFwdKC = 64;   // columns per pipeline stage, forward (2 stages per warp)
+constexpr int kBwdMmaWarps = 12;
+constexpr int kBwdKC = 32;   // backward stages are quarter samples
 
 __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                          uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -206,10 +210,13 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// x = hi + lo with hi, lo representable in TF32 (10-bit mantissa).  hi is x rounded to nearest
+// (integer add of half an ulp, then mask), so x - hi is exact in fp32 and symmetric around 0; lo is
+// that remainder with the low 13 bits cleared (error <= 2^-21 |x|).  4 integer/FP ops instead of
+// the two cvt.rna.tf32.f32, which sm_100 expands to ~5 instructions each (measured with ncu).
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-  const float r = x - __uint_as_float(hi);
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+  hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi)) & 0xffffe000u;
 }
 
 __device__ __forceinline__ void cp_async_16(float* dst_smem, const float* src) {
@@ -226,7 +233,7 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-__global__ void __launch_bounds__(kMmaWarps * 32, 1)
+__global__ void __launch_bounds__(kFwdMmaWarps * 32, 1)
 interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
                                int32_t B, int32_t F, int32_t D, float* __restrict__ out,
                                int64_t out_stride) {
@@ -234,38 +241,47 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
   const int n = F + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
-  constexpr int ld = kKC + 4;
+  constexpr int ld = kFwdKC + 4;
   const int stage_floats = n * ld;
   const int out_dim = D + n * (n - 1) / 2;
   const int outs_floats = (out_dim + 3) & ~3;
-  float* wbase = smem + (size_t)warp * (3 * stage_floats + outs_floats);
-  float* outs = wbase + 3 * stage_floats;
-  const int nch = D / kKC;
+  float* wbase = smem + (size_t)warp * (2 * stage_floats + outs_floats);
+  float* outs = wbase + 2 * stage_floats;
+  const int nch = D / kFwdKC;
   const int ntiles = (n + 7) >> 3;  // live 8-row tiles
-  const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
+  const int64_t gw = (int64_t)blockIdx.x * kFwdMmaWarps + warp, tw = (int64_t)gridDim.x * kFwdMmaWarps;
   const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
   // rows at a 16-byte pitch (out_stride == round_up(out_dim, 4)) leave with 128-bit stores; the pad
   // columns carry zeros so a consumer may treat the row as out_stride wide
   const bool vec_out = out_stride == outs_floats && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
   for (int c = out_dim + lane; c < outs_floats; c += 32) outs[c] = 0.f;
 
+  // copy pattern of a stage: lane l moves 16-byte chunk (l & 15) of rows (l >> 4) + 2k, k = 0, 1, ...
+  // Row 0 is the dense vector, rows 1..F the sample's sparse block (contiguous, D floats apart).
+  const int r0 = lane >> 4, cc4 = 4 * (lane & 15);
+  int stage_of = 0;  // q % 2 of the next stage to issue
+  int64_t s_i = gw;  // sample / column chunk of the next stage to issue
+  int h_i = 0;
   auto issue = [&](int64_t q) {
     if (q < Q) {
-      const int64_t it = q / nch;
-      const int h = (int)(q - it * nch);
-      const int64_t s = gw + it * tw;
-      float* st = wbase + (q % 3) * stage_floats;
-      const float* dsrc = dense + s * D + h * kKC;
-      const float* ssrc = sparse + s * (int64_t)F * D + h * kKC;
-      for (int c = lane; c < n * (kKC / 4); c += 32) {
-        const int r = c >> 4, cc = c & 15;
-        cp_async_16(st + r * ld + 4 * cc, (r == 0 ? dsrc : ssrc + (int64_t)(r - 1) * D) + 4 * cc);
+      float* dst = wbase + stage_of * stage_floats + r0 * ld + cc4;
+      const float* src = sparse + s_i * (int64_t)F * D + (int64_t)(r0 - 1) * D + h_i * kFwdKC + cc4;
+      if (r0 == 0) cp_async_16(dst, dense + s_i * D + h_i * kFwdKC + cc4);
+      else if (r0 < n) cp_async_16(dst, src);
+      for (int r = r0 + 2; r < n; r += 2) {
+        dst += 2 * ld;
+        src += 2 * D;
+        cp_async_16(dst, src);
+      }
+      if (++h_i == nch) {
+        h_i = 0;
+        s_i += tw;
       }
     }
+    stage_of ^= 1;
     cp_async_commit();  // always: keeps the group count uniform
   };
   issue(0);
-  issue(1);
 
   constexpr int kTM[6] = {0, 0, 0, 0, 1, 1};
   constexpr int kTN[6] = {0, 1, 2, 3, 2, 3};
@@ -274,23 +290,35 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 #pragma unroll
   for (int j = 0; j < 4; ++j) rowoff[j] = min(8 * j + g, n - 1) * ld + t;
 
+  // output slot of every accumulator element of this lane (-1: lower triangle / padding)
+  int ooff[6][4];
+#pragma unroll
+  for (int x = 0; x < 6; ++x)
+#pragma unroll
+    for (int y = 0; y < 4; ++y) {
+      const int i = 16 * kTM[x] + g + ((y & 2) ? 8 : 0);
+      const int j = 8 * kTN[x] + 2 * t + (y & 1);
+      ooff[x][y] = (i < j && j < n) ? D + tri_index(i, j, n) : -1;
+    }
+  int stage_cons = 0;
+  int64_t it = 0;
+  int h = 0;
   for (int64_t q = 0; q < Q; ++q) {
-    cp_async_wait<1>();
+    cp_async_wait<0>();
     __syncwarp();
-    issue(q + 2);
-    const int64_t it = q / nch;
-    const int h = (int)(q - it * nch);
-    const float* st = wbase + (q % 3) * stage_floats;
+    issue(q + 1);
+    const float* st = wbase + stage_cons * stage_floats;
+    stage_cons ^= 1;
     if (h == 0) {
 #pragma unroll
       for (int x = 0; x < 6; ++x)
 #pragma unroll
         for (int y = 0; y < 4; ++y) acc[x][y] = 0.f;
     }
-    outs[h * kKC + lane] = st[lane];  // dense passthrough
-    outs[h * kKC + 32 + lane] = st[32 + lane];
+    outs[h * kFwdKC + lane] = st[lane];  // dense passthrough
+    outs[h * kFwdKC + 32 + lane] = st[32 + lane];
 #pragma unroll 2
-    for (int k0 = 0; k0 < kKC; k0 += 8) {
+    for (int k0 = 0; k0 < kFwdKC; k0 += 8) {
       uint32_t bh[4][2], bl[4][2];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -308,15 +336,11 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
       }
     }
     if (h == nch - 1) {
-      float* o = outs + D;
 #pragma unroll
       for (int x = 0; x < 6; ++x) {
 #pragma unroll
-        for (int y = 0; y < 4; ++y) {
-          const int i = 16 * kTM[x] + g + ((y & 2) ? 8 : 0);
-          const int j = 8 * kTN[x] + 2 * t + (y & 1);
-          if (i < j && j < n) o[tri_index(i, j, n)] = acc[x][y];
-        }
+        for (int y = 0; y < 4; ++y)
+          if (ooff[x][y] >= 0) outs[ooff[x][y]] = acc[x][y];
       }
       __syncwarp();
       float* dst = out + (gw + it * tw) * out_stride;
@@ -328,6 +352,10 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
         for (int c = out_dim + lane; c < out_stride; c += 32) dst[c] = 0.f;
       }
     }
+    if (++h == nch) {
+      h = 0;
+      ++it;
+    }
   }
 }
 
@@ -337,7 +365,7 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 // kept in registers), X streamed in 64-column stages with row stride 72 (B-fragment loads are
 // conflict free).  grad_out rows ride in the same cp.async groups (4-byte copies: rows are only
 // 4-byte aligned).  Results leave as 8-byte stores that fill whole 32-byte sectors.
-__global__ void __launch_bounds__(kMmaWarps * 32, 1)
+__global__ void __launch_bounds__(kBwdMmaWarps * 32, 1)
 interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
                                 const float* __restrict__ grad_out, int64_t grad_stride, int32_t B,
                                 int32_t F, int32_t D, float* __restrict__ grad_dense,
@@ -346,20 +374,20 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
   const int n = F + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
-  constexpr int ld = kKC + 8;
+  constexpr int ld = kBwdKC + 8;
   constexpr int ldG = 36;
   const int stage_floats = n * ld;
   const int n_tri = n * (n - 1) / 2;
   const int out_dim = D + n_tri;
   const int gs_floats = (out_dim + 3) & ~3;
   const int per_warp = 2 * stage_floats + 32 * ldG + 2 * gs_floats;
-  uint16_t* ij = reinterpret_cast<uint16_t*>(smem + (size_t)kMmaWarps * per_warp);  // [n_tri] (i | j << 8)
+  uint16_t* ij = reinterpret_cast<uint16_t*>(smem + (size_t)kBwdMmaWarps * per_warp);  // [n_tri] (i | j << 8)
   float* wbase = smem + (size_t)warp * per_warp;
   float* Gs = wbase + 2 * stage_floats;
   float* gst = Gs + 32 * ldG;
-  const int nch = D / kKC;
+  const int nch = D / kBwdKC;
   const int ksteps = (n + 7) >> 3;
-  const int64_t gw = (int64_t)blockIdx.x * kMmaWarps + warp, tw = (int64_t)gridDim.x * kMmaWarps;
+  const int64_t gw = (int64_t)blockIdx.x * kBwdMmaWarps + warp, tw = (int64_t)gridDim.x * kBwdMmaWarps;
   const int64_t Q = gw < B ? ((B - gw + tw - 1) / tw) * nch : 0;
   // 16-byte copies of grad_out rows when their pitch allows it (the pad floats are read, never used)
   const bool vec_g = (grad_stride & 3) == 0 && grad_stride >= gs_floats &&
@@ -376,28 +404,38 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
   for (int c = lane; c < 32 * ldG; c += 32) Gs[c] = 0.f;  // diagonal and padding stay zero
   __syncthreads();
 
+  // same copy pattern as the forward kernel; the grad_out row rides in the group of chunk 0
+  constexpr int kCH = kBwdKC / 4, kRP = 32 / kCH;  // 16-byte chunks per row, rows per pass
+  const int r0 = lane / kCH, cc4 = 4 * (lane % kCH);
+  int64_t s_i = gw, it_i = 0;
+  int h_i = 0, stage_of = 0;
   auto issue = [&](int64_t q) {
     if (q < Q) {
-      const int64_t it = q / nch;
-      const int h = (int)(q - it * nch);
-      const int64_t s = gw + it * tw;
-      float* st = wbase + (q & 1) * stage_floats;
-      const float* dsrc = dense + s * D + h * kKC;
-      const float* ssrc = sparse + s * (int64_t)F * D + h * kKC;
-      for (int c = lane; c < n * (kKC / 4); c += 32) {
-        const int r = c >> 4, cc = c & 15;
-        cp_async_16(st + r * ld + 4 * cc, (r == 0 ? dsrc : ssrc + (int64_t)(r - 1) * D) + 4 * cc);
+      float* dst = wbase + stage_of * stage_floats + r0 * ld + cc4;
+      const float* src = sparse + s_i * (int64_t)F * D + (int64_t)(r0 - 1) * D + h_i * kBwdKC + cc4;
+      if (r0 == 0) cp_async_16(dst, dense + s_i * D + h_i * kBwdKC + cc4);
+      else if (r0 < n) cp_async_16(dst, src);
+      for (int r = r0 + kRP; r < n; r += kRP) {
+        dst += kRP * ld;
+        src += kRP * D;
+        cp_async_16(dst, src);
       }
-      if (h == 0) {
-        float* gd = gst + (it & 1) * gs_floats;
-        const float* gsrc = grad_out + s * grad_stride;
+      if (h_i == 0) {
+        float* gd = gst + (it_i & 1) * gs_floats;
+        const float* gsrc = grad_out + s_i * grad_stride;
         if (vec_g) {
           for (int c = lane; c < (gs_floats >> 2); c += 32) cp_async_16(gd + 4 * c, gsrc + 4 * c);
         } else {
           for (int c = lane; c < out_dim; c += 32) cp_async_4(gd + c, gsrc + c);
         }
       }
+      if (++h_i == nch) {
+        h_i = 0;
+        s_i += tw;
+        ++it_i;
+      }
     }
+    stage_of ^= 1;
     cp_async_commit();
   };
   issue(0);
@@ -410,13 +448,12 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
     rowoff[k][1] = min(8 * k + t + 4, n - 1) * ld + g;
   }
 
+  int64_t it = 0, s = gw;
+  int h = 0;
   for (int64_t q = 0; q < Q; ++q) {
     cp_async_wait<0>();
     __syncwarp();
     issue(q + 1);
-    const int64_t it = q / nch;
-    const int h = (int)(q - it * nch);
-    const int64_t s = gw + it * tw;
     const float* st = wbase + (q & 1) * stage_floats;
     const float* gcur = gst + (it & 1) * gs_floats;
     if (h == 0) {
@@ -440,7 +477,7 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
       __syncwarp();  // Gs is rewritten by the next sample only after every lane has its fragments
     }
 #pragma unroll 1
-    for (int nt = 0; nt < kKC / 8; ++nt) {
+    for (int nt = 0; nt < kBwdKC / 8; ++nt) {
       float acc[2][4];
 #pragma unroll
       for (int mi = 0; mi < 2; ++mi)
@@ -462,7 +499,7 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
           }
         }
       }
-      const int d = h * kKC + 8 * nt + 2 * t;
+      const int d = h * kBwdKC + 8 * nt + 2 * t;
 #pragma unroll
       for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
@@ -480,6 +517,11 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
           }
         }
     }
+    if (++h == nch) {
+      h = 0;
+      ++it;
+      s += tw;
+    }
   }
 }
 
@@ -493,15 +535,15 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   if (out_stride < D + (int64_t)(F + 1) * F / 2) return B200_EINVAL;
   const int n = F + 1;
-  if (n <= 32 && D % kKC == 0) {
+  if (n <= 32 && D % kFwdKC == 0) {
     const int out_dim = D + n * (n - 1) / 2;
-    const size_t msmem = sizeof(float) * kMmaWarps * (3 * (size_t)n * (kKC + 4) + ((out_dim + 3) & ~3));
+    const size_t msmem = sizeof(float) * kFwdMmaWarps * (2 * (size_t)n * (kFwdKC + 4) + ((out_dim + 3) & ~3));
     if (msmem <= 227 * 1024) {
       B200_CUDA_TRY(cudaFuncSetAttribute(interaction_forward_mma_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
-      int64_t mgrid = ceil_div(B, kMmaWarps);
+      int64_t mgrid = ceil_div(B, kFwdMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
-      interaction_forward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+      interaction_forward_mma_kernel<<<(unsigned)mgrid, kFwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
           dense, sparse, B, F, D, out, out_stride);
       B200_LAUNCH_CHECK();
       return B200_OK;
@@ -528,16 +570,16 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   if (grad_stride < D + (int64_t)(F + 1) * F / 2) return B200_EINVAL;
   const int n = F + 1;
-  if (n <= 32 && D % kKC == 0) {
+  if (n <= 32 && D % kBwdKC == 0) {
     const int n_tri = n * (n - 1) / 2;
-    const size_t per_warp = 2 * (size_t)n * (kKC + 8) + 32 * 36 + 2 * (size_t)((D + n_tri + 3) & ~3);
-    const size_t msmem = sizeof(float) * kMmaWarps * per_warp + ((sizeof(uint16_t) * n_tri + 15) & ~(size_t)15);
+    const size_t per_warp = 2 * (size_t)n * (kBwdKC + 8) + 32 * 36 + 2 * (size_t)((D + n_tri + 3) & ~3);
+    const size_t msmem = sizeof(float) * kBwdMmaWarps * per_warp + ((sizeof(uint16_t) * n_tri + 15) & ~(size_t)15);
     if (msmem <= 227 * 1024) {
       B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_mma_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
-      int64_t mgrid = ceil_div(B, kMmaWarps);
+      int64_t mgrid = ceil_div(B, kBwdMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
-      interaction_backward_mma_kernel<<<(unsigned)mgrid, kMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+      interaction_backward_mma_kernel<<<(unsigned)mgrid, kBwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
           dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
       B200_LAUNCH_CHECK();
       return B200_OK;

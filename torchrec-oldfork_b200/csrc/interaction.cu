@@ -196,8 +196,9 @@ interaction_backward_kernel(const float* __restrict__ dense, const float* __rest
 // ---------------------------------------------------------------------------------------------
 // 12 warps per SM: the kernels are latency-bound per warp (LDS -> split -> dependent MMAs), the
 // tensor pipe is ~1/3 busy at 8 warps (ncu), so residency is what shared memory is spent on.
-constexpr int kFwdMmaWarps = 12;
-constexpr int kFwdKC = 64;   // columns per pipeline stage, forward (2 stages per warp)
+constexpr int kFwdMmaWarps = 16;
+constexpr int kFwdKC = 32;
+constexpr int kFwdStages = 3;   // columns per pipeline stage, forward (2 stages per warp)
 constexpr int kBwdMmaWarps = 12;
 constexpr int kBwdKC = 32;   // backward stages are quarter samples
 
@@ -233,6 +234,7 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+template <bool FULL>  // FULL: 25 <= n <= 32, all six 16x8 tiles are live (no per-tile guards)
 __global__ void __launch_bounds__(kFwdMmaWarps * 32, 1)
 interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
                                int32_t B, int32_t F, int32_t D, float* __restrict__ out,
@@ -245,8 +247,8 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
   const int stage_floats = n * ld;
   const int out_dim = D + n * (n - 1) / 2;
   const int outs_floats = (out_dim + 3) & ~3;
-  float* wbase = smem + (size_t)warp * (2 * stage_floats + outs_floats);
-  float* outs = wbase + 2 * stage_floats;
+  float* wbase = smem + (size_t)warp * (kFwdStages * stage_floats + outs_floats);
+  float* outs = wbase + kFwdStages * stage_floats;
   const int nch = D / kFwdKC;
   const int ntiles = (n + 7) >> 3;  // live 8-row tiles
   const int64_t gw = (int64_t)blockIdx.x * kFwdMmaWarps + warp, tw = (int64_t)gridDim.x * kFwdMmaWarps;
@@ -258,7 +260,8 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 
   // copy pattern of a stage: lane l moves 16-byte chunk (l & 15) of rows (l >> 4) + 2k, k = 0, 1, ...
   // Row 0 is the dense vector, rows 1..F the sample's sparse block (contiguous, D floats apart).
-  const int r0 = lane >> 4, cc4 = 4 * (lane & 15);
+  constexpr int kCH = kFwdKC / 4, kRP = 32 / kCH;  // 16-byte chunks per row, rows per pass
+  const int r0 = lane / kCH, cc4 = 4 * (lane % kCH);
   int stage_of = 0;  // q % 2 of the next stage to issue
   int64_t s_i = gw;  // sample / column chunk of the next stage to issue
   int h_i = 0;
@@ -268,9 +271,9 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
       const float* src = sparse + s_i * (int64_t)F * D + (int64_t)(r0 - 1) * D + h_i * kFwdKC + cc4;
       if (r0 == 0) cp_async_16(dst, dense + s_i * D + h_i * kFwdKC + cc4);
       else if (r0 < n) cp_async_16(dst, src);
-      for (int r = r0 + 2; r < n; r += 2) {
-        dst += 2 * ld;
-        src += 2 * D;
+      for (int r = r0 + kRP; r < n; r += kRP) {
+        dst += kRP * ld;
+        src += kRP * D;
         cp_async_16(dst, src);
       }
       if (++h_i == nch) {
@@ -278,10 +281,11 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
         s_i += tw;
       }
     }
-    stage_of ^= 1;
+    stage_of = stage_of == kFwdStages - 1 ? 0 : stage_of + 1;
     cp_async_commit();  // always: keeps the group count uniform
   };
-  issue(0);
+#pragma unroll
+  for (int q = 0; q < kFwdStages - 1; ++q) issue(q);
 
   constexpr int kTM[6] = {0, 0, 0, 0, 1, 1};
   constexpr int kTN[6] = {0, 1, 2, 3, 2, 3};
@@ -304,19 +308,19 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
   int64_t it = 0;
   int h = 0;
   for (int64_t q = 0; q < Q; ++q) {
-    cp_async_wait<0>();
+    cp_async_wait<kFwdStages - 2>();
     __syncwarp();
-    issue(q + 1);
+    issue(q + kFwdStages - 1);
     const float* st = wbase + stage_cons * stage_floats;
-    stage_cons ^= 1;
+    stage_cons = stage_cons == kFwdStages - 1 ? 0 : stage_cons + 1;
     if (h == 0) {
 #pragma unroll
       for (int x = 0; x < 6; ++x)
 #pragma unroll
         for (int y = 0; y < 4; ++y) acc[x][y] = 0.f;
     }
-    outs[h * kFwdKC + lane] = st[lane];  // dense passthrough
-    outs[h * kFwdKC + 32 + lane] = st[32 + lane];
+#pragma unroll
+    for (int c = 0; c < kFwdKC; c += 32) outs[h * kFwdKC + c + lane] = st[c + lane];  // dense passthrough
 #pragma unroll 2
     for (int k0 = 0; k0 < kFwdKC; k0 += 8) {
       uint32_t bh[4][2], bl[4][2];
@@ -328,7 +332,7 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 #pragma unroll
       for (int x = 0; x < 6; ++x) {
         const int mi = kTM[x], nj = kTN[x];
-        if (nj < ntiles && 2 * mi < ntiles) {
+        if (FULL || (nj < ntiles && 2 * mi < ntiles)) {
           mma_tf32(acc[x], bl[2 * mi][0], bl[2 * mi + 1][0], bl[2 * mi][1], bl[2 * mi + 1][1], bh[nj][0], bh[nj][1]);
           mma_tf32(acc[x], bh[2 * mi][0], bh[2 * mi + 1][0], bh[2 * mi][1], bh[2 * mi + 1][1], bl[nj][0], bl[nj][1]);
           mma_tf32(acc[x], bh[2 * mi][0], bh[2 * mi + 1][0], bh[2 * mi][1], bh[2 * mi + 1][1], bh[nj][0], bh[nj][1]);
@@ -365,6 +369,7 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 // kept in registers), X streamed in 64-column stages with row stride 72 (B-fragment loads are
 // conflict free).  grad_out rows ride in the same cp.async groups (4-byte copies: rows are only
 // 4-byte aligned).  Results leave as 8-byte stores that fill whole 32-byte sectors.
+template <bool FULL>  // FULL: 25 <= n <= 32 (four k-steps, both row tiles live)
 __global__ void __launch_bounds__(kBwdMmaWarps * 32, 1)
 interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
                                 const float* __restrict__ grad_out, int64_t grad_stride, int32_t B,
@@ -485,13 +490,13 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
         for (int y = 0; y < 4; ++y) acc[mi][y] = 0.f;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        if (k < ksteps) {
+        if (FULL || k < ksteps) {
           uint32_t bh0, bl0, bh1, bl1;
           split_tf32(st[rowoff[k][0] + 8 * nt], bh0, bl0);
           split_tf32(st[rowoff[k][1] + 8 * nt], bh1, bl1);
 #pragma unroll
           for (int mi = 0; mi < 2; ++mi) {
-            if (16 * mi < n) {
+            if (FULL || 16 * mi < n) {
               mma_tf32(acc[mi], al[mi][k][0], al[mi][k][1], al[mi][k][2], al[mi][k][3], bh0, bh1);
               mma_tf32(acc[mi], ah[mi][k][0], ah[mi][k][1], ah[mi][k][2], ah[mi][k][3], bl0, bl1);
               mma_tf32(acc[mi], ah[mi][k][0], ah[mi][k][1], ah[mi][k][2], ah[mi][k][3], bh0, bh1);
@@ -537,13 +542,13 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
   const int n = F + 1;
   if (n <= 32 && D % kFwdKC == 0) {
     const int out_dim = D + n * (n - 1) / 2;
-    const size_t msmem = sizeof(float) * kFwdMmaWarps * (2 * (size_t)n * (kFwdKC + 4) + ((out_dim + 3) & ~3));
+    const size_t msmem = sizeof(float) * kFwdMmaWarps * (kFwdStages * (size_t)n * (kFwdKC + 4) + ((out_dim + 3) & ~3));
     if (msmem <= 227 * 1024) {
-      B200_CUDA_TRY(cudaFuncSetAttribute(interaction_forward_mma_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+      auto kern = n > 24 ? interaction_forward_mma_kernel<true> : interaction_forward_mma_kernel<false>;
+      B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
       int64_t mgrid = ceil_div(B, kFwdMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
-      interaction_forward_mma_kernel<<<(unsigned)mgrid, kFwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+      kern<<<(unsigned)mgrid, kFwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
           dense, sparse, B, F, D, out, out_stride);
       B200_LAUNCH_CHECK();
       return B200_OK;
@@ -575,11 +580,11 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
     const size_t per_warp = 2 * (size_t)n * (kBwdKC + 8) + 32 * 36 + 2 * (size_t)((D + n_tri + 3) & ~3);
     const size_t msmem = sizeof(float) * kBwdMmaWarps * per_warp + ((sizeof(uint16_t) * n_tri + 15) & ~(size_t)15);
     if (msmem <= 227 * 1024) {
-      B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_mma_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+      auto kern = n > 24 ? interaction_backward_mma_kernel<true> : interaction_backward_mma_kernel<false>;
+      B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
       int64_t mgrid = ceil_div(B, kBwdMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
-      interaction_backward_mma_kernel<<<(unsigned)mgrid, kBwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
+      kern<<<(unsigned)mgrid, kBwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
           dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
       B200_LAUNCH_CHECK();
       return B200_OK;

@@ -363,11 +363,17 @@ def run_ours(args) -> None:
     for name in ("tbe_sort", "interaction_forward", "interaction_backward"):
         if name in kern:
             kernels[name] = {"mean_ms_per_call": kern[name][1]}
+    traffic = None
+    try:  # DRAM bytes per launch from the committed ncu capture (only valid for the cfg2 shape at N=1)
+        if world == 1 and args.batch == 65536 and args.row_cap == 40_000_000:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["tbe_backward_tile_kernel"]
+    except Exception:
+        traffic = None
     if "tbe_backward" in kernels:
         k = kernels["tbe_backward"]
         roof = {"kernel": "tbe_backward_tile_kernel (+combine) — fused segment-reduce + rowwise Adagrad",
                 "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                "frac": k["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                "frac": k["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_step"] // calls_per_step}
     line = {
         "metric": "dlrm_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,

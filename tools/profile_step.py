@@ -1,0 +1,49 @@
+"""torch.profiler view of a few DLRM training steps under torchrun (diagnostic; not a bench).
+usage: torchrun --nproc-per-node N tools/profile_step.py"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "torchrec-oldfork_b200")]
+import bench  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    lr = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29577")
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    sys.argv = [sys.argv[0]]
+    args = bench.parse_args()
+    torch.backends.cuda.matmul.allow_tf32 = True
+    dmp, opt, rows = bench.build_gpu_model(args, rank, world, dev, dist.group.WORLD)
+    batches = [b.to(dev) for b in bench.make_batches(rows, args.batch, rank, 2)]
+
+    def step(b):
+        opt.zero_grad(set_to_none=True)
+        loss, _ = dmp(b)
+        loss.backward()
+        opt.step()
+
+    for i in range(5):
+        step(batches[i % 2])
+    torch.cuda.synchronize()
+    from torch.profiler import ProfilerActivity, profile
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        for i in range(4):
+            step(batches[i % 2])
+        torch.cuda.synchronize()
+    if rank == 0:
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=22, max_name_column_width=60))
+        print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=60))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

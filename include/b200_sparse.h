@@ -193,6 +193,44 @@ int b200_interaction_backward(const float* dense, const float* sparse, const flo
 int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsum /*[W+1]*/,
                           int32_t W, int32_t B_local, int forward, float scale, void* stream);
 
+/* ---------------------------------------------------------------- fused lookup + exchange (NVLink peer memory)
+ *
+ * One process per GPU; every rank maps its peers' buffers (CUDA IPC / symmetric memory) and passes
+ * device arrays of W base pointers.  These entry points replace lookup -> alltoall_pooled
+ * (comm_ops.py:203-560) / reduce_scatter_pooled (:382-890) and their backward collectives with
+ * direct peer stores / loads inside the lookup kernels; the caller brackets them with cross-rank
+ * barriers (all ranks' stores done before anyone reads; all reads done before buffers are reused). */
+
+/* b200_tbe_forward whose pooled row of global sample b is written to
+ * dst_bases[b / B_dst] + (b % B_dst) * dst_pitch + dst_col[t]  (elements of the output dtype). */
+int b200_tbe_forward_peer(const void* weights, int weight_dtype, const int64_t* weights_offsets,
+                          const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
+                          int32_t max_D, int32_t all_D_mult8, const void* indices,
+                          const void* offsets, int index_dtype, const float* per_sample_weights,
+                          int pooling_mode, void* const* dst_bases /*device [n_dst]*/,
+                          int32_t n_dst, int32_t B_dst, int64_t dst_pitch,
+                          const int32_t* dst_col /*device [T]*/, int output_dtype, void* stream);
+
+/* b200_tbe_backward whose gradient row of global sample b is read from
+ * grad_bases[b / B_src] + (b % B_src) * grad_stride + src_col[t], scaled by grad_scale
+ * (the 1/W of comm_ops.py:527-528, 883). */
+int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, int32_t n_src,
+                           int32_t B_src, int64_t grad_stride, const int32_t* src_col /*device [T]*/,
+                           float grad_scale, const void* sorted_keys,
+                           const int32_t* sorted_payload, const int32_t* bag_of_pos, int64_t N,
+                           int key_bits, void* weights, int weight_dtype,
+                           const int64_t* weights_offsets, const int32_t* D_offsets,
+                           const int64_t* hash_size_cumsum, int32_t T, int32_t B, int32_t max_D,
+                           int32_t all_D_mult8, const void* offsets, int index_dtype,
+                           const float* per_sample_weights, int pooling_mode, int optimizer,
+                           float* momentum1, const int64_t* momentum1_offsets,
+                           float learning_rate, float eps, void* partial_scratch, void* stream);
+
+/* Row-wise sharding: out[b, out_col : out_col + Dw] = sum_r stage[r][b][:] (rank order), stage
+ * [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer. */
+int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_local, int32_t Dw, float* out,
+                           int64_t out_pitch, int32_t out_col, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

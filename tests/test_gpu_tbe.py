@@ -205,3 +205,92 @@ def test_interaction_fwd_bwd(ops, B, F, D):
     gd, gs = ops.interaction_backward(dev(dense), dev(sparse), dev(go))
     np.testing.assert_allclose(gd.cpu().numpy(), egd, rtol=1e-5, atol=1e-4)
     np.testing.assert_allclose(gs.cpu().numpy(), egs, rtol=1e-5, atol=1e-4)
+
+
+# ---------------------------------------------------------------------------------------------
+# fused lookup + exchange entry points, exercised on ONE GPU with local buffers standing in for the
+# peers' (the multi-GPU run is tests/dist_parity_worker.py)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", [0, 3, 4])
+@pytest.mark.parametrize("n_dst", [1, 2, 4])
+def test_forward_peer_scatter(ops, case, n_dst):
+    rows, dims, B, L = CASES[case]
+    B = (B + n_dst - 1) // n_dst * n_dst
+    rng = np.random.default_rng(case + 50)
+    w, wo, Do, hsc = build_tables(rng, rows, dims, "fp32")
+    _, offsets, indices = make_jagged(rng, len(rows), B, L, rows, idx_dtype=np.int64)
+    exp = R.tbe_forward(w_to_np(w), wo, Do, indices, offsets)
+    total_D = int(Do[-1])
+    # destination layout: features in reversed order, 8 spare columns in front, pitch padded
+    col = np.zeros(len(dims), dtype=np.int32)
+    c = 8
+    for t in reversed(range(len(dims))):
+        col[t] = c
+        c += dims[t]
+    pitch = c + 4
+    B_dst = B // n_dst
+    bufs = [torch.full((B_dst, pitch), -7.0, device="cuda") for _ in range(n_dst)]
+    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
+    ops.tbe_forward_peer(w.cuda(), dev(wo), dev(Do), total_D, max(dims), all(d % 8 == 0 for d in dims),
+                         dev(indices), dev(offsets), None, 0, bases, B_dst, pitch, dev(col))
+    got = torch.cat(bufs, 0).cpu().numpy()
+    for t, d in enumerate(dims):
+        np.testing.assert_allclose(got[:, col[t]:col[t] + d], exp[:, Do[t]:Do[t] + d], rtol=1e-5, atol=1e-5)
+    assert np.all(got[:, :8] == -7.0) and np.all(got[:, c:] == -7.0)  # nothing outside the feature columns
+
+
+@pytest.mark.parametrize("case", [0, 1, 4])
+@pytest.mark.parametrize("opt", ["sgd", "rowwise_adagrad"])
+def test_backward_peer_gather(ops, case, opt):
+    rows, dims, B, L = BWD_CASES[case]
+    n_src = 2
+    B = (B + n_src - 1) // n_src * n_src
+    rng = np.random.default_rng(case + 80)
+    T = len(rows)
+    w, wo, Do, hsc = build_tables(rng, rows, dims, "fp32")
+    _, offsets, indices = make_jagged(rng, T, B, L, rows, idx_dtype=np.int64)
+    total_D = int(Do[-1])
+    grad = rng.standard_normal((B, total_D)).astype(np.float32)
+    mom = rng.random(int(hsc[-1])).astype(np.float32)
+    mo = hsc[:-1].copy()
+    lr, eps, gscale = 0.05, 1e-8, 0.5
+    w_ref, mom_ref = w_to_np(w).copy(), mom.copy()
+    R.tbe_backward(grad * np.float32(gscale), w_ref, wo, Do, hsc, indices, offsets, opt, lr, eps, mom_ref, mo)
+    # the gradient lives in n_src buffers with a permuted column layout and a padded pitch
+    col = np.zeros(T, dtype=np.int32)
+    c = 4
+    for t in reversed(range(T)):
+        col[t] = c
+        c += dims[t]
+    pitch = c + 12
+    B_src = B // n_src
+    bufs = []
+    for r in range(n_src):
+        g = np.zeros((B_src, pitch), dtype=np.float32)
+        for t in range(T):
+            g[:, col[t]:col[t] + dims[t]] = grad[r * B_src:(r + 1) * B_src, Do[t]:Do[t] + dims[t]]
+        bufs.append(dev(g))
+    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
+    wg, momg = w.cuda(), dev(mom)
+    bits = int(np.log2(max(int(hsc[-1]), 1)) + 1)
+    d_off = dev(offsets)
+    srt = ops.tbe_sort_indices(dev(indices), d_off, dev(hsc), bits, B, False)
+    ops.tbe_backward_peer(bases, B_src, pitch, dev(col), gscale, srt, wg, dev(wo), dev(Do), dev(hsc), B, max(dims),
+                          all(d % 8 == 0 for d in dims), d_off, None, 0, 0 if opt == "sgd" else 1,
+                          momg if opt == "rowwise_adagrad" else None,
+                          dev(mo) if opt == "rowwise_adagrad" else None, lr, eps)
+    np.testing.assert_allclose(w_to_np(wg), w_ref, rtol=1e-5, atol=5e-4)
+    if opt == "rowwise_adagrad":
+        np.testing.assert_allclose(momg.cpu().numpy(), mom_ref, rtol=1e-5, atol=1e-5)
+
+
+def test_peer_stage_reduce(ops):
+    rng = np.random.default_rng(5)
+    W, B, Dw, pitch, col = 3, 37, 24, 64, 16
+    stage = rng.standard_normal((W, B, Dw)).astype(np.float32)
+    out = torch.full((B, pitch), 9.0, device="cuda")
+    ops.peer_stage_reduce(dev(stage), W, B, Dw, out, col)
+    exp = stage[0] + stage[1] + stage[2]
+    got = out.cpu().numpy()
+    np.testing.assert_array_equal(got[:, col:col + Dw], exp)
+    assert np.all(got[:, :col] == 9.0) and np.all(got[:, col + Dw:] == 9.0)

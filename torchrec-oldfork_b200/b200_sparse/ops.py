@@ -404,6 +404,66 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
     return out
 
 
+# ------------------------------------------------------------------------ fused lookup + exchange
+def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
+                     total_D: int, max_D: int, all_D_mult8: bool, indices: torch.Tensor, offsets: torch.Tensor,
+                     per_sample_weights: Optional[torch.Tensor], pooling_mode: int, dst_bases: torch.Tensor,
+                     B_dst: int, dst_pitch: int, dst_col: torch.Tensor) -> None:
+    """Pooled lookup whose rows go to dst_bases[b // B_dst] (int64 device array of fp32 buffer
+    addresses, usually NVLink peer mappings) at row b % B_dst, column dst_col[t]."""
+    dev = _need_cuda(weights, weights_offsets, D_offsets, indices, offsets, per_sample_weights, dst_bases, dst_col)
+    if indices.dtype != offsets.dtype:
+        raise TypeError("indices and offsets must share a dtype")
+    if dst_bases.dtype != torch.int64 or dst_col.dtype != torch.int32:
+        raise TypeError("dst_bases must be int64 addresses and dst_col int32 columns")
+    idt = _idx_dt(indices, "indices")
+    T = D_offsets.numel() - 1
+    B = (offsets.numel() - 1) // T
+    if per_sample_weights is not None:
+        per_sample_weights = per_sample_weights.float().contiguous()
+    with torch.cuda.device(dev), _timed("tbe_forward", dev, 1):
+        check(lib.b200_tbe_forward_peer(_p(weights), _DT[weights.dtype], _p(weights_offsets), _p(D_offsets), T, B,
+                                        total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
+                                        _p(offsets.contiguous()), idt, _p(per_sample_weights), int(pooling_mode),
+                                        _p(dst_bases), dst_bases.numel(), int(B_dst), int(dst_pitch), _p(dst_col),
+                                        _DT[torch.float32], _stream(dev)), "b200_tbe_forward_peer")
+
+
+def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, src_col: torch.Tensor,
+                      grad_scale: float, srt: SortedIndices, weights: torch.Tensor, weights_offsets: torch.Tensor,
+                      D_offsets: torch.Tensor, hash_size_cumsum: torch.Tensor, B: int, max_D: int,
+                      all_D_mult8: bool, offsets: torch.Tensor, per_sample_weights: Optional[torch.Tensor],
+                      pooling_mode: int, optimizer: int, momentum1: Optional[torch.Tensor],
+                      momentum1_offsets: Optional[torch.Tensor], learning_rate: float, eps: float) -> None:
+    """Fused backward + optimizer reading the gradient row of sample b from grad_bases[b // B_src]."""
+    dev = _need_cuda(grad_bases, src_col, weights, weights_offsets, D_offsets, hash_size_cumsum, offsets)
+    if grad_bases.dtype != torch.int64 or src_col.dtype != torch.int32:
+        raise TypeError("grad_bases must be int64 addresses and src_col int32 columns")
+    T = D_offsets.numel() - 1
+    scratch_bytes = lib.b200_tbe_backward_scratch_bytes(srt.N, max_D)
+    scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
+    if per_sample_weights is not None:
+        per_sample_weights = per_sample_weights.float().contiguous()
+    with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):
+        check(lib.b200_tbe_backward_peer(_p(grad_bases), grad_bases.numel(), int(B_src), int(grad_stride),
+                                         _p(src_col), float(grad_scale), _p(srt.keys), _p(srt.payload),
+                                         _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights), _DT[weights.dtype],
+                                         _p(weights_offsets), _p(D_offsets), _p(hash_size_cumsum), T, B, max_D,
+                                         int(all_D_mult8), _p(offsets), _idx_dt(offsets, "offsets"),
+                                         _p(per_sample_weights), int(pooling_mode), int(optimizer), _p(momentum1),
+                                         _p(momentum1_offsets), float(learning_rate), float(eps), _p(scratch),
+                                         _stream(dev)), "b200_tbe_backward_peer")
+
+
+def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: torch.Tensor, out_col: int) -> None:
+    """out[:, out_col:out_col+Dw] = sum over the W rank slots of stage ([W, B_local, Dw] fp32)."""
+    dev = _need_cuda(stage, out)
+    with torch.cuda.device(dev):
+        KernelProfile.launches += 1
+        check(lib.b200_peer_stage_reduce(_p(stage), int(W), int(B_local), int(Dw), _p(out), out.stride(0),
+                                         int(out_col), _stream(dev)), "b200_peer_stage_reduce")
+
+
 # ------------------------------------------------------------------------ dot interaction
 def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
     """[B, D + (F+1)F/2].  pad_rows=True returns a view of a buffer whose rows sit at a 16-byte

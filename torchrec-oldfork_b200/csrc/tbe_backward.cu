@@ -292,6 +292,13 @@ struct BwdArgs {
   float* momentum1;
   const int64_t* momentum1_offsets;
   float lr, eps;
+  // Peer gather (sharded training): the gradient row of global sample b lives on rank b / B_src at
+  // grad_bases[rank] + (b % B_src) * grad_stride + src_col[t].  With NVLink peer mappings this IS
+  // the backward all-to-all (table-wise) / all-gather (row-wise).  nullptr => local `grad`.
+  const float* const* grad_bases;
+  const int32_t* src_col;
+  int32_t B_src;
+  float grad_scale;  // 1/W of the sharded path (GRADIENT_DIVISION), 1 otherwise
   float* part_rows;  // [numCTAs][2][ROW]  (0 = leading partial H, 1 = trailing partial T)
   BwdMeta* meta;     // [numCTAs]
   int32_t num_ctas;
@@ -362,9 +369,18 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
       scale = 1.0f / (float)L;
     }
     if (a.psw) scale *= a.psw[pos];
+    scale *= a.grad_scale;
   }
-  const bool scaled = a.mean || a.psw != nullptr;
-  const uint32_t goff4 = (uint32_t)(((int64_t)b * a.grad_stride + Dbeg) >> 2);
+  const bool scaled = a.mean || a.psw != nullptr || a.grad_scale != 1.0f;
+  const float* gptr = a.grad;
+  if (valid) {
+    if (a.grad_bases) {
+      const int r = b / a.B_src;
+      gptr = a.grad_bases[r] + (int64_t)(b - r * a.B_src) * a.grad_stride + a.src_col[t];
+    } else {
+      gptr = a.grad + (int64_t)b * a.grad_stride + Dbeg;
+    }
+  }
 
   float acc[NV][EPV];
 #pragma unroll
@@ -391,7 +407,7 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
     unsigned long long* const mg = s_ptr[warp][0];
     unsigned long long* const mw = s_ptr[warp][1];
     unsigned long long* const mm = s_ptr[warp][2];
-    mg[lane] = (unsigned long long)(a.grad + ((int64_t)goff4 << 2));
+    mg[lane] = (unsigned long long)gptr;
     mw[lane] = (unsigned long long)(weights + woff);
     if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) mm[lane] = (unsigned long long)(a.momentum1 + moff);
     s_scale[warp][lane] = scale;
@@ -511,9 +527,9 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
   auto issue = [&](int p) {
     if (p < nvalid) {
       unsigned char* st = ring + (p % kStages) * kStageBytes;
-      const uint32_t g4 = __shfl_sync(kFull, goff4, p);
+      const float* grow = reinterpret_cast<const float*>(
+          __shfl_sync(kFull, (unsigned long long)gptr, p));
       const int Dp = __shfl_sync(kFull, Dt, p);
-      const float* grow = a.grad + ((int64_t)g4 << 2);
       const bool fin = (Cm >> p) & 1u;
       int64_t wo = 0, mo = 0;
       if (fin) {  // warp-uniform
@@ -804,7 +820,7 @@ extern "C" size_t b200_tbe_backward_scratch_bytes(int64_t N, int32_t max_D) {
          align256((size_t)ctas * sizeof(BwdMeta)) + 256;
 }
 
-extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
+static int tbe_backward_impl(const float* grad_output, int64_t grad_stride,
                                  const void* sorted_keys, const int32_t* sorted_payload,
                                  const int32_t* bag_of_pos, int64_t N, int key_bits, void* weights,
                                  int weight_dtype, const int64_t* weights_offsets,
@@ -814,11 +830,11 @@ extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
                                  const float* per_sample_weights, int pooling_mode, int optimizer,
                                  float* momentum1, const int64_t* momentum1_offsets,
                                  float learning_rate, float eps, void* partial_scratch,
-                                 void* stream) {
+                                 const float* const* grad_bases, int32_t B_src,
+                                 const int32_t* src_col, float grad_scale, void* stream) {
   using namespace b200;
   if (N == 0 || T == 0 || B == 0) return B200_OK;
   if ((grad_stride & 3) != 0) return B200_EINVAL;
-  if (((int64_t)B * grad_stride) >> 34) return B200_EINVAL;  // 32-bit float4 offsets
   if (per_sample_weights && !bag_of_pos) return B200_EINVAL;
   if (optimizer == B200_OPT_ROWWISE_ADAGRAD && (!momentum1 || !momentum1_offsets)) return B200_EINVAL;
   cudaStream_t s = (cudaStream_t)stream;
@@ -847,6 +863,10 @@ extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
   ARGS.momentum1_offsets = momentum1_offsets;              \
   ARGS.lr = learning_rate;                                 \
   ARGS.eps = eps;                                          \
+  ARGS.grad_bases = grad_bases;                            \
+  ARGS.src_col = src_col;                                  \
+  ARGS.B_src = B_src;                                      \
+  ARGS.grad_scale = grad_scale;                            \
   ARGS.part_rows = part_rows;                              \
   ARGS.meta = meta;                                        \
   ARGS.num_ctas = (int32_t)ctas;
@@ -861,4 +881,46 @@ extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
   B200_FILL(a);
   return dispatch_w<uint32_t>(a, weight_dtype, all_D_mult8 != 0, optimizer, max_D, s);
 #undef B200_FILL
+}
+
+extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
+                                 const void* sorted_keys, const int32_t* sorted_payload,
+                                 const int32_t* bag_of_pos, int64_t N, int key_bits, void* weights,
+                                 int weight_dtype, const int64_t* weights_offsets,
+                                 const int32_t* D_offsets, const int64_t* hash_size_cumsum,
+                                 int32_t T, int32_t B, int32_t max_D, int32_t all_D_mult8,
+                                 const void* offsets, int index_dtype,
+                                 const float* per_sample_weights, int pooling_mode, int optimizer,
+                                 float* momentum1, const int64_t* momentum1_offsets,
+                                 float learning_rate, float eps, void* partial_scratch,
+                                 void* stream) {
+  if (!grad_output) return B200_EINVAL;
+  return tbe_backward_impl(grad_output, grad_stride, sorted_keys, sorted_payload, bag_of_pos, N,
+                           key_bits, weights, weight_dtype, weights_offsets, D_offsets,
+                           hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
+                           per_sample_weights, pooling_mode, optimizer, momentum1,
+                           momentum1_offsets, learning_rate, eps, partial_scratch, nullptr, 0,
+                           nullptr, 1.0f, stream);
+}
+
+extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_src, int32_t B_src,
+                                      int64_t grad_stride, const int32_t* src_col,
+                                      float grad_scale, const void* sorted_keys,
+                                      const int32_t* sorted_payload, const int32_t* bag_of_pos,
+                                      int64_t N, int key_bits, void* weights, int weight_dtype,
+                                      const int64_t* weights_offsets, const int32_t* D_offsets,
+                                      const int64_t* hash_size_cumsum, int32_t T, int32_t B,
+                                      int32_t max_D, int32_t all_D_mult8, const void* offsets,
+                                      int index_dtype, const float* per_sample_weights,
+                                      int pooling_mode, int optimizer, float* momentum1,
+                                      const int64_t* momentum1_offsets, float learning_rate,
+                                      float eps, void* partial_scratch, void* stream) {
+  if (!grad_bases || !src_col || n_src <= 0 || B_src <= 0 || (int64_t)n_src * B_src < B)
+    return B200_EINVAL;
+  return tbe_backward_impl(nullptr, grad_stride, sorted_keys, sorted_payload, bag_of_pos, N,
+                           key_bits, weights, weight_dtype, weights_offsets, D_offsets,
+                           hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
+                           per_sample_weights, pooling_mode, optimizer, momentum1,
+                           momentum1_offsets, learning_rate, eps, partial_scratch, grad_bases,
+                           B_src, src_col, grad_scale, stream);
 }

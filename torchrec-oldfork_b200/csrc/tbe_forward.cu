@@ -68,13 +68,25 @@ __device__ __forceinline__ void fwd_load_slot(const unsigned char* p, float (&f)
   }
 }
 
-template <typename W, typename O, int EPV, int NV>
+// Destination of the pooled rows when they are written straight into (peer) output buffers:
+// bag b goes to bases[b / B_dst] at row b % B_dst, column col[t], rows `pitch` elements apart.
+// With NVLink peer mappings in `bases` this IS the output all-to-all of table-wise sharding (and the
+// scatter half of row-wise sharding's reduce-scatter): no pooled [B_global, D_local] tensor, no NCCL
+// pass and no re-layout copy exist.
+struct FwdPeerDst {
+  void* const* bases;
+  const int32_t* col;
+  int64_t pitch;
+  int32_t B_dst;
+};
+
+template <typename W, typename O, int EPV, int NV, bool PEER>
 __global__ void __launch_bounds__(kFwdThreads)
 tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ weights_offsets,
                    const int32_t* __restrict__ D_offsets, int32_t T, int32_t B, int32_t total_D,
                    int32_t tiles_per_table, const void* __restrict__ indices,
                    const void* __restrict__ offsets, bool idx64,
-                   const float* __restrict__ psw, bool mean, O* __restrict__ out) {
+                   const float* __restrict__ psw, bool mean, O* __restrict__ out, FwdPeerDst peer) {
   constexpr int kStages = FwdRing<NV>::kStages;
   constexpr int kStageBytes = FwdRing<NV>::kStageBytes;
   constexpr int kAhead = kStages - 1;
@@ -102,7 +114,17 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
   unsigned remaining = __ballot_sync(kFull, in_tile && rel_end > rel_start);
   const unsigned empty = __ballot_sync(kFull, in_tile && rel_end <= rel_start);
 
-  O* __restrict__ out_tile = out + (int64_t)b0 * total_D + D_begin + EPV * lane;
+  O* __restrict__ out_tile = PEER ? nullptr : out + (int64_t)b0 * total_D + D_begin + EPV * lane;
+  const int peer_col = PEER ? peer.col[t] + EPV * lane : 0;
+  auto row_ptr = [&](int bag) -> O* {
+    if constexpr (PEER) {
+      const int b = b0 + bag;
+      const int r = b / peer.B_dst;
+      return reinterpret_cast<O*>(peer.bases[r]) + (int64_t)(b - r * peer.B_dst) * peer.pitch + peer_col;
+    } else {
+      return out_tile + (int64_t)bag * total_D;
+    }
+  };
   bool act[NV];
 #pragma unroll
   for (int v = 0; v < NV; ++v) act[v] = EPV * (lane + 32 * v) < D;
@@ -114,10 +136,15 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
 #pragma unroll
     for (int e = 0; e < EPV; ++e) z[e] = 0.f;
 #pragma unroll
+    O* zr = row_ptr(j);
+#pragma unroll
     for (int v = 0; v < NV; ++v)
-      if (act[v]) store_vec<O, EPV, true>(out_tile + (int64_t)j * total_D + EPV * 32 * v, z);
+      if (act[v]) store_vec<O, EPV, true>(zr + EPV * 32 * v, z);
   }
-  if (len <= 0) return;
+  if (len <= 0) {
+    if constexpr (PEER) __threadfence_system();
+    return;
+  }
 
   unsigned char* const wsm = fwd_smem + (size_t)warp * FwdRing<NV>::kWarpBytes;
   unsigned char* const lring = wsm + lane * 16;
@@ -207,13 +234,14 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
             }
           if (p + 1 == cur_end) {  // bag boundary: write the pooled row once
             const float scale = mean ? 1.0f / (float)(cur_end - prev_end) : 1.0f;
+            O* orow = row_ptr(cur_bag);
 #pragma unroll
             for (int v = 0; v < NV; ++v) {
               if (mean) {
 #pragma unroll
                 for (int e = 0; e < EPV; ++e) acc[v][e] *= scale;
               }
-              if (act[v]) store_vec<O, EPV, true>(out_tile + (int64_t)cur_bag * total_D + EPV * 32 * v, acc[v]);
+              if (act[v]) store_vec<O, EPV, true>(orow + EPV * 32 * v, acc[v]);
 #pragma unroll
               for (int e = 0; e < EPV; ++e) acc[v][e] = 0.f;
             }
@@ -227,13 +255,15 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
     }
   }
   fwd_wait<0>();
+  if constexpr (PEER) __threadfence_system();  // peer stores visible before the cross-rank barrier
 }
 
 template <typename W, typename O, int EPV>
 static int launch_forward_nv(const void* weights, const int64_t* weights_offsets,
                              const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
                              int32_t max_D, const void* indices, const void* offsets, bool idx64,
-                             const float* psw, bool mean, void* output, cudaStream_t s) {
+                             const float* psw, bool mean, void* output, const FwdPeerDst* peer,
+                             cudaStream_t s) {
   const int tiles_per_table = (B + 31) / 32;
   const int64_t tiles = (int64_t)T * tiles_per_table;
   const int64_t grid = ceil_div(tiles, kFwdThreads / 32);
@@ -241,9 +271,16 @@ static int launch_forward_nv(const void* weights, const int64_t* weights_offsets
   if (grid > 0x7fffffffLL) return B200_EINVAL;
   const int vecs = (int)ceil_div(max_D, EPV * 32);
 #define B200_FWD_LAUNCH(NV)                                                                     \
-  tbe_forward_kernel<W, O, EPV, NV><<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>( \
-      (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table, indices,    \
-      offsets, idx64, psw, mean, (O*)output)
+  if (peer)                                                                                     \
+    tbe_forward_kernel<W, O, EPV, NV, true>                                                      \
+        <<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>(               \
+            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table,       \
+            indices, offsets, idx64, psw, mean, nullptr, *peer);                                 \
+  else                                                                                          \
+    tbe_forward_kernel<W, O, EPV, NV, false>                                                     \
+        <<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>(               \
+            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table,       \
+            indices, offsets, idx64, psw, mean, (O*)output, FwdPeerDst{})
   if (vecs <= 1)
     B200_FWD_LAUNCH(1);
   else if (vecs <= 2)
@@ -263,14 +300,15 @@ template <typename W, int EPV>
 static int launch_forward_out(int output_dtype, const void* weights, const int64_t* wo,
                               const int32_t* Do, int32_t T, int32_t B, int32_t total_D,
                               int32_t max_D, const void* indices, const void* offsets, bool idx64,
-                              const float* psw, bool mean, void* output, cudaStream_t s) {
+                              const float* psw, bool mean, void* output, const FwdPeerDst* peer,
+                              cudaStream_t s) {
   switch (output_dtype) {
     case B200_F32:
       return launch_forward_nv<W, float, EPV>(weights, wo, Do, T, B, total_D, max_D, indices,
-                                              offsets, idx64, psw, mean, output, s);
+                                              offsets, idx64, psw, mean, output, peer, s);
     case B200_F16:
       return launch_forward_nv<W, __half, EPV>(weights, wo, Do, T, B, total_D, max_D, indices,
-                                               offsets, idx64, psw, mean, output, s);
+                                               offsets, idx64, psw, mean, output, peer, s);
     default:
       return B200_EUNSUPPORTED;
   }
@@ -278,12 +316,13 @@ static int launch_forward_out(int output_dtype, const void* weights, const int64
 
 }  // namespace b200
 
-extern "C" int b200_tbe_forward(const void* weights, int weight_dtype,
+static int tbe_forward_impl(const void* weights, int weight_dtype,
                                 const int64_t* weights_offsets, const int32_t* D_offsets,
                                 int32_t T, int32_t B, int32_t total_D, int32_t max_D,
                                 int32_t all_D_mult8, const void* indices, const void* offsets,
                                 int index_dtype, const float* per_sample_weights,
-                                int pooling_mode, void* output, int output_dtype, void* stream) {
+                                int pooling_mode, void* output, int output_dtype,
+                            const b200::FwdPeerDst* peer, void* stream) {
   using namespace b200;
   if (T < 0 || B < 0 || total_D < 0 || (total_D % 4) != 0) return B200_EINVAL;
   if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
@@ -295,26 +334,54 @@ extern "C" int b200_tbe_forward(const void* weights, int weight_dtype,
     case B200_F32:
       return launch_forward_out<float, 4>(output_dtype, weights, weights_offsets, D_offsets, T, B,
                                           total_D, max_D, indices, offsets, idx64,
-                                          per_sample_weights, mean, output, s);
+                                          per_sample_weights, mean, output, peer, s);
     case B200_F16:
       if (all_D_mult8)
         return launch_forward_out<__half, 8>(output_dtype, weights, weights_offsets, D_offsets, T,
                                              B, total_D, max_D, indices, offsets, idx64,
-                                             per_sample_weights, mean, output, s);
+                                             per_sample_weights, mean, output, peer, s);
       return launch_forward_out<__half, 4>(output_dtype, weights, weights_offsets, D_offsets, T, B,
                                            total_D, max_D, indices, offsets, idx64,
-                                           per_sample_weights, mean, output, s);
+                                           per_sample_weights, mean, output, peer, s);
     case B200_BF16:
       if (all_D_mult8)
         return launch_forward_out<__nv_bfloat16, 8>(output_dtype, weights, weights_offsets,
                                                     D_offsets, T, B, total_D, max_D, indices,
                                                     offsets, idx64, per_sample_weights, mean,
-                                                    output, s);
+                                                    output, peer, s);
       return launch_forward_out<__nv_bfloat16, 4>(output_dtype, weights, weights_offsets,
                                                   D_offsets, T, B, total_D, max_D, indices,
                                                   offsets, idx64, per_sample_weights, mean, output,
-                                                  s);
+                                                  peer, s);
     default:
       return B200_EUNSUPPORTED;
   }
+}
+
+extern "C" int b200_tbe_forward(const void* weights, int weight_dtype,
+                                const int64_t* weights_offsets, const int32_t* D_offsets,
+                                int32_t T, int32_t B, int32_t total_D, int32_t max_D,
+                                int32_t all_D_mult8, const void* indices, const void* offsets,
+                                int index_dtype, const float* per_sample_weights,
+                                int pooling_mode, void* output, int output_dtype, void* stream) {
+  return tbe_forward_impl(weights, weight_dtype, weights_offsets, D_offsets, T, B, total_D, max_D,
+                          all_D_mult8, indices, offsets, index_dtype, per_sample_weights,
+                          pooling_mode, output, output_dtype, nullptr, stream);
+}
+
+extern "C" int b200_tbe_forward_peer(const void* weights, int weight_dtype,
+                                     const int64_t* weights_offsets, const int32_t* D_offsets,
+                                     int32_t T, int32_t B, int32_t total_D, int32_t max_D,
+                                     int32_t all_D_mult8, const void* indices, const void* offsets,
+                                     int index_dtype, const float* per_sample_weights,
+                                     int pooling_mode, void* const* dst_bases, int32_t n_dst,
+                                     int32_t B_dst, int64_t dst_pitch, const int32_t* dst_col,
+                                     int output_dtype, void* stream) {
+  if (!dst_bases || !dst_col || n_dst <= 0 || B_dst <= 0 || (int64_t)n_dst * B_dst < B ||
+      (dst_pitch & 3))
+    return B200_EINVAL;
+  b200::FwdPeerDst peer{dst_bases, dst_col, dst_pitch, B_dst};
+  return tbe_forward_impl(weights, weight_dtype, weights_offsets, D_offsets, T, B, total_D, max_D,
+                          all_D_mult8, indices, offsets, index_dtype, per_sample_weights,
+                          pooling_mode, nullptr, output_dtype, &peer, stream);
 }

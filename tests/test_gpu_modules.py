@@ -172,17 +172,21 @@ def test_quantized_ebc():
 
 
 @pytest.mark.parametrize("world", [2])
-def test_multi_gpu_sharded_vs_unsharded(world):
-    """TW + RW over `world` GPUs (torchrun, NCCL); skipped on a single-GPU box."""
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
+def test_multi_gpu_sharded_vs_unsharded(world, exchange):
+    """TW + RW over `world` GPUs (torchrun): the fused peer-memory exchange and the NCCL collectives both
+    reproduce the unsharded model; skipped on a single-GPU box."""
     import subprocess
     import sys
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, B200_PEER_DIST="1" if exchange == "peer" else "0")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-                        "--master-addr", "127.0.0.1", "--master-port", "29611",
-                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "DIST PARITY OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+                        "--master-addr", "127.0.0.1", "--master-port", "29611" if exchange == "peer" else "29621",
+                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600,
+                       env=env)
+    assert r.returncode == 0 and f"exchange={exchange}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
 def test_interaction_row_pitch_and_pitched_linear():

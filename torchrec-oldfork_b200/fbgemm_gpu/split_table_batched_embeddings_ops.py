@@ -201,13 +201,19 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
     # ------------------------------------------------------------------ forward
     def forward(self, indices: Tensor, offsets: Tensor, per_sample_weights: Optional[Tensor] = None,
                 feature_requires_grad: Optional[Tensor] = None) -> Tensor:
+        indices, offsets = self.prepare_indices(indices, offsets)
+        return _tbe_autograd.lookup(self, indices, offsets, per_sample_weights, feature_requires_grad)
+
+    def prepare_indices(self, indices: Tensor, offsets: Tensor) -> Tuple[Tensor, Tensor]:
+        """Dtype normalisation + bounds check (reference :585-595) shared by forward() and the fused
+        lookup+exchange path of torchrec.distributed.peer_dist."""
         if indices.dtype != offsets.dtype or indices.dtype not in (torch.int32, torch.int64):
             indices, offsets = indices.long(), offsets.long()
         if self.bounds_check_mode_int != BoundsCheckMode.NONE.value:
             torch.ops.fbgemm.bounds_check_indices(self.rows_per_table, indices, offsets,
                                                   self.bounds_check_mode_int, self.bounds_check_warning)
         self.step += 1
-        return _tbe_autograd.lookup(self, indices, offsets, per_sample_weights, feature_requires_grad)
+        return indices, offsets
 
     def prefetch(self, indices: Tensor, offsets: Tensor) -> None:
         """No UVM cache in this build: nothing to prefetch (reference :736-743 early-returns too)."""

@@ -22,7 +22,7 @@ from torchrec.distributed.embedding_types import (
 from torchrec.distributed.sharding.rw_sharding import RwPooledEmbeddingSharding
 from torchrec.distributed.sharding.tw_sharding import TwPooledEmbeddingSharding
 from torchrec.distributed.types import (
-    Awaitable, LazyAwaitable, ModuleSharder, ParameterSharding, ShardedModule, ShardedModuleContext,
+    Awaitable, LazyAwaitable, ModuleSharder, NoWait, ParameterSharding, ShardedModule, ShardedModuleContext,
     ShardingEnv, ShardingType)
 from torchrec.modules.embedding_configs import EmbeddingTableConfig
 from torchrec.modules.embedding_modules import EmbeddingBagCollection, EmbeddingBagCollectionInterface
@@ -118,6 +118,10 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         self._has_uninitialized_input_dist = True
         self._has_uninitialized_output_dist = True
         self._has_features_permute = True
+        self._env = env
+        self._peer = None          # fused lookup + exchange over NVLink peer memory (peer_dist.py)
+        self._peer_checked = False
+        self._last_local_batch = 0
         optims = [(f"lookups.{i}", m.fused_optimizer) for i, m in enumerate(self._lookups)
                   if isinstance(m, FusedOptimizerModule)]
         self._optim = CombinedOptimizer([o for _, o in optims]) if optims else CombinedOptimizer([])
@@ -153,6 +157,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         if self._has_uninitialized_input_dist:
             self._create_input_dist(features.keys())
             self._has_uninitialized_input_dist = False
+        self._last_local_batch = features.stride()
         with torch.no_grad():
             if self._has_features_permute:
                 features = features.permute(self._features_order, self._features_order_tensor)
@@ -173,10 +178,23 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         return EmbeddingBagCollectionAwaitable([d(e) for d, e in zip(self._output_dists, output)],
                                                self._embedding_dims, self._embedding_names)
 
+    def _peer_dist(self):
+        if not self._peer_checked:
+            from torchrec.distributed import peer_dist
+            self._peer_checked = True
+            if not self._is_weighted:
+                self._peer = peer_dist.try_build(self, self._env.process_group, self._device)
+        return self._peer
+
     def compute_and_output_dist(self, ctx: ShardedModuleContext, input: SparseFeaturesList
                                 ) -> LazyAwaitable[KeyedTensor]:
         if self._has_uninitialized_output_dist:
             self._create_output_dist()
+        peer = self._peer_dist()
+        if peer is not None:
+            values = peer(input, self._last_local_batch)
+            return NoWait(KeyedTensor(keys=self._embedding_names, length_per_key=self._embedding_dims,
+                                      values=values, key_dim=1))
         return EmbeddingBagCollectionAwaitable(
             [d(lookup(f)) for lookup, d, f in zip(self._lookups, self._output_dists, input)],
             self._embedding_dims, self._embedding_names)

@@ -1,0 +1,231 @@
+"""Fused lookup + exchange over NVLink peer memory for ShardedEmbeddingBagCollection.
+
+The reference runs lookup -> NCCL collective -> re-layout copy for every sharding type
+(table-wise: alltoall_pooled, comm_ops.py:203-560; row-wise: reduce_scatter_pooled, :382-890) and the
+transposed collectives in backward.  Here every rank maps its peers' output / gradient buffers
+(torch symmetric memory: CUDA VMM handles exchanged once) and the lookup kernels do the exchange:
+
+forward   table-wise : b200_tbe_forward_peer stores the pooled row of global sample b straight into
+                       rank (b // B_local)'s final [B_local, sum D] buffer, at that feature's column.
+          row-wise   : the same kernel stores the partial sums into slot `my rank` of the destination's
+                       staging buffer; after the barrier b200_peer_stage_reduce sums the W slots in rank
+                       order (deterministic) into the final buffer.
+backward  both       : b200_tbe_backward_peer loads the gradient row of sample b from rank
+                       (b // B_local)'s gradient buffer while it streams the sorted ids, applies 1/W and
+                       the fused optimizer.  This is the reverse all-to-all and the all-gather at once.
+
+Three stream-ordered cross-rank barriers per step bracket the peer accesses; no pooled
+[B_global, D_local] tensor, no NCCL pass over the embeddings and no split/cat copy exist.
+Enabled for CUDA process groups with world_size > 1 (B200_PEER_DIST=0 disables it); the NCCL path in
+comm_ops.py / dist_data.py stays as the portable implementation and is what the gloo tests run.
+"""
+from __future__ import annotations
+
+import os
+import warnings
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from b200_sparse import ops as _b200
+from torchrec.distributed import comm_ops
+
+
+def peer_dist_wanted(pg: Optional[dist.ProcessGroup], device: Optional[torch.device]) -> bool:
+    if os.environ.get("B200_PEER_DIST", "1") == "0":
+        return False
+    if pg is None or device is None or device.type != "cuda":
+        return False
+    return dist.get_world_size(pg) > 1 and dist.get_backend(pg) == "nccl"
+
+
+class PeerExchange:
+    """Symmetric buffers of one sharded module for a given local batch size."""
+
+    def __init__(self, pg: dist.ProcessGroup, device: torch.device, B_local: int, total_D: int, rw_dim: int) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+        self.W, self.rank = dist.get_world_size(pg), dist.get_rank(pg)
+        self.B_local, self.total_D, self.rw_dim = B_local, total_D, rw_dim
+        gname = pg.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(gname)
+        except Exception:  # newer torch: rendezvous does it
+            pass
+
+        def make(shape) -> Tuple[torch.Tensor, object, torch.Tensor]:
+            t = symm_mem.empty(shape, dtype=torch.float32, device=device)
+            h = symm_mem.rendezvous(t, gname)
+            ptrs = [int(p) for p in h.buffer_ptrs]
+            return t, h, ptrs
+
+        self.out, self._h_out, out_ptrs = make((B_local, total_D))
+        self.grad, self._h_grad, grad_ptrs = make((B_local, total_D))
+        self.out_bases = torch.tensor(out_ptrs, dtype=torch.int64, device=device)
+        self.grad_bases = torch.tensor(grad_ptrs, dtype=torch.int64, device=device)
+        self.stage = None
+        self.stage_bases = None
+        if rw_dim > 0:
+            self.stage, self._h_stage, st_ptrs = make((self.W, B_local, rw_dim))
+            slot = self.rank * B_local * rw_dim * 4  # my slot in every destination's staging buffer
+            self.stage_bases = torch.tensor([p + slot for p in st_ptrs], dtype=torch.int64, device=device)
+
+    def barrier(self) -> None:
+        self._h_out.barrier()
+
+
+class _Part:
+    """One table-batched lookup module with its column maps."""
+
+    __slots__ = ("tbe", "row_wise", "dst_col", "src_col", "n_features")
+
+    def __init__(self, tbe, row_wise: bool, dst_col: torch.Tensor, src_col: torch.Tensor, n_features: int) -> None:
+        self.tbe, self.row_wise, self.dst_col, self.src_col, self.n_features = tbe, row_wise, dst_col, src_col, n_features
+
+
+class PeerLookupDist:
+    """compute_and_output_dist of a ShardedEmbeddingBagCollection through peer memory."""
+
+    def __init__(self, sebc, pg: dist.ProcessGroup, device: torch.device) -> None:
+        from torchrec.distributed.sharding.rw_sharding import BaseRwEmbeddingSharding
+        from torchrec.distributed.sharding.tw_sharding import BaseTwEmbeddingSharding
+        self._pg, self._device = pg, device
+        self._W, self._rank = dist.get_world_size(pg), dist.get_rank(pg)
+        self._exchanges: Dict[int, PeerExchange] = {}
+        self._parts: List[List[_Part]] = []  # per sharding, per module
+        col0 = 0
+        self._rw_col0, self._rw_dim = 0, 0
+        for sharding, lookup in zip(sebc._sharding_type_to_sharding.values(), sebc._lookups):
+            mods = list(lookup._emb_modules)
+            if len(lookup._score_emb_modules):
+                raise NotImplementedError("weighted features take the NCCL path")
+            dims_total = sum(sharding.embedding_dims())
+            parts: List[_Part] = []
+            if isinstance(sharding, BaseTwEmbeddingSharding):
+                local0 = col0 + sum(sharding._dim_sum_per_rank()[:self._rank])
+                for m in mods:
+                    cols = (m.emb_module.D_offsets[:-1] + local0).to(torch.int32)
+                    parts.append(_Part(m.emb_module, False, cols, cols, m.config.num_features()))
+                    local0 += m.emb_module.total_D
+            elif isinstance(sharding, BaseRwEmbeddingSharding):
+                if self._rw_dim:
+                    raise NotImplementedError("one row-wise sharding per module")
+                self._rw_col0, self._rw_dim = col0, dims_total
+                local0 = 0
+                for m in mods:
+                    stage_cols = (m.emb_module.D_offsets[:-1] + local0).to(torch.int32)
+                    parts.append(_Part(m.emb_module, True, stage_cols, (stage_cols + col0).to(torch.int32),
+                                       m.config.num_features()))
+                    local0 += m.emb_module.total_D
+            else:
+                raise NotImplementedError(type(sharding).__name__)
+            self._parts.append(parts)
+            col0 += dims_total
+        self._total_D = col0
+        self._splits = [[p.n_features for p in parts] for parts in self._parts]
+        # every lookup module's placeholder parameter enters the autograd graph, as in the per-module
+        # path: DDP registers them and waits for each one before it reduces a bucket
+        self._placeholders = [p.tbe.placeholder_autograd_tensor for parts in self._parts for p in parts]
+        if not self._placeholders:  # a rank without tables still joins every barrier, forward and backward
+            self._placeholders = [torch.zeros(0, device=device, requires_grad=True)]
+
+    def exchange(self, B_local: int) -> PeerExchange:
+        px = self._exchanges.get(B_local)
+        if px is None:
+            px = PeerExchange(self._pg, self._device, B_local, self._total_D, self._rw_dim)
+            self._exchanges[B_local] = px
+        return px
+
+    def __call__(self, dist_input, B_local: int) -> torch.Tensor:
+        """dist_input: SparseFeaturesList (one per sharding) after the KJT all-to-all; B_local: this
+        rank's batch size (every rank must use the same one: no variable batch)."""
+        work = []  # (part, indices, offsets)
+        for parts, sf in zip(self._parts, dist_input):
+            kjt = sf.id_list_features
+            if not parts:
+                continue
+            pieces = kjt.split([p.n_features for p in parts]) if len(parts) > 1 else [kjt]
+            for p, piece in zip(parts, pieces):
+                assert piece.stride() == B_local * self._W, "variable batch size per rank is out of scope"
+                idx, off = p.tbe.prepare_indices(piece.values(), piece.offsets())
+                work.append((p, idx, off))
+        px = self.exchange(B_local)
+        return _PeerLookup.apply(self, px, work, *self._placeholders)
+
+
+class _PeerLookup(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, owner: PeerLookupDist, px: PeerExchange, work, *placeholders):
+        from fbgemm_gpu import _tbe_autograd as ta
+        need_grad = any(ctx.needs_input_grad[3:])
+        ctx.n_placeholders = len(placeholders)
+        main = torch.cuda.current_stream(px.out.device)
+        sorts = []
+        for p, idx, off in work:
+            m = p.tbe
+            T = m.D_offsets.numel() - 1
+            B = (off.numel() - 1) // T
+            if need_grad and idx.numel() > 0:
+                side = ta._side_stream(idx.device)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    s = torch.ops.fbgemm.b200_tbe_sort_indices(idx, off, m.hash_size_cumsum,
+                                                               m.total_hash_size_bits, B, False)
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                for t in (idx, off):
+                    t.record_stream(side)
+                for t in s:
+                    t.record_stream(main)
+                sorts.append((s, ev, B))
+            else:
+                sorts.append((None, None, B))
+        px.barrier()  # A: every rank is done with the buffers of the previous step
+        for (p, idx, off) in work:
+            m = p.tbe
+            bases = px.stage_bases if p.row_wise else px.out_bases
+            pitch = px.rw_dim if p.row_wise else px.total_D
+            _b200.tbe_forward_peer(m.weights_dev, m.weights_offsets, m.D_offsets, m.total_D, m.max_D,
+                                   m._all_D_mult8, idx, off, None, int(m.pooling_mode), bases, px.B_local, pitch,
+                                   p.dst_col)
+        px.barrier()  # B: all peer stores have landed
+        if px.stage is not None:
+            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col0)
+        ctx.px, ctx.work, ctx.sorts = px, work, sorts
+        return px.out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        from fbgemm_gpu import _tbe_autograd as ta
+        px = ctx.px
+        px.grad.copy_(grad_out)
+        px.barrier()  # C: every rank's gradient buffer is complete
+        scale = 1.0 / px.W if comm_ops.GRADIENT_DIVISION else 1.0
+        for (p, idx, off), (s, ev, B) in zip(ctx.work, ctx.sorts):
+            if s is None:
+                continue
+            m = p.tbe
+            a = m.optimizer_args
+            if a.gradient_clipping:
+                raise NotImplementedError("gradient clipping with the peer path")
+            if ev is not None:
+                torch.cuda.current_stream(idx.device).wait_event(ev)
+            keys, payload, _bag = s
+            srt = _b200.SortedIndices(keys, payload, None, keys.numel(), max(1, m.total_hash_size_bits), None)
+            _b200.tbe_backward_peer(px.grad_bases, px.B_local, px.total_D, p.src_col, scale, srt, m.weights_dev,
+                                    m.weights_offsets, m.D_offsets, m.hash_size_cumsum, B, m.max_D, m._all_D_mult8,
+                                    off, None, int(m.pooling_mode), ta._OPT_CODE[m.optimizer],
+                                    m.momentum1_dev if m.momentum1_dev.numel() else None, m.momentum1_offsets,
+                                    a.learning_rate, a.eps)
+        ctx.work = ctx.sorts = None
+        return (None, None, None) + (None,) * ctx.n_placeholders
+
+
+def try_build(sebc, pg, device) -> Optional[PeerLookupDist]:
+    if not peer_dist_wanted(pg, device):
+        return None
+    try:
+        return PeerLookupDist(sebc, pg, device)
+    except NotImplementedError as e:
+        warnings.warn(f"peer-memory embedding exchange not used ({e}); falling back to NCCL collectives")
+        return None

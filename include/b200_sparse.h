@@ -226,10 +226,11 @@ int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, in
                            float* momentum1, const int64_t* momentum1_offsets,
                            float learning_rate, float eps, void* partial_scratch, void* stream);
 
-/* Row-wise sharding: out[b, out_col : out_col + Dw] = sum_r stage[r][b][:] (rank order), stage
- * [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer. */
+/* Row-wise sharding: out[b, out_col4[c] : +4] = sum_r stage[r][b][4c : 4c+4] (rank order) for every
+ * float4 column c of the stage [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer;
+ * out_col4 (device int32 [Dw/4], multiples of 4) places each feature anywhere in the output row. */
 int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_local, int32_t Dw, float* out,
-                           int64_t out_pitch, int32_t out_col, void* stream);
+                           int64_t out_pitch, const int32_t* out_col4, void* stream);
 
 #ifdef __cplusplus
 }

@@ -289,8 +289,11 @@ def test_peer_stage_reduce(ops):
     W, B, Dw, pitch, col = 3, 37, 24, 64, 16
     stage = rng.standard_normal((W, B, Dw)).astype(np.float32)
     out = torch.full((B, pitch), 9.0, device="cuda")
-    ops.peer_stage_reduce(dev(stage), W, B, Dw, out, col)
+    # two features of widths 8 and 16 placed at columns 40 and 16 of the output
+    col4 = np.array([40, 44, 16, 20, 24, 28], dtype=np.int32)
+    ops.peer_stage_reduce(dev(stage), W, B, Dw, out, dev(col4))
     exp = stage[0] + stage[1] + stage[2]
     got = out.cpu().numpy()
-    np.testing.assert_array_equal(got[:, col:col + Dw], exp)
-    assert np.all(got[:, :col] == 9.0) and np.all(got[:, col + Dw:] == 9.0)
+    np.testing.assert_array_equal(got[:, 40:48], exp[:, :8])
+    np.testing.assert_array_equal(got[:, 16:32], exp[:, 8:])
+    assert np.all(got[:, :16] == 9.0) and np.all(got[:, 32:40] == 9.0) and np.all(got[:, 48:] == 9.0)

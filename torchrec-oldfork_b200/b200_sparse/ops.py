@@ -455,13 +455,17 @@ def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, sr
                                          _stream(dev)), "b200_tbe_backward_peer")
 
 
-def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: torch.Tensor, out_col: int) -> None:
-    """out[:, out_col:out_col+Dw] = sum over the W rank slots of stage ([W, B_local, Dw] fp32)."""
-    dev = _need_cuda(stage, out)
+def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: torch.Tensor,
+                      out_col4: torch.Tensor) -> None:
+    """Sum over the W rank slots of stage ([W, B_local, Dw] fp32); float4 column c of the stage goes to
+    output column out_col4[c] (int32 device tensor [Dw // 4])."""
+    dev = _need_cuda(stage, out, out_col4)
+    if out_col4.dtype != torch.int32 or out_col4.numel() != Dw // 4:
+        raise TypeError("out_col4 must be int32 with Dw // 4 entries")
     with torch.cuda.device(dev):
         KernelProfile.launches += 1
         check(lib.b200_peer_stage_reduce(_p(stage), int(W), int(B_local), int(Dw), _p(out), out.stride(0),
-                                         int(out_col), _stream(dev)), "b200_peer_stage_reduce")
+                                         _p(out_col4), _stream(dev)), "b200_peer_stage_reduce")
 
 
 # ------------------------------------------------------------------------ dot interaction

@@ -152,7 +152,7 @@ extern "C" int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t
 namespace b200 {
 __global__ void __launch_bounds__(256)
 peer_stage_reduce_kernel(const float* __restrict__ stage, int32_t W, int64_t rows, int32_t Dw4,
-                         float* __restrict__ out, int64_t pitch, int32_t out_col) {
+                         float* __restrict__ out, int64_t pitch, const int32_t* __restrict__ out_col4) {
   const int64_t total = rows * Dw4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -166,22 +166,22 @@ peer_stage_reduce_kernel(const float* __restrict__ stage, int32_t W, int64_t row
       acc.z += __uint_as_float(u.z);
       acc.w += __uint_as_float(u.w);
     }
-    *reinterpret_cast<float4*>(out + b * pitch + out_col + 4 * c) = acc;
+    *reinterpret_cast<float4*>(out + b * pitch + out_col4[c]) = acc;
   }
 }
 }  // namespace b200
 
 extern "C" int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_local, int32_t Dw,
-                                      float* out, int64_t out_pitch, int32_t out_col,
+                                      float* out, int64_t out_pitch, const int32_t* out_col4,
                                       void* stream) {
   using namespace b200;
-  if (W <= 0 || B_local < 0 || Dw < 0 || (Dw & 3) || (out_pitch & 3) || (out_col & 3)) return B200_EINVAL;
+  if (W <= 0 || B_local < 0 || Dw < 0 || (Dw & 3) || (out_pitch & 3) || !out_col4) return B200_EINVAL;
   if (B_local == 0 || Dw == 0) return B200_OK;
   const int64_t total = (int64_t)B_local * (Dw >> 2);
   int64_t grid = ceil_div(total, 256);
   if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
   peer_stage_reduce_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
-      stage, W, B_local, Dw >> 2, out, out_pitch, out_col);
+      stage, W, B_local, Dw >> 2, out, out_pitch, out_col4);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -193,7 +193,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         peer = self._peer_dist()
         if peer is not None:
             values = peer(input, self._last_local_batch)
-            return NoWait(KeyedTensor(keys=self._embedding_names, length_per_key=self._embedding_dims,
+            return NoWait(KeyedTensor(keys=peer.embedding_names, length_per_key=peer.embedding_dims,
                                       values=values, key_dim=1))
         return EmbeddingBagCollectionAwaitable(
             [d(lookup(f)) for lookup, d, f in zip(self._lookups, self._output_dists, input)],

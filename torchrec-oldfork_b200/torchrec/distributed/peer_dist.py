@@ -93,36 +93,59 @@ class PeerLookupDist:
         self._W, self._rank = dist.get_world_size(pg), dist.get_rank(pg)
         self._exchanges: Dict[int, PeerExchange] = {}
         self._parts: List[List[_Part]] = []  # per sharding, per module
-        col0 = 0
-        self._rw_col0, self._rw_dim = 0, 0
+        # Output columns follow the MODEL's feature order (the unsharded EmbeddingBagCollection's
+        # KeyedTensor), not the per-sharding-type grouping of the NCCL path: the kernels place every
+        # feature where the consumer wants it, so no reorder copy follows the exchange.
+        uses: Dict[str, int] = {}
+        for cfg in sebc._embedding_bag_configs:
+            for f in cfg.feature_names:
+                uses[f] = uses.get(f, 0) + 1
+        self.embedding_names: List[str] = []
+        self.embedding_dims: List[int] = []
+        col_of: Dict[str, int] = {}
+        col = 0
+        for cfg in sebc._embedding_bag_configs:
+            for f in cfg.feature_names:
+                name = f + "@" + cfg.name if uses[f] > 1 else f
+                col_of[name] = col
+                self.embedding_names.append(name)
+                self.embedding_dims.append(cfg.embedding_dim)
+                col += cfg.embedding_dim
+        self._total_D = col
+        self._rw_dim = 0
+        self._rw_col4: Optional[torch.Tensor] = None
+
+        def cols(names: List[str]) -> torch.Tensor:
+            return torch.tensor([col_of[n] for n in names], dtype=torch.int32, device=device)
+
         for sharding, lookup in zip(sebc._sharding_type_to_sharding.values(), sebc._lookups):
             mods = list(lookup._emb_modules)
             if len(lookup._score_emb_modules):
                 raise NotImplementedError("weighted features take the NCCL path")
-            dims_total = sum(sharding.embedding_dims())
             parts: List[_Part] = []
             if isinstance(sharding, BaseTwEmbeddingSharding):
-                local0 = col0 + sum(sharding._dim_sum_per_rank()[:self._rank])
                 for m in mods:
-                    cols = (m.emb_module.D_offsets[:-1] + local0).to(torch.int32)
-                    parts.append(_Part(m.emb_module, False, cols, cols, m.config.num_features()))
-                    local0 += m.emb_module.total_D
+                    c = cols(m.config.embedding_names())
+                    parts.append(_Part(m.emb_module, False, c, c, m.config.num_features()))
             elif isinstance(sharding, BaseRwEmbeddingSharding):
                 if self._rw_dim:
                     raise NotImplementedError("one row-wise sharding per module")
-                self._rw_col0, self._rw_dim = col0, dims_total
                 local0 = 0
+                chunk_cols: List[int] = []
                 for m in mods:
                     stage_cols = (m.emb_module.D_offsets[:-1] + local0).to(torch.int32)
-                    parts.append(_Part(m.emb_module, True, stage_cols, (stage_cols + col0).to(torch.int32),
-                                       m.config.num_features()))
+                    names = m.config.embedding_names()
+                    parts.append(_Part(m.emb_module, True, stage_cols, cols(names), m.config.num_features()))
+                    for n, d in zip(names, m.config.embedding_dims()):
+                        chunk_cols.extend(col_of[n] + 4 * k for k in range(d // 4))
                     local0 += m.emb_module.total_D
+                self._rw_dim = local0
+                self._rw_col4 = torch.tensor(chunk_cols, dtype=torch.int32, device=device)
             else:
                 raise NotImplementedError(type(sharding).__name__)
             self._parts.append(parts)
-            col0 += dims_total
-        self._total_D = col0
-        self._splits = [[p.n_features for p in parts] for parts in self._parts]
+        if any(d % 4 for d in self.embedding_dims):
+            raise NotImplementedError("embedding dims must be multiples of 4")
         # every lookup module's placeholder parameter enters the autograd graph, as in the per-module
         # path: DDP registers them and waits for each one before it reduces a bucket
         self._placeholders = [p.tbe.placeholder_autograd_tensor for parts in self._parts for p in parts]
@@ -190,7 +213,7 @@ class _PeerLookup(torch.autograd.Function):
                                    p.dst_col)
         px.barrier()  # B: all peer stores have landed
         if px.stage is not None:
-            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col0)
+            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4)
         ctx.px, ctx.work, ctx.sorts = px, work, sorts
         return px.out
 

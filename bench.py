@@ -289,12 +289,11 @@ def run_ours(args) -> None:
     dev_batches = [b.to(dev) for b in host_batches]
     torch.cuda.synchronize()
 
-    def train_step(batch):
-        dense_opt.zero_grad(set_to_none=True)
-        loss, _ = dmp(batch)
-        loss.backward()
-        dense_opt.step()
-        return loss
+    # The step is driven by the repo's public training API: TrainPipelineSparseDist.progress() =
+    # H2D of batch i+2 | sparse input dist of batch i+1 | forward/backward/optimizer of batch i.
+    import itertools
+    from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
+    pipe = TrainPipelineSparseDist(dmp, dense_opt, dev)
 
     def timed(fn, steps):
         dist.barrier()
@@ -310,30 +309,35 @@ def run_ours(args) -> None:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    for i in range(max(args.warmup, 3)):
-        train_step(dev_batches[i % len(dev_batches)])
-    torch.cuda.synchronize()
     shapes = lookup_shapes(dmp, dev_batches[0])  # runs the input collectives: every rank must call it
+    dev_iter = itertools.cycle(dev_batches)
+    for i in range(max(args.warmup, 3)):
+        pipe.progress(dev_iter)
+    torch.cuda.synchronize()
 
     # ---- value: inputs resident in HBM
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     KernelProfile.reset(enabled=True)
-    ms_total = timed(lambda i: train_step(dev_batches[i % len(dev_batches)]), args.steps)
+    ms_total = timed(lambda i: pipe.progress(dev_iter), args.steps)
     launches = KernelProfile.launches
     kern = KernelProfile.summary_ms()
     KernelProfile.reset(enabled=False)
     clocks = sampler.stop() if rank == 0 else {}
+    pipe.reset()
 
-    # ---- e2e: pinned host batch -> H2D every step, loss read back every step
+    # ---- e2e: pinned host batch -> H2D every step (memcpy stream), loss read back every step
+    host_iter = itertools.cycle(host_batches)
+
     def e2e_step(i):
-        b = host_batches[i % len(host_batches)].to(dev, non_blocking=True)
-        return float(train_step(b).item())
+        loss, _logits, _labels = pipe.progress(host_iter)
+        return float(loss.item())
 
-    for i in range(2):
+    for i in range(3):
         e2e_step(i)
     ms_e2e = timed(e2e_step, args.steps)
+    pipe.reset()
 
     if rank != 0:
         dist.destroy_process_group()

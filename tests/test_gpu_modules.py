@@ -235,3 +235,60 @@ def test_interaction_row_pitch_and_pitched_linear():
     torch.optim.SGD(lin.parameters(), lr=0.1).step()
     wf = lin.weight.detach().as_strided((N, 480), (480, 1), lin.weight.storage_offset())
     assert torch.count_nonzero(wf[:, width:]) == 0 and lin.weight.stride() == (480, 1)
+
+
+def test_train_pipeline_sparse_dist_matches_sequential(pg):
+    """TrainPipelineSparseDist (H2D | input dist | step, three batches in flight) produces the same losses
+    and weights as stepping through the same pinned host batches one by one."""
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig
+    from torchrec.datasets.random import RandomRecDataset
+    from torchrec.distributed import DistributedModelParallel, ShardingEnv
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
+    from torchrec.models.dlrm import DLRM, DLRMTrain
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda")
+    rows, D, B = [50, 7, 1000, 3], 16, 64
+    keys = [f"f{i}" for i in range(len(rows))]
+
+    def build():
+        torch.manual_seed(11)
+        ebc = EmbeddingBagCollection([EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r,
+                                                         feature_names=[keys[i]]) for i, r in enumerate(rows)],
+                                     device=torch.device("meta"))
+        model = DLRMTrain(ebc, 13, [32, D], [32, 1], dense_device=dev)
+        sharders = [EmbeddingBagCollectionSharder(fused_params={"learning_rate": 0.05,
+                                                                "optimizer": EmbOptimType.EXACT_ROWWISE_ADAGRAD})]
+        dmp = DistributedModelParallel(model, env=ShardingEnv.from_process_group(pg), device=dev, sharders=sharders)
+        return dmp, torch.optim.SGD(list(dmp.parameters()), lr=0.05)
+
+    a, opt_a = build()
+    b, opt_b = build()
+    with torch.no_grad():
+        for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+            assert ka == kb
+            vb.copy_(va)
+    ds = iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
+                               manual_seed=5))
+    host = [next(ds).pin_memory() for _ in range(5)]
+    seq_losses = []
+    for hb in host:
+        opt_a.zero_grad()
+        loss, _ = a(hb.to(dev))
+        loss.backward()
+        opt_a.step()
+        seq_losses.append(float(loss))
+    pipe = TrainPipelineSparseDist(b, opt_b, dev)
+    it = iter(host)
+    pipe_losses = []
+    while True:
+        try:
+            out = pipe.progress(it)
+        except StopIteration:
+            break
+        pipe_losses.append(float(out[0]))
+    assert len(pipe_losses) == len(host)
+    np.testing.assert_allclose(pipe_losses, seq_losses, rtol=1e-5, atol=1e-6)
+    for (k, va), (_, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+        torch.testing.assert_close(vb, va, rtol=1e-5, atol=1e-6, msg=k)

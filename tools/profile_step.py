@@ -25,7 +25,16 @@ def main():
     dmp, opt, rows = bench.build_gpu_model(args, rank, world, dev, dist.group.WORLD)
     batches = [b.to(dev) for b in bench.make_batches(rows, args.batch, rank, 2)]
 
+    import itertools
+    from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
+    use_pipe = os.environ.get("PIPE", "1") == "1"
+    pipe = TrainPipelineSparseDist(dmp, opt, dev)
+    it = itertools.cycle(batches)
+
     def step(b):
+        if use_pipe:
+            pipe.progress(it)
+            return
         opt.zero_grad(set_to_none=True)
         loss, _ = dmp(b)
         loss.backward()
@@ -39,6 +48,7 @@ def main():
         for i in range(4):
             step(batches[i % 2])
         torch.cuda.synchronize()
+    prof.export_chrome_trace(os.path.join(ROOT, "gpurun_out", f"trace_n{world}_r{rank}.json"))
     if rank == 0:
         print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=22, max_name_column_width=60))
         print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=60))

@@ -121,7 +121,6 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         self._env = env
         self._peer = None          # fused lookup + exchange over NVLink peer memory (peer_dist.py)
         self._peer_checked = False
-        self._last_local_batch = 0
         optims = [(f"lookups.{i}", m.fused_optimizer) for i, m in enumerate(self._lookups)
                   if isinstance(m, FusedOptimizerModule)]
         self._optim = CombinedOptimizer([o for _, o in optims]) if optims else CombinedOptimizer([])
@@ -157,7 +156,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         if self._has_uninitialized_input_dist:
             self._create_input_dist(features.keys())
             self._has_uninitialized_input_dist = False
-        self._last_local_batch = features.stride()
+        ctx.local_batch = features.stride()
         with torch.no_grad():
             if self._has_features_permute:
                 features = features.permute(self._features_order, self._features_order_tensor)
@@ -192,7 +191,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
             self._create_output_dist()
         peer = self._peer_dist()
         if peer is not None:
-            values = peer(input, self._last_local_batch)
+            values = peer(input, ctx.local_batch)
             return NoWait(KeyedTensor(keys=peer.embedding_names, length_per_key=peer.embedding_dims,
                                       values=values, key_dim=1))
         return EmbeddingBagCollectionAwaitable(

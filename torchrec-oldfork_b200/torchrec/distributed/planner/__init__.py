@@ -2,8 +2,10 @@
 out of scope — SURVEY.md §2a T14; its A100-era constants would mis-plan B200 anyway).
 
 Plans are explicit: `ParameterConstraints(sharding_types=[...], compute_kernels=[...])` per table
-decide the sharding type; table-wise tables are placed greedily on the rank with the fewest bytes;
-the result is deterministic, so every rank computes the same plan without a broadcast."""
+decide the sharding type; table-wise tables are placed greedily on the rank with the least LOOKUP
+traffic (bytes gathered per sample = embedding_dim x element size: a 3-row table costs a step as much
+as a 40M-row one), ties broken by stored bytes, subject to the HBM capacity; the result is
+deterministic, so every rank computes the same plan without a broadcast."""
 from __future__ import annotations
 
 from dataclasses import dataclass, field
@@ -47,7 +49,8 @@ class EmbeddingShardingPlanner:
     def plan(self, module: nn.Module, sharders: List[ModuleSharder]) -> ShardingPlan:
         W = self._topology.world_size
         by_type = {s.module_type: s for s in sharders}
-        load = [0] * W
+        load = [0] * W      # stored bytes per rank
+        traffic = [0] * W   # bytes gathered per sample per rank
         plan: Dict[str, Dict[str, ParameterSharding]] = {}
         for path, child in module.named_modules():
             sharder = by_type.get(type(child))
@@ -66,13 +69,17 @@ class EmbeddingShardingPlanner:
                 if c.sharding_types is None and nbytes > self._topology.hbm_cap // 2 and \
                         ShardingType.ROW_WISE.value in allowed and W > 1:
                     st = ShardingType.ROW_WISE.value
+                row_bytes = (p.shape[1] if p.dim() == 2 else 1) * p.element_size()
                 if st == ShardingType.TABLE_WISE.value:
-                    r = min(range(W), key=lambda i: (load[i], i))
+                    fits = [i for i in range(W) if load[i] + nbytes <= self._topology.hbm_cap] or list(range(W))
+                    r = min(fits, key=lambda i: (traffic[i], load[i], i))
                     load[r] += nbytes
+                    traffic[r] += row_bytes
                     entry[name] = ParameterSharding(st, kernels[0], ranks=[r])
                 elif st == ShardingType.ROW_WISE.value:
                     for i in range(W):
                         load[i] += nbytes // W
+                        traffic[i] += row_bytes  # every rank looks every sample up in its row block
                     entry[name] = ParameterSharding(st, kernels[0], ranks=list(range(W)))
                 else:
                     raise ValueError(f"sharding type {st} is not supported by this package")

@@ -167,6 +167,11 @@ class ShardedModule(abc.ABC, nn.Module, Generic[CompIn, DistOut, Out]):
         return self.output_dist(ctx, self.compute(ctx, input))
 
     def forward(self, *input, **kwargs) -> LazyAwaitable[Out]:
+        pipelined = getattr(self, "_pipelined_inputs", None)
+        if pipelined:
+            # TrainPipelineSparseDist ran input_dist for this batch on its data-dist stream already
+            ctx, dist_input = pipelined.popleft()
+            return self.compute_and_output_dist(ctx, dist_input)
         ctx = self.create_context()
         dist_input = self.input_dist(ctx, *input, **kwargs).wait()
         return self.compute_and_output_dist(ctx, dist_input)

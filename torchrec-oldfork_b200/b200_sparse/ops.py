@@ -486,6 +486,17 @@ def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: boo
     return buf[:, :width] if pitch != width else buf
 
 
+# Gradient sinks: a consumer that needs grad_sparse in a buffer of its own (the peer-memory exchange
+# keeps the pooled-embedding gradient in symmetric memory so that other ranks can read it) registers
+# that buffer here; interaction_backward then writes grad_sparse straight into it instead of a fresh
+# tensor, which saves the consumer a [B, F*D] copy per step.
+_GRAD_SINKS: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def register_grad_sink(buf: torch.Tensor) -> None:
+    _GRAD_SINKS[(buf.device.index, buf.numel())] = buf
+
+
 def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
                          grad_out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     dev = _need_cuda(dense, sparse, grad_out)
@@ -495,7 +506,8 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     if grad_out.dim() != 2 or grad_out.stride(1) != 1 or grad_out.stride(0) < grad_out.shape[1]:
         grad_out = grad_out.contiguous()  # a row-pitched view is consumed in place
     gd = torch.empty_like(dense)
-    gs = torch.empty_like(sparse)
+    sink = _GRAD_SINKS.get((dev.index, sparse.numel()))
+    gs = sink.view(sparse.shape) if sink is not None and sink.dtype == sparse.dtype else torch.empty_like(sparse)
     with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
         check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D,
                                             _p(gd), _p(gs), _stream(dev)), "b200_interaction_backward")

@@ -74,12 +74,18 @@ def create_embedding_configs_by_sharding(module: EmbeddingBagCollectionInterface
 
 
 class SparseFeaturesListAwaitable(Awaitable[SparseFeaturesList]):
-    def __init__(self, awaitables: List[Awaitable[SparseFeatures]]) -> None:
+    """Holds the phase-1 (lengths) awaitables of every sharding: building it only ENQUEUES the lengths
+    all-to-alls; wait() reads the receive sizes (the one host sync per sharding), starts every values
+    all-to-all, then waits for them.  A pipeline can therefore enqueue phase 1 early and take the host
+    sync when the exchange has long finished."""
+
+    def __init__(self, awaitables: List[Awaitable[Awaitable[SparseFeatures]]]) -> None:
         super().__init__()
         self.awaitables = awaitables
 
     def _wait_impl(self) -> SparseFeaturesList:
-        return SparseFeaturesList([a.wait() for a in self.awaitables])
+        phase2 = [a.wait() for a in self.awaitables]
+        return SparseFeaturesList([a.wait() for a in phase2])
 
 
 class EmbeddingBagCollectionAwaitable(LazyAwaitable[KeyedTensor]):
@@ -165,7 +171,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
             for dist_module, f in zip(self._input_dists, shards):
                 sf = SparseFeatures(id_list_features=None if self._is_weighted else f,
                                     id_score_list_features=f if self._is_weighted else None)
-                awaitables.append(dist_module(sf).wait())
+                awaitables.append(dist_module(sf))
             return SparseFeaturesListAwaitable(awaitables)
 
     def compute(self, ctx: ShardedModuleContext, dist_input: SparseFeaturesList) -> List[torch.Tensor]:

@@ -61,6 +61,7 @@ class PeerExchange:
 
         self.out, self._h_out, out_ptrs = make((B_local, total_D))
         self.grad, self._h_grad, grad_ptrs = make((B_local, total_D))
+        _b200.register_grad_sink(self.grad)  # the dot-interaction backward writes its grad_sparse here
         self.out_bases = torch.tensor(out_ptrs, dtype=torch.int64, device=device)
         self.grad_bases = torch.tensor(grad_ptrs, dtype=torch.int64, device=device)
         self.stage = None
@@ -221,7 +222,8 @@ class _PeerLookup(torch.autograd.Function):
     def backward(ctx, grad_out):
         from fbgemm_gpu import _tbe_autograd as ta
         px = ctx.px
-        px.grad.copy_(grad_out)
+        if grad_out.data_ptr() != px.grad.data_ptr() or not grad_out.is_contiguous():
+            px.grad.copy_(grad_out)  # producers that know the sink (ops.register_grad_sink) skip this pass
         px.barrier()  # C: every rank's gradient buffer is complete
         scale = 1.0 / px.W if comm_ops.GRADIENT_DIVISION else 1.0
         for (p, idx, off), (s, ev, B) in zip(ctx.work, ctx.sorts):

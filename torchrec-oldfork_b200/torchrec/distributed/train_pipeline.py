@@ -79,26 +79,40 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
             m._pipelined_inputs = deque()
         self._batch_i = self._batch_ip1 = self._batch_ip2 = None
         self._dist_done: Deque[torch.cuda.Event] = deque()
+        self._issued: list = []
 
-    # reference _start_data_dist (:254-300) + _wait_for_batch
-    def _start_sparse_data_dist(self, batch) -> None:
-        """Runs input_dist of every sharded module for `batch` on the data-dist stream, including the
-        wait of the second all-to-all phase, and leaves the result in the module's pipelined queue."""
-        main = torch.cuda.current_stream(self._device)
+    # reference _start_data_dist (:254-300) + _wait_sparse_data_dist, split in two so that the host sync
+    # of phase 1 is taken only after the whole step of the previous batch has been queued
+    def _issue_sparse_data_dist(self, batch) -> None:
+        """Enqueues bucketize / permute and the lengths all-to-alls of `batch` on the data-dist stream."""
         with torch.cuda.stream(self._data_dist_stream):
             self._data_dist_stream.wait_stream(self._memcpy_stream)
             batch.record_stream(self._data_dist_stream)
             kjt = self._features_of(batch)
+            self._issued = []
             for m in self._sharded:
                 ctx = m.create_context()
-                dist_input = m.input_dist(ctx, kjt).wait()
+                self._issued.append((m, ctx, m.input_dist(ctx, kjt)))
+
+    def _complete_sparse_data_dist(self) -> None:
+        """Reads the receive sizes, runs the values all-to-alls and the recat on the data-dist stream and
+        leaves the distributed features in each module's pipelined queue."""
+        main = torch.cuda.current_stream(self._device)
+        with torch.cuda.stream(self._data_dist_stream):
+            for m, ctx, awaitable in self._issued:
+                dist_input = awaitable.wait()
                 record = getattr(dist_input, "record_stream", None)
                 if record is not None:
                     record(main)
                 m._pipelined_inputs.append((ctx, dist_input))
+            self._issued = []
             ev = torch.cuda.Event()
             ev.record(self._data_dist_stream)
             self._dist_done.append(ev)
+
+    def _start_sparse_data_dist(self, batch) -> None:
+        self._issue_sparse_data_dist(batch)
+        self._complete_sparse_data_dist()
 
     def reset(self) -> None:
         """Drops the prefetched batches and their queued sparse distributions."""
@@ -106,6 +120,7 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         for m in self._sharded:
             m._pipelined_inputs.clear()
         self._dist_done.clear()
+        self._issued = []
         self._batch_i = self._batch_ip1 = self._batch_ip2 = None
         self._connected = False
 
@@ -139,15 +154,18 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         self._batch_i.record_stream(main)
         # batch i+2: host -> device
         self._batch_ip2 = self._copy(dataloader_iter)
+        # batch i+1, phase 1: its lengths all-to-alls enter the NCCL queue ahead of this step's gradient
+        # all-reduces ...
+        if self._batch_ip1 is not None:
+            self._issue_sparse_data_dist(self._batch_ip1)
         losses, output = self._model(self._batch_i)
         if self._model.training:
             torch.sum(losses, dim=0).backward()
             self._optimizer.step()
-        # batch i+1: the sparse distribution (and its host read of the length table) is issued once the
-        # whole step of batch i is queued, so the host blocks while the GPU still has the backward of
-        # batch i to run.  (The reference issues it between forward and backward, :529, which leaves the
-        # GPU idle for the duration of the host sync.)
+        # ... phase 2: the host read of the receive sizes happens once the whole step of batch i is
+        # queued, when that exchange has long finished, so neither the host nor the GPU waits.  (The
+        # reference does both phases between forward and backward, :529: the GPU idles during the sync.)
         if self._batch_ip1 is not None:
-            self._start_sparse_data_dist(self._batch_ip1)
+            self._complete_sparse_data_dist()
         self._batch_i, self._batch_ip1 = self._batch_ip1, self._batch_ip2
         return output

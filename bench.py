@@ -286,6 +286,8 @@ def run_ours(args) -> None:
 
     dmp, dense_opt, rows = build_gpu_model(args, rank, world, dev, pg)
     host_batches = make_batches(rows, args.batch, rank, 4)
+    for hb in host_batches:
+        hb.sparse_features.length_per_key()  # host-side totals travel with the KJT (no device read later)
     dev_batches = [b.to(dev) for b in host_batches]
     torch.cuda.synchronize()
 

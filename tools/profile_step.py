@@ -23,7 +23,10 @@ def main():
     args = bench.parse_args()
     torch.backends.cuda.matmul.allow_tf32 = True
     dmp, opt, rows = bench.build_gpu_model(args, rank, world, dev, dist.group.WORLD)
-    batches = [b.to(dev) for b in bench.make_batches(rows, args.batch, rank, 2)]
+    host = bench.make_batches(rows, args.batch, rank, 2)
+    for hb in host:
+        hb.sparse_features.length_per_key()
+    batches = [b.to(dev) for b in host]
 
     import itertools
     from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
@@ -43,6 +46,28 @@ def main():
     for i in range(5):
         step(batches[i % 2])
     torch.cuda.synchronize()
+    if os.environ.get("CPROFILE") == "1":
+        import cProfile
+        import pstats
+        import time
+        t0 = time.perf_counter()
+        for i in range(20):
+            step(batches[i % 2])
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        pr = cProfile.Profile()
+        pr.enable()
+        for i in range(20):
+            step(batches[i % 2])
+        pr.disable()
+        torch.cuda.synchronize()
+        if rank == 0:
+            print(f"host enqueue/step {1e3 * (t1 - t0) / 20:.2f} ms, wall/step {1e3 * (t2 - t0) / 20:.2f} ms")
+            st = pstats.Stats(pr)
+            st.sort_stats("cumulative").print_stats(70)
+        dist.destroy_process_group()
+        return
     from torch.profiler import ProfilerActivity, profile
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
         for i in range(4):

@@ -74,7 +74,13 @@ def _need_cuda(*ts: Optional[torch.Tensor]) -> torch.device:
     return dev
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream(dev: torch.device) -> int:
+    """cudaStream_t of torch's current stream on `dev` (every launch goes there)."""
+    if _raw_stream is not None:
+        return _raw_stream(dev.index if dev.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(dev).cuda_stream
 
 

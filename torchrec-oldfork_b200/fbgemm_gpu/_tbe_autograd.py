@@ -82,7 +82,7 @@ def _side_stream(dev: torch.device) -> "torch.cuda.Stream":
     idx = dev.index if dev.index is not None else torch.cuda.current_device()
     s = _SIDE_STREAMS.get(idx)
     if s is None:
-        s = torch.cuda.Stream(device=dev)
+        s = torch.cuda.Stream(device=dev, priority=-1)  # small kernels: let them slip in between big ones
         _SIDE_STREAMS[idx] = s
     return s
 

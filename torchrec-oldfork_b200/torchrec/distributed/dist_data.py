@@ -105,7 +105,8 @@ class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
             return
         src = input.lengths().contiguous().view(-1)
         self._lengths = src.new_empty(self._local_split * B * self._workers)
-        self._in_lengths_per_worker = _split_lengths(splits, input.keys(), input.offset_per_key())
+        # the lengths exchange has fixed split sizes; the (data-dependent) send sizes of the values
+        # exchange are read in wait(), so issuing phase 1 never blocks the host
         self._work = dist.all_to_all_single(
             self._lengths, src, output_split_sizes=[self._local_split * B] * self._workers,
             input_split_sizes=[s * B for s in splits], group=pg, async_op=True)
@@ -114,6 +115,8 @@ class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
         out_lengths_per_worker: List[int] = []
         length_per_key: Optional[List[int]] = None
         if self._workers > 1:
+            self._in_lengths_per_worker = _split_lengths(self._splits, self._input.keys(),
+                                                         self._input.offset_per_key())
             self._work.wait()
             if self._local_split > 0:
                 # one D2H read: [W, F_local] totals -> receive splits and per-key totals

@@ -71,6 +71,10 @@ class PeerExchange:
             slot = self.rank * B_local * rw_dim * 4  # my slot in every destination's staging buffer
             self.stage_bases = torch.tensor([p + slot for p in st_ptrs], dtype=torch.int64, device=device)
 
+        # True after a backward pass: its barrier C already proves that every rank is done with the
+        # buffers of that step, so the next forward may skip barrier A (see _PeerLookup.forward)
+        self.quiesced = False
+
     def barrier(self) -> None:
         self._h_out.barrier()
 
@@ -204,7 +208,14 @@ class _PeerLookup(torch.autograd.Function):
                 sorts.append((s, ev, B))
             else:
                 sorts.append((None, None, B))
-        px.barrier()  # A: every rank is done with the buffers of the previous step
+        # A: every rank must be done with the buffers of the previous use.  After a training step that is
+        # already known: barrier C of its backward comes after each rank's last read of `out` (the
+        # interaction backward) and of the staging buffer, and peers only overwrite `grad` after barrier
+        # B below.  Only forward-after-forward (evaluation) needs the explicit barrier.  Every rank runs
+        # the same sequence, so the decision is identical everywhere.
+        if not px.quiesced:
+            px.barrier()
+        px.quiesced = False
         for (p, idx, off) in work:
             m = p.tbe
             bases = px.stage_bases if p.row_wise else px.out_bases
@@ -225,6 +236,7 @@ class _PeerLookup(torch.autograd.Function):
         if grad_out.data_ptr() != px.grad.data_ptr() or not grad_out.is_contiguous():
             px.grad.copy_(grad_out)  # producers that know the sink (ops.register_grad_sink) skip this pass
         px.barrier()  # C: every rank's gradient buffer is complete
+        px.quiesced = True
         scale = 1.0 / px.W if comm_ops.GRADIENT_DIVISION else 1.0
         for (p, idx, off), (s, ev, B) in zip(ctx.work, ctx.sorts):
             if s is None:

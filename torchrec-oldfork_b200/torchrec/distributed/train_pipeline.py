@@ -36,7 +36,7 @@ class TrainPipelineBase(Generic[In, Out]):
 
     def __init__(self, model: nn.Module, optimizer: torch.optim.Optimizer, device: torch.device) -> None:
         self._model, self._optimizer, self._device = model, optimizer, device
-        self._memcpy_stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
+        self._memcpy_stream = torch.cuda.Stream(device=device, priority=-1) if device.type == "cuda" else None
         self._cur_batch = None
         self._connected = False
 
@@ -72,7 +72,9 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         super().__init__(model, optimizer, device)
         if device.type != "cuda":
             raise RuntimeError("TrainPipelineSparseDist overlaps CUDA streams; use TrainPipelineBase on CPU")
-        self._data_dist_stream = torch.cuda.Stream(device=device)
+        # high priority: the small bucketize / permute / reduction kernels whose results the host waits for
+        # must not queue behind the thousands of CTAs of the previous batch's backward
+        self._data_dist_stream = torch.cuda.Stream(device=device, priority=-1)
         self._features_of = sparse_features_fn or (lambda b: b.sparse_features)
         self._sharded: List[ShardedModule] = [m for m in model.modules() if isinstance(m, ShardedModule)]
         for m in self._sharded:
@@ -129,6 +131,10 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
             host = next(it)
         except StopIteration:
             return None
+        kjt = self._features_of(host)
+        if kjt is not None and not kjt.values().is_cuda:
+            kjt.length_per_key()  # per-key totals from the HOST copy: the table-wise exchange then needs no
+            #                       device read for its send sizes (they travel with the KJT through .to())
         with torch.cuda.stream(self._memcpy_stream):
             return _to_device(host, self._device, True)
 

@@ -202,14 +202,17 @@ int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsu
  * barriers (all ranks' stores done before anyone reads; all reads done before buffers are reused). */
 
 /* b200_tbe_forward whose pooled row of global sample b is written to
- * dst_bases[b / B_dst] + (b % B_dst) * dst_pitch + dst_col[t]  (elements of the output dtype). */
+ * dst_bases[b / B_dst] + (b % B_dst) * dst_pitch + dst_col[t]  (elements of the output dtype).
+ * skip_empty != 0: empty bags store nothing (the destination is pre-zeroed; used for the partial sums
+ * of row-wise sharding, where a bag is empty on every rank that owns none of its rows). */
 int b200_tbe_forward_peer(const void* weights, int weight_dtype, const int64_t* weights_offsets,
                           const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
                           int32_t max_D, int32_t all_D_mult8, const void* indices,
                           const void* offsets, int index_dtype, const float* per_sample_weights,
                           int pooling_mode, void* const* dst_bases /*device [n_dst]*/,
                           int32_t n_dst, int32_t B_dst, int64_t dst_pitch,
-                          const int32_t* dst_col /*device [T]*/, int output_dtype, void* stream);
+                          const int32_t* dst_col /*device [T]*/, int output_dtype,
+                          int32_t skip_empty, void* stream);
 
 /* b200_tbe_backward whose gradient row of global sample b is read from
  * grad_bases[b / B_src] + (b % B_src) * grad_stride + src_col[t], scaled by grad_scale
@@ -228,9 +231,11 @@ int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, in
 
 /* Row-wise sharding: out[b, out_col4[c] : +4] = sum_r stage[r][b][4c : 4c+4] (rank order) for every
  * float4 column c of the stage [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer;
- * out_col4 (device int32 [Dw/4], multiples of 4) places each feature anywhere in the output row. */
-int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_local, int32_t Dw, float* out,
-                           int64_t out_pitch, const int32_t* out_col4, void* stream);
+ * out_col4 (device int32 [Dw/4], multiples of 4) places each feature anywhere in the output row.
+ * clear_stage != 0: every non-zero slot read is zeroed again, ready for a skip_empty forward. */
+int b200_peer_stage_reduce(float* stage, int32_t W, int32_t B_local, int32_t Dw, float* out,
+                           int64_t out_pitch, const int32_t* out_col4, int32_t clear_stage,
+                           void* stream);
 
 #ifdef __cplusplus
 }

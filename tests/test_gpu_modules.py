@@ -171,7 +171,7 @@ def test_quantized_ebc():
     assert sd["embedding_bags.t0.weight"].shape == (100, 144)
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("exchange", ["peer", "nccl"])
 def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     """TW + RW over `world` GPUs (torchrun): the fused peer-memory exchange and the NCCL collectives both

@@ -237,6 +237,17 @@ def test_forward_peer_scatter(ops, case, n_dst):
     for t, d in enumerate(dims):
         np.testing.assert_allclose(got[:, col[t]:col[t] + d], exp[:, Do[t]:Do[t] + d], rtol=1e-5, atol=1e-5)
     assert np.all(got[:, :8] == -7.0) and np.all(got[:, c:] == -7.0)  # nothing outside the feature columns
+    # skip_empty: empty bags leave the (pre-filled) destination untouched, every other bag is as before
+    bufs2 = [torch.full((B_dst, pitch), -7.0, device="cuda") for _ in range(n_dst)]
+    bases2 = torch.tensor([b.data_ptr() for b in bufs2], dtype=torch.int64, device="cuda")
+    ops.tbe_forward_peer(w.cuda(), dev(wo), dev(Do), total_D, max(dims), all(d % 8 == 0 for d in dims),
+                         dev(indices), dev(offsets), None, 0, bases2, B_dst, pitch, dev(col), skip_empty=True)
+    got2 = torch.cat(bufs2, 0).cpu().numpy()
+    lens = np.diff(offsets).reshape(len(dims), B)
+    for t, d in enumerate(dims):
+        blk = got2[:, col[t]:col[t] + d]
+        assert np.all(blk[lens[t] == 0] == -7.0)
+        np.testing.assert_array_equal(blk[lens[t] > 0], got[:, col[t]:col[t] + d][lens[t] > 0])
 
 
 @pytest.mark.parametrize("case", [0, 1, 4])
@@ -297,3 +308,8 @@ def test_peer_stage_reduce(ops):
     np.testing.assert_array_equal(got[:, 40:48], exp[:, :8])
     np.testing.assert_array_equal(got[:, 16:32], exp[:, 8:])
     assert np.all(got[:, :16] == 9.0) and np.all(got[:, 32:40] == 9.0) and np.all(got[:, 48:] == 9.0)
+    # clear_stage: same sums, and the stage reads back as zeros
+    st = dev(stage)
+    out2 = torch.full((B, pitch), 9.0, device="cuda")
+    ops.peer_stage_reduce(st, W, B, Dw, out2, dev(col4), clear_stage=True)
+    assert torch.equal(out2, out) and not st.any()

@@ -65,7 +65,7 @@ def main():
         if rank == 0:
             print(f"host enqueue/step {1e3 * (t1 - t0) / 20:.2f} ms, wall/step {1e3 * (t2 - t0) / 20:.2f} ms")
             st = pstats.Stats(pr)
-            st.sort_stats("cumulative").print_stats(70)
+            st.sort_stats("tottime").print_stats(28)
         dist.destroy_process_group()
         return
     from torch.profiler import ProfilerActivity, profile
@@ -73,9 +73,10 @@ def main():
         for i in range(4):
             step(batches[i % 2])
         torch.cuda.synchronize()
-    prof.export_chrome_trace(os.path.join(ROOT, "gpurun_out", f"trace_n{world}_r{rank}.json"))
+    if os.environ.get("TRACE") == "1":
+        prof.export_chrome_trace(os.path.join(ROOT, "gpurun_out", f"trace_n{world}_r{rank}.json"))
     if rank == 0:
-        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=22, max_name_column_width=60))
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=32, max_name_column_width=60))
         print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=60))
     dist.destroy_process_group()
 

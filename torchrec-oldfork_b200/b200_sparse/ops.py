@@ -414,9 +414,10 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
 def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
                      total_D: int, max_D: int, all_D_mult8: bool, indices: torch.Tensor, offsets: torch.Tensor,
                      per_sample_weights: Optional[torch.Tensor], pooling_mode: int, dst_bases: torch.Tensor,
-                     B_dst: int, dst_pitch: int, dst_col: torch.Tensor) -> None:
+                     B_dst: int, dst_pitch: int, dst_col: torch.Tensor, skip_empty: bool = False) -> None:
     """Pooled lookup whose rows go to dst_bases[b // B_dst] (int64 device array of fp32 buffer
-    addresses, usually NVLink peer mappings) at row b % B_dst, column dst_col[t]."""
+    addresses, usually NVLink peer mappings) at row b % B_dst, column dst_col[t].  skip_empty: empty
+    bags store nothing (pre-zeroed destination)."""
     dev = _need_cuda(weights, weights_offsets, D_offsets, indices, offsets, per_sample_weights, dst_bases, dst_col)
     if indices.dtype != offsets.dtype:
         raise TypeError("indices and offsets must share a dtype")
@@ -432,7 +433,8 @@ def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
                                         total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
                                         _p(offsets.contiguous()), idt, _p(per_sample_weights), int(pooling_mode),
                                         _p(dst_bases), dst_bases.numel(), int(B_dst), int(dst_pitch), _p(dst_col),
-                                        _DT[torch.float32], _stream(dev)), "b200_tbe_forward_peer")
+                                        _DT[torch.float32], int(bool(skip_empty)), _stream(dev)),
+              "b200_tbe_forward_peer")
 
 
 def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, src_col: torch.Tensor,
@@ -462,16 +464,17 @@ def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, sr
 
 
 def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: torch.Tensor,
-                      out_col4: torch.Tensor) -> None:
+                      out_col4: torch.Tensor, clear_stage: bool = False) -> None:
     """Sum over the W rank slots of stage ([W, B_local, Dw] fp32); float4 column c of the stage goes to
-    output column out_col4[c] (int32 device tensor [Dw // 4])."""
+    output column out_col4[c] (int32 device tensor [Dw // 4]).  clear_stage: zero what was read."""
     dev = _need_cuda(stage, out, out_col4)
     if out_col4.dtype != torch.int32 or out_col4.numel() != Dw // 4:
         raise TypeError("out_col4 must be int32 with Dw // 4 entries")
     with torch.cuda.device(dev):
         KernelProfile.launches += 1
         check(lib.b200_peer_stage_reduce(_p(stage), int(W), int(B_local), int(Dw), _p(out), out.stride(0),
-                                         _p(out_col4), _stream(dev)), "b200_peer_stage_reduce")
+                                         _p(out_col4), int(bool(clear_stage)), _stream(dev)),
+              "b200_peer_stage_reduce")
 
 
 # ------------------------------------------------------------------------ dot interaction

@@ -94,7 +94,7 @@ extern "C" const char* b200_error_string(int code) {
   }
 }
 
-extern "C" int b200_abi_version(void) { return 2; }
+extern "C" int b200_abi_version(void) { return 3; }
 
 extern "C" int b200_tbe_grad_indice_weights(const float* grad_output, int64_t grad_stride,
                                             const void* weights, int weight_dtype,
@@ -151,8 +151,9 @@ extern "C" int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t
 // columns [out_col, out_col + Dw) of the [B_local, pitch] output.
 namespace b200 {
 __global__ void __launch_bounds__(256)
-peer_stage_reduce_kernel(const float* __restrict__ stage, int32_t W, int64_t rows, int32_t Dw4,
-                         float* __restrict__ out, int64_t pitch, const int32_t* __restrict__ out_col4) {
+peer_stage_reduce_kernel(float* __restrict__ stage, int32_t W, int64_t rows, int32_t Dw4,
+                         float* __restrict__ out, int64_t pitch, const int32_t* __restrict__ out_col4,
+                         bool clear) {
   const int64_t total = rows * Dw4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -160,7 +161,12 @@ peer_stage_reduce_kernel(const float* __restrict__ stage, int32_t W, int64_t row
     const int c = (int)(i - b * Dw4);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = 0; r < W; ++r) {
-      const uint4 u = ldg_stream_16(reinterpret_cast<const float4*>(stage) + (int64_t)r * total + i);
+      float4* slot = reinterpret_cast<float4*>(stage) + (int64_t)r * total + i;
+      const float4 f = __ldcg(slot);  // written by peers, re-zeroed below: no non-coherent path
+      const uint4 u = make_uint4(__float_as_uint(f.x), __float_as_uint(f.y), __float_as_uint(f.z),
+                                 __float_as_uint(f.w));
+      // consume: the next step's peers only store the non-empty bags, the rest must read as zero
+      if (clear && (u.x | u.y | u.z | u.w)) *slot = make_float4(0.f, 0.f, 0.f, 0.f);
       acc.x += __uint_as_float(u.x);
       acc.y += __uint_as_float(u.y);
       acc.z += __uint_as_float(u.z);
@@ -171,9 +177,9 @@ peer_stage_reduce_kernel(const float* __restrict__ stage, int32_t W, int64_t row
 }
 }  // namespace b200
 
-extern "C" int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_local, int32_t Dw,
+extern "C" int b200_peer_stage_reduce(float* stage, int32_t W, int32_t B_local, int32_t Dw,
                                       float* out, int64_t out_pitch, const int32_t* out_col4,
-                                      void* stream) {
+                                      int32_t clear_stage, void* stream) {
   using namespace b200;
   if (W <= 0 || B_local < 0 || Dw < 0 || (Dw & 3) || (out_pitch & 3) || !out_col4) return B200_EINVAL;
   if (B_local == 0 || Dw == 0) return B200_OK;
@@ -181,7 +187,7 @@ extern "C" int b200_peer_stage_reduce(const float* stage, int32_t W, int32_t B_l
   int64_t grid = ceil_div(total, 256);
   if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
   peer_stage_reduce_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
-      stage, W, B_local, Dw >> 2, out, out_pitch, out_col4);
+      stage, W, B_local, Dw >> 2, out, out_pitch, out_col4, clear_stage != 0);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -78,6 +78,7 @@ struct FwdPeerDst {
   const int32_t* col;
   int64_t pitch;
   int32_t B_dst;
+  int32_t skip_empty;  // destination is pre-zeroed: empty bags store nothing (row-wise partial sums)
 };
 
 template <typename W, typename O, int EPV, int NV, bool PEER>
@@ -130,7 +131,7 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
   for (int v = 0; v < NV; ++v) act[v] = EPV * (lane + 32 * v) < D;
 
   // Empty bags pool to zeros.
-  for (unsigned m = empty; m; m &= m - 1) {
+  for (unsigned m = (PEER && peer.skip_empty) ? 0u : empty; m; m &= m - 1) {
     const int j = __ffs(m) - 1;
     float z[EPV];
 #pragma unroll
@@ -376,11 +377,11 @@ extern "C" int b200_tbe_forward_peer(const void* weights, int weight_dtype,
                                      int index_dtype, const float* per_sample_weights,
                                      int pooling_mode, void* const* dst_bases, int32_t n_dst,
                                      int32_t B_dst, int64_t dst_pitch, const int32_t* dst_col,
-                                     int output_dtype, void* stream) {
+                                     int output_dtype, int32_t skip_empty, void* stream) {
   if (!dst_bases || !dst_col || n_dst <= 0 || B_dst <= 0 || (int64_t)n_dst * B_dst < B ||
       (dst_pitch & 3))
     return B200_EINVAL;
-  b200::FwdPeerDst peer{dst_bases, dst_col, dst_pitch, B_dst};
+  b200::FwdPeerDst peer{dst_bases, dst_col, dst_pitch, B_dst, skip_empty ? 1 : 0};
   return tbe_forward_impl(weights, weight_dtype, weights_offsets, D_offsets, T, B, total_D, max_D,
                           all_D_mult8, indices, offsets, index_dtype, per_sample_weights,
                           pooling_mode, nullptr, output_dtype, &peer, stream);

@@ -54,7 +54,9 @@ class GroupedPooledEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Te
         if len(outs) == 0:
             kjt = sparse_features.id_list_features or sparse_features.id_score_list_features
             B = kjt.stride() if kjt is not None else 0
-            return torch.empty((B, 0), device=self._device)
+            # a rank without tables of this sharding type still takes part in the output collective and
+            # in its backward: the empty block must be part of the autograd graph
+            return torch.empty((B, 0), device=self._device, requires_grad=torch.is_grad_enabled())
         return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
 
     def _all_modules(self) -> List[nn.Module]:

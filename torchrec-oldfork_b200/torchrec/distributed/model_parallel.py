@@ -41,6 +41,17 @@ class DefaultDataParallelWrapper(DataParallelWrapper):
             return
         if not any(p.requires_grad for p in dmp._dmp_wrapped_module.parameters()):
             return
+        # Everything under a ShardedModule is model-parallel: the table shards are updated by the fused
+        # backward, and the number of lookup modules (hence of their autograd placeholders) differs from
+        # rank to rank.  DDP must see the same dense parameter list everywhere (reference :96-104).
+        ignore: List[str] = []
+        for mod_name, mod in dmp._dmp_wrapped_module.named_modules():
+            if isinstance(mod, ShardedModule):
+                for sub_name, sub in nn.Module.named_modules(mod):
+                    full = ".".join(x for x in (mod_name, sub_name) if x)
+                    for n, _ in list(sub._parameters.items()) + list(sub._buffers.items()):
+                        ignore.append(f"{full}.{n}" if full else n)
+        DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(dmp._dmp_wrapped_module, ignore)
         dmp._dmp_wrapped_module = DistributedDataParallel(
             module=dmp._dmp_wrapped_module.to(device),
             device_ids=None if device.type == "cpu" else [device], process_group=pg,

@@ -7,9 +7,11 @@ transposed collectives in backward.  Here every rank maps its peers' output / gr
 
 forward   table-wise : b200_tbe_forward_peer stores the pooled row of global sample b straight into
                        rank (b // B_local)'s final [B_local, sum D] buffer, at that feature's column.
-          row-wise   : the same kernel stores the partial sums into slot `my rank` of the destination's
-                       staging buffer; after the barrier b200_peer_stage_reduce sums the W slots in rank
-                       order (deterministic) into the final buffer.
+          row-wise   : the same kernel stores the partial sums of its NON-EMPTY bags into slot `my rank`
+                       of the destination's (all-zero) staging buffer; after the barrier
+                       b200_peer_stage_reduce sums the W slots in rank order (deterministic) into the
+                       final buffer and zeroes what it read.  With one id per bag this moves 1/W of
+                       what a reduce-scatter of dense partial sums moves.
 backward  both       : b200_tbe_backward_peer loads the gradient row of sample b from rank
                        (b // B_local)'s gradient buffer while it streams the sorted ids, applies 1/W and
                        the fused optimizer.  This is the reverse all-to-all and the all-gather at once.
@@ -68,6 +70,9 @@ class PeerExchange:
         self.stage_bases = None
         if rw_dim > 0:
             self.stage, self._h_stage, st_ptrs = make((self.W, B_local, rw_dim))
+            # kept all-zero between steps: peers store only their non-empty partial bags and
+            # b200_peer_stage_reduce re-zeroes what it consumed (the first forward's barrier A orders this)
+            self.stage.zero_()
             slot = self.rank * B_local * rw_dim * 4  # my slot in every destination's staging buffer
             self.stage_bases = torch.tensor([p + slot for p in st_ptrs], dtype=torch.int64, device=device)
 
@@ -222,10 +227,11 @@ class _PeerLookup(torch.autograd.Function):
             pitch = px.rw_dim if p.row_wise else px.total_D
             _b200.tbe_forward_peer(m.weights_dev, m.weights_offsets, m.D_offsets, m.total_D, m.max_D,
                                    m._all_D_mult8, idx, off, None, int(m.pooling_mode), bases, px.B_local, pitch,
-                                   p.dst_col)
+                                   p.dst_col, skip_empty=p.row_wise)
         px.barrier()  # B: all peer stores have landed
         if px.stage is not None:
-            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4)
+            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4,
+                                    clear_stage=True)
         ctx.px, ctx.work, ctx.sorts = px, work, sorts
         return px.out
 

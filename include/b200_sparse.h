@@ -72,6 +72,16 @@ int b200_permute_data(const int32_t* permute, int32_t Tp, int32_t B,
                       const void* weights, void* out_weights, int weight_bytes,
                       int64_t out_capacity, void* stream);
 
+/* permute_2D_sparse_data in ONE launch for callers that know the permuted total (`out_capacity`;
+ * torchrec passes it: jagged_tensor.py:946 `permuted_lengths_sum`, dist_data.py:257).  A feature
+ * row's B bags are one contiguous value range, so only T per-feature totals are computed (into
+ * `ws`), never per-bag offsets.  T, Tp <= 1024, else B200_EUNSUPPORTED (use the two-step pair). */
+int b200_permute_2d_fused(const int32_t* permute, const void* lengths, int lengths_dtype,
+                          int32_t T, int32_t Tp, int32_t B, void* out_lengths,
+                          const void* values, void* out_values, int value_bytes,
+                          const void* weights, void* out_weights, int weight_bytes,
+                          int64_t out_capacity, void* ws, void* stream);
+
 /* torch.ops.fbgemm.expand_into_jagged_permute (fbgemm_gpu/src/sparse_ops.cu:671-730). */
 int b200_expand_into_jagged_permute(const int32_t* permute, const void* input_offsets,
                                     const void* output_offsets, int dtype, int64_t permute_size,

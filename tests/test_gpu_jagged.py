@@ -40,7 +40,8 @@ def test_permute_2d_reference_vector(ops):
     np.testing.assert_array_equal(ol.cpu().numpy().reshape(-1), [1, 1, 1, 0, 2, 0, 0, 3, 0])
 
 
-@pytest.mark.parametrize("T,B,L", [(3, 5, 4), (26, 512, 1), (7, 33, 40), (1, 1, 0), (4, 1000, 3)])
+@pytest.mark.parametrize("T,B,L", [(3, 5, 4), (26, 512, 1), (7, 33, 40), (1, 1, 0), (4, 1000, 3), (26, 5000, 2),
+                                   (700, 7, 3), (1100, 3, 2)])
 @pytest.mark.parametrize("weighted", [False, True])
 @pytest.mark.parametrize("vdt", [np.int64, np.int32])
 def test_permute_2d_random(ops, T, B, L, weighted, vdt):
@@ -112,7 +113,8 @@ def test_bucketize_reference_long_indices(ops):
         np.testing.assert_array_equal(out[1].cpu().numpy(), ni)
 
 
-@pytest.mark.parametrize("T,B,L,W", [(3, 7, 5, 2), (26, 256, 1, 8), (2, 9, 64, 4), (5, 100, 3, 3)])
+@pytest.mark.parametrize("T,B,L,W", [(3, 7, 5, 2), (26, 256, 1, 8), (2, 9, 64, 4), (5, 100, 3, 3), (26, 4096, 1, 8),
+                                     (6, 3000, 9, 5)])
 @pytest.mark.parametrize("idt", [np.int32, np.int64])
 @pytest.mark.parametrize("extras", [False, True])
 def test_bucketize_random(ops, T, B, L, W, idt, extras):

@@ -49,6 +49,11 @@ CASES = [
     ([20], [1024], 5, 9),
     ([500, 40, 9, 1000], [8, 32, 16, 4], 200, 40),
     ([5000] * 6, [128] * 6, 256, 1),
+    # narrow rows -> packed kernel (several rows per warp instruction): 4-, 8- and 16-lane groups
+    ([200, 3000, 17], [64, 64, 64], 100, 12),
+    ([1000, 30, 555], [32, 16, 8], 77, 1),
+    ([4000, 9], [24, 32], 261, 70),
+    ([300], [16], 1, 5),
 ]
 
 
@@ -71,6 +76,19 @@ def test_forward(ops, case, wdt, idt, mode):
     got16 = ops.tbe_forward(w.cuda(), dev(wo), dev(Do), int(Do[-1]), max(dims), mult8, dev(indices), dev(offsets),
                             dev(psw) if psw is not None else None, 1 if mode == "mean" else 0, torch.float16)
     np.testing.assert_allclose(got16.float().cpu().numpy(), exp, rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("wdt", ["fp32", "fp16"])
+@pytest.mark.parametrize("dims", [[128, 256, 128, 128], [32, 64, 16, 64]])
+def test_forward_large_batch(ops, wdt, dims):
+    """Batches big enough for full 32-bag warp tiles (small batches take 4..16-bag tiles)."""
+    rows, B = [1000] * 4, 60000
+    rng = np.random.default_rng(77)
+    w, wo, Do, hsc = build_tables(rng, rows, dims, wdt)
+    _, offsets, indices = make_jagged(rng, 4, B, 2, rows)
+    exp = R.tbe_forward(w_to_np(w), wo, Do, indices, offsets, False, None)
+    got = ops.tbe_forward(w.cuda(), dev(wo), dev(Do), int(Do[-1]), max(dims), True, dev(indices), dev(offsets), None, 0)
+    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-5, atol=1e-5)
 
 
 BWD_CASES = [
@@ -174,6 +192,25 @@ def test_quantize_and_int8_forward(ops, D):
         got = ops.tbe_int8_forward(dev(packed.reshape(-1)), dev(wo), dev(Do), D, D, 16, dev(indices),
                                    dev(offsets), None, 0, odt)
         np.testing.assert_allclose(got.float().cpu().numpy(), exp, rtol=tol, atol=tol * 10)
+
+
+def test_int8_forward_large_batch(ops):
+    """Full 32-bag warp tiles (the small cases above run with 4-bag tiles)."""
+    rng = np.random.default_rng(5)
+    D, rows, T, B = 128, 300, 2, 160000
+    q = R.quantize_rowwise_8bit_sbhalf(rng.standard_normal((rows, D)).astype(np.float32))
+    rb = R.int8_row_bytes(D)
+    packed = np.zeros((rows, rb), dtype=np.uint8)
+    packed[:, :4] = q[:, D:]
+    packed[:, 4:4 + D] = q[:, :D]
+    flat = np.concatenate([packed.reshape(-1)] * T)
+    Do = np.array([0, D, 2 * D], dtype=np.int32)
+    wo = np.array([0, rows * rb], dtype=np.int64)
+    _, offsets, indices = make_jagged(rng, T, B, 1, [rows] * T, idx_dtype=np.int32)
+    exp = R.tbe_int8_forward(flat, wo, Do, indices, offsets, 16, False, None, np.float32)
+    got = ops.tbe_int8_forward(dev(flat), dev(wo), dev(Do), 2 * D, D, 16, dev(indices), dev(offsets), None, 0,
+                               torch.float32)
+    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-5, atol=1e-4)
 
 
 def test_interaction_golden(ops):

@@ -28,6 +28,7 @@ SIGNATURES = {
     "b200_cumsum": (_int, [_p, _p, _i64, _int, _int, _p, _p]),
     "b200_permute_lengths": (_int, [_p, _p, _int, _i32, _i32, _i32, _p, _p, _p, _p, _p]),
     "b200_permute_data": (_int, [_p, _i32, _i32, _p, _p, _p, _p, _int, _p, _p, _int, _i64, _p]),
+    "b200_permute_2d_fused": (_int, [_p, _p, _int, _i32, _i32, _i32, _p, _p, _p, _int, _p, _p, _int, _i64, _p, _p]),
     "b200_expand_into_jagged_permute": (_int, [_p, _p, _p, _int, _i64, _p, _i64, _p]),
     "b200_offsets_range": (_int, [_p, _int, _i64, _p, _i64, _p]),
     "b200_block_bucketize": (_int, [_p, _int, _p, _int, _p, _i32, _i32, _i32, _i64, _p, _p, _p, _p,

@@ -151,6 +151,19 @@ def permute_sparse_data(
     out_lengths = torch.empty(out_shape, dtype=lengths_c.dtype, device=dev)
     if Tp == 0 or B == 0:
         return out_lengths, values_c.new_empty(0), (None if weights_c is None else weights_c.new_empty(0))
+    if two_d and permuted_lengths_sum is not None and T <= 1024 and Tp <= 1024:
+        # the hot callers (KJT.permute, the input-dist recat) know the total: one fused launch
+        total = int(permuted_lengths_sum)
+        out_values = torch.empty(total, dtype=values_c.dtype, device=dev)
+        out_weights = torch.empty(total, dtype=weights_c.dtype, device=dev) if weights_c is not None else None
+        with torch.cuda.device(dev):
+            KernelProfile.launches += 1
+            check(lib.b200_permute_2d_fused(_p(permute), _p(lengths_c), ldt, T, Tp, B, _p(out_lengths),
+                                            _p(values_c), _p(out_values), values_c.element_size(),
+                                            _p(weights_c), _p(out_weights),
+                                            weights_c.element_size() if weights_c is not None else 4,
+                                            total, _p(_ws(dev)), _stream(dev)), "b200_permute_2d_fused")
+        return out_lengths, out_values, out_weights
     in_off = torch.empty(T * B + 1, dtype=torch.int64, device=dev)
     out_off = torch.empty(Tp * B + 1, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):

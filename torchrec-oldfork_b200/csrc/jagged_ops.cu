@@ -55,26 +55,34 @@ __device__ __forceinline__ int64_t block_reduce_sum(int64_t v, int64_t* s_warp) 
 }
 
 // Exclusive scan of one value per thread across the block; returns the exclusive prefix of
-// this thread and the block total through `total`.
+// this thread and the block total through `total`.  The warp totals are scanned once by warp 0
+// (not summed by every thread): the scan kernels are instruction-bound, not HBM-bound.
 __device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* s_warp, int64_t& total) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (int)(blockDim.x >> 5);
   int64_t inc = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const int64_t n = __shfl_up_sync(kFull, inc, o);
     if (lane >= o) inc += n;
   }
-  __syncthreads();
+  __syncthreads();  // s_warp may still be read by the previous call
   if (lane == 31) s_warp[warp] = inc;
   __syncthreads();
-  int64_t warp_prefix = 0, tot = 0;
-  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
-    const int64_t x = s_warp[w];
-    if (w < warp) warp_prefix += x;
-    tot += x;
+  if (warp == 0) {
+    const int64_t x = lane < nwarps ? s_warp[lane] : 0;
+    int64_t winc = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int64_t n = __shfl_up_sync(kFull, winc, o);
+      if (lane >= o) winc += n;
+    }
+    if (lane < nwarps) s_warp[lane] = winc - x;  // exclusive prefix of warp `lane`
+    if (lane == 31) s_warp[nwarps] = winc;       // block total
   }
-  total = tot;
-  return warp_prefix + inc - v;
+  __syncthreads();
+  total = s_warp[nwarps];
+  return s_warp[warp] + inc - v;
 }
 
 struct Chunk {
@@ -117,22 +125,49 @@ __device__ __forceinline__ int64_t scan_finish_phase(LoadF load, StoreF store, i
   const int64_t grand = block_reduce_sum(all, s_warp);
   const Chunk c = block_chunk(n);
   int64_t running = base0;
+  // Warp-striped arrangement: warp w owns the contiguous 32*kScanItems elements
+  // [tile0 + w*32*kScanItems, ...), lane l holds elements seg + k*32 + l.  Loads and stores are
+  // fully coalesced and the scan costs kScanItems warp scans + one scan of the warp totals.
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t tile0 = c.begin; tile0 < c.end; tile0 += (int64_t)kScanThreads * kScanItems) {
-    const int64_t i0 = tile0 + (int64_t)threadIdx.x * kScanItems;
-    int64_t x[kScanItems];
-    int64_t tsum = 0;
+    const int64_t seg = tile0 + (int64_t)warp * (32 * kScanItems) + lane;
+    int64_t x[kScanItems], pre[kScanItems];
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) x[k] = (seg + 32 * k < c.end) ? load(seg + 32 * k) : 0;
+    int64_t wrun = 0;
 #pragma unroll
     for (int k = 0; k < kScanItems; ++k) {
-      x[k] = (i0 + k < c.end) ? load(i0 + k) : 0;
-      tsum += x[k];
-    }
-    int64_t tile_total;
-    int64_t pre = running + block_exclusive_scan(tsum, s_warp, tile_total);
+      int64_t inc = x[k];
 #pragma unroll
-    for (int k = 0; k < kScanItems; ++k) {
-      if (i0 + k < c.end) store(i0 + k, pre, x[k]);
-      pre += x[k];
+      for (int o = 1; o < 32; o <<= 1) {
+        const int64_t nb = __shfl_up_sync(kFull, inc, o);
+        if (lane >= o) inc += nb;
+      }
+      pre[k] = wrun + inc - x[k];
+      wrun += __shfl_sync(kFull, inc, 31);
     }
+    // exclusive scan of the warp totals (one value per warp, held by every lane)
+    __syncthreads();  // s_warp may still be read by the previous round
+    if (lane == 0) s_warp[warp] = wrun;
+    __syncthreads();
+    if (warp == 0) {
+      const int nwarps = kScanThreads / 32;
+      const int64_t t = lane < nwarps ? s_warp[lane] : 0;
+      int64_t winc = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int64_t nb = __shfl_up_sync(kFull, winc, o);
+        if (lane >= o) winc += nb;
+      }
+      if (lane < nwarps) s_warp[lane] = winc - t;
+      if (lane == 31) s_warp[nwarps] = winc;
+    }
+    __syncthreads();
+    const int64_t wbase = running + s_warp[warp];
+    const int64_t tile_total = s_warp[kScanThreads / 32];
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+      if (seg + 32 * k < c.end) store(seg + 32 * k, wbase + pre[k], x[k]);
     running += tile_total;
   }
   return grand;
@@ -158,7 +193,7 @@ template <typename T>
 __global__ void __launch_bounds__(kScanThreads)
 cumsum_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t n, int mode,
               int64_t* __restrict__ ws) {
-  __shared__ int64_t s_warp[kScanThreads / 32];
+  __shared__ int64_t s_warp[kScanThreads / 32 + 1];
   cg::grid_group grid = cg::this_grid();
   auto load = [&](int64_t i) -> int64_t { return (int64_t)in[i]; };
   scan_reduce_phase(load, n, ws, s_warp);
@@ -179,7 +214,7 @@ permute_lengths_kernel(const int32_t* __restrict__ permute, const T* __restrict_
                        int32_t T_in, int32_t Tp, int32_t B, T* __restrict__ out_lengths,
                        int64_t* __restrict__ in_offsets, int64_t* __restrict__ out_offsets,
                        int64_t* __restrict__ ws) {
-  __shared__ int64_t s_warp[kScanThreads / 32];
+  __shared__ int64_t s_warp[kScanThreads / 32 + 1];
   cg::grid_group grid = cg::this_grid();
   const int64_t n_in = (int64_t)T_in * B, n_out = (int64_t)Tp * B;
   auto load_in = [&](int64_t i) -> int64_t { return (int64_t)lengths[i]; };
@@ -270,6 +305,93 @@ static unsigned grid_for_groups(int64_t segments, int G, int threads) {
   return (unsigned)blocks;
 }
 
+// ---------------------------------------------------------------- permute_2D, fused
+// permute_2D_sparse_data moves whole feature rows: the B bags of input feature permute[tp] are ONE
+// contiguous range of `values`, so only T per-feature totals are needed - not the T*B per-bag
+// offsets the reference (and permute_lengths_kernel above) builds with two device-wide scans.
+// One cooperative launch:  zero T sums | sync | per-feature length sums (warp per 1024-bag piece,
+// one atomic each) | sync | every CTA scans the <= 1024 totals in shared memory, then copies
+// out_lengths (row gather) and the values / weights (flat, binary search over Tp+1 offsets).
+constexpr int kPermMaxFeatures = 1024;
+constexpr int kPermPiece = 1024;
+
+template <typename LT, int VB, int WB>
+__global__ void __launch_bounds__(kScanThreads)
+permute_2d_fused_kernel(const int32_t* __restrict__ permute, const LT* __restrict__ lengths, int32_t T,
+                        int32_t Tp, int32_t B, LT* __restrict__ out_lengths,
+                        const void* __restrict__ values, void* __restrict__ out_values,
+                        const void* __restrict__ weights, void* __restrict__ out_weights,
+                        int64_t out_capacity, int64_t* __restrict__ ws) {
+  using V = typename RawT<VB>::type;
+  using Wt = typename RawT<WB>::type;
+  __shared__ int64_t s_in[kPermMaxFeatures + 1];
+  __shared__ int64_t s_out[kPermMaxFeatures + 1];
+  __shared__ int64_t s_warp[kScanThreads / 32 + 1];
+  cg::grid_group grid = cg::this_grid();
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+
+  for (int64_t i = tid; i < T; i += nthreads) ws[i] = 0;
+  grid.sync();
+
+  // per-feature totals
+  const int pieces_per_row = (int)ceil_div(B, kPermPiece);
+  const int64_t n_pieces = (int64_t)T * pieces_per_row;
+  for (int64_t pc = tid >> 5; pc < n_pieces; pc += nthreads >> 5) {
+    const int t = (int)(pc / pieces_per_row);
+    const int b_lo = (int)(pc - (int64_t)t * pieces_per_row) * kPermPiece;
+    const int b_hi = min(B, b_lo + kPermPiece);
+    const LT* __restrict__ row = lengths + (int64_t)t * B;
+    int64_t v = 0;
+    for (int b = b_lo + lane; b < b_hi; b += 32 * 8) {
+      LT x[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) x[k] = (b + 32 * k < b_hi) ? row[b + 32 * k] : (LT)0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v += (int64_t)x[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    if (lane == 0 && v != 0) atomicAdd((unsigned long long*)&ws[t], (unsigned long long)v);
+  }
+  grid.sync();
+
+  // feature offsets of the input and of the permuted output (every CTA computes its own copy)
+  {
+    const int i0 = 2 * threadIdx.x, i1 = i0 + 1;
+    const int64_t a0 = i0 < T ? ws[i0] : 0, a1 = i1 < T ? ws[i1] : 0;
+    int64_t tot;
+    const int64_t pre = block_exclusive_scan(a0 + a1, s_warp, tot);
+    if (i0 < T) s_in[i0] = pre;
+    if (i1 < T) s_in[i1] = pre + a0;
+    if (threadIdx.x == 0) s_in[T] = tot;
+    const int64_t c0 = i0 < Tp ? ws[permute[i0]] : 0, c1 = i1 < Tp ? ws[permute[i1]] : 0;
+    const int64_t pre2 = block_exclusive_scan(c0 + c1, s_warp, tot);
+    if (i0 < Tp) s_out[i0] = pre2;
+    if (i1 < Tp) s_out[i1] = pre2 + c0;
+    if (threadIdx.x == 0) s_out[Tp] = tot;
+  }
+  __syncthreads();
+
+  const int64_t n_out_len = (int64_t)Tp * B;
+  for (int64_t i = tid; i < n_out_len; i += nthreads) {
+    const int64_t tp = i / B;
+    out_lengths[i] = lengths[(int64_t)permute[tp] * B + (i - tp * B)];
+  }
+  const int64_t total = min(s_out[Tp], out_capacity);
+  for (int64_t j = tid; j < total; j += nthreads) {
+    int lo = 0, hi = Tp;  // largest tp with s_out[tp] <= j  (empty features are skipped)
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (s_out[mid] <= j) lo = mid; else hi = mid;
+    }
+    const int64_t src = s_in[permute[lo]] + (j - s_out[lo]);
+    reinterpret_cast<V*>(out_values)[j] = reinterpret_cast<const V*>(values)[src];
+    if (weights) reinterpret_cast<Wt*>(out_weights)[j] = reinterpret_cast<const Wt*>(weights)[src];
+  }
+}
+
 // ---------------------------------------------------------------- expand_into_jagged_permute
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -312,6 +434,23 @@ __device__ __forceinline__ void bucket_of(index_t raw, index_t blk, int32_t W, u
   const u idx = (u)raw;
   const u ublk = (u)blk;
   const u bound = (u)(blk * (index_t)W);  // same wrap-around as the reference's index_t product
+  if constexpr (sizeof(index_t) == 8) {
+    // ids and block sizes almost always fit 32 bits: a 32-bit divide is ~5x cheaper than the
+    // emulated 64-bit one
+    if (((idx | ublk) >> 32) == 0) {
+      const uint32_t i32 = (uint32_t)idx, b32 = (uint32_t)ublk;
+      if (idx < bound) {
+        const uint32_t q = i32 / b32;
+        p = q;
+        new_idx = i32 - q * b32;
+      } else {
+        const uint32_t q = i32 / (uint32_t)W;
+        p = i32 - q * (uint32_t)W;
+        new_idx = q;
+      }
+      return;
+    }
+  }
   if (idx < bound) {
     p = (uint64_t)(idx / ublk);
     new_idx = (uint64_t)(idx % ublk);
@@ -319,6 +458,12 @@ __device__ __forceinline__ void bucket_of(index_t raw, index_t blk, int32_t W, u
     p = (uint64_t)(idx % (u)W);
     new_idx = (uint64_t)(idx / (u)W);
   }
+}
+
+// i / d for non-negative int64 operands, through a 32-bit divide when both fit
+__device__ __forceinline__ int64_t fast_div(int64_t i, int64_t d) {
+  if (((uint64_t)(i | d) >> 32) == 0) return (int64_t)((uint32_t)i / (uint32_t)d);
+  return i / d;
 }
 
 template <typename offset_t, typename index_t>
@@ -330,7 +475,7 @@ block_bucketize_kernel(const offset_t* __restrict__ lengths, const index_t* __re
                        index_t* __restrict__ new_pos, index_t* __restrict__ unbucketize_permute,
                        int64_t* __restrict__ offsets, int64_t* __restrict__ new_offsets,
                        bool warp_per_row, int64_t* __restrict__ ws) {
-  __shared__ int64_t s_warp[kScanThreads / 32];
+  __shared__ int64_t s_warp[kScanThreads / 32 + 1];
   cg::grid_group grid = cg::this_grid();
   const int64_t TB = (int64_t)T * B;
   const int64_t WTB = TB * W;
@@ -428,6 +573,89 @@ block_bucketize_kernel(const offset_t* __restrict__ lengths, const index_t* __re
           if (lane == (31 - __clz(peers))) *cur = base + __popc(peers);
         }
         __syncwarp();
+      }
+    }
+  }
+}
+
+// Short-bag variant (average bag <= 8 ids, e.g. Criteo's 1 id per bag, and N < 2^31): thread per
+// bag; the scan of the W*T*B bucket counters is kept as int32 positions (the generic kernel writes
+// and re-reads them as int64) and the per-element work of that scan is a plain coalesced store:
+//   R1 | sync | F1: offsets[bt] = scan(lengths) and, in the same pass, the W bucket counts of bag
+//   bt -> new_lengths (coalesced over bt) | sync | R2 | sync | F2: pos32 = exclusive scan of
+//   new_lengths | sync | P3: thread per bag scatters its ids to pos32[bucket][bag] (+ rank in bag).
+template <typename offset_t, typename index_t>
+__global__ void __launch_bounds__(kScanThreads)
+block_bucketize_short_kernel(const offset_t* __restrict__ lengths, const index_t* __restrict__ indices,
+                             const index_t* __restrict__ block_sizes, int32_t T, int32_t B, int32_t W,
+                             const float* __restrict__ weights, offset_t* __restrict__ new_lengths,
+                             index_t* __restrict__ new_indices, float* __restrict__ new_weights,
+                             index_t* __restrict__ new_pos, index_t* __restrict__ unbucketize_permute,
+                             int64_t* __restrict__ offsets, int32_t* __restrict__ pos32,
+                             int64_t* __restrict__ ws) {
+  __shared__ int64_t s_warp[kScanThreads / 32 + 1];
+  cg::grid_group grid = cg::this_grid();
+  const int64_t TB = (int64_t)T * B;
+  const int64_t WTB = TB * W;
+
+  auto load_len = [&](int64_t i) -> int64_t { return (int64_t)lengths[i]; };
+  scan_reduce_phase(load_len, TB, ws, s_warp);
+  grid.sync();
+  const int64_t total = scan_finish_phase(
+      load_len,
+      [&](int64_t bt, int64_t pre, int64_t len) {
+        offsets[bt] = pre;
+        const index_t blk = block_sizes[fast_div(bt, B)];
+        if (len == 1) {  // the common case: one coalesced pass, no read-modify-write
+          uint64_t p, ni;
+          bucket_of<index_t>(indices[pre], blk, W, p, ni);
+          for (int32_t q = 0; q < W; ++q) new_lengths[(int64_t)q * TB + bt] = (offset_t)(q == (int32_t)p);
+        } else {
+          for (int32_t q = 0; q < W; ++q) new_lengths[(int64_t)q * TB + bt] = 0;
+          for (int64_t i = pre; i < pre + len; ++i) {
+            uint64_t p, ni;
+            bucket_of<index_t>(indices[i], blk, W, p, ni);
+            new_lengths[(int64_t)p * TB + bt] += 1;  // own cells only
+          }
+        }
+      },
+      TB, ws, s_warp);
+  if (blockIdx.x == 0 && threadIdx.x == 0) offsets[TB] = total;
+  grid.sync();
+
+  auto load_nl = [&](int64_t i) -> int64_t { return (int64_t)new_lengths[i]; };
+  scan_reduce_phase(load_nl, WTB, ws + kMaxCoopBlocks, s_warp);
+  grid.sync();
+  scan_finish_phase(
+      load_nl, [&](int64_t i, int64_t pre, int64_t) { pos32[i] = (int32_t)pre; }, WTB,
+      ws + kMaxCoopBlocks, s_warp);
+  grid.sync();
+
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t bt = tid; bt < TB; bt += nthreads) {
+    const int64_t s = offsets[bt], e = offsets[bt + 1];
+    if (e <= s) continue;
+    const index_t blk = block_sizes[fast_div(bt, B)];
+    if (e - s == 1) {
+      uint64_t p, ni;
+      bucket_of<index_t>(indices[s], blk, W, p, ni);
+      const int64_t pos = pos32[(int64_t)p * TB + bt];
+      new_indices[pos] = (index_t)ni;
+      if (unbucketize_permute) unbucketize_permute[s] = (index_t)pos;
+      if (new_weights) new_weights[pos] = weights[s];
+      if (new_pos) new_pos[pos] = 0;
+    } else {
+      for (int64_t k = s; k < e; ++k) {
+        uint64_t p, ni;
+        bucket_of<index_t>(indices[k], blk, W, p, ni);
+        int32_t* cur = pos32 + (int64_t)p * TB + bt;  // own cells only
+        const int64_t pos = *cur;
+        *cur = (int32_t)(pos + 1);
+        new_indices[pos] = (index_t)ni;
+        if (unbucketize_permute) unbucketize_permute[k] = (index_t)pos;
+        if (new_weights) new_weights[pos] = weights[k];
+        if (new_pos) new_pos[pos] = (index_t)(k - s);
       }
     }
   }
@@ -651,6 +879,71 @@ extern "C" int b200_permute_data(const int32_t* permute, int32_t Tp, int32_t B,
   }
 }
 
+template <typename LT, int VB>
+static int permute_2d_fused_w(int weight_bytes, cudaStream_t s, int64_t work, const int32_t* permute,
+                              const LT* lengths, int32_t T, int32_t Tp, int32_t B, LT* out_lengths,
+                              const void* values, void* out_values, const void* weights,
+                              void* out_weights, int64_t cap, int64_t* ws) {
+  switch (weights ? weight_bytes : 4) {
+    case 2:
+      return coop_launch(permute_2d_fused_kernel<LT, VB, 2>, work, s, permute, lengths, T, Tp, B,
+                         out_lengths, values, out_values, weights, out_weights, cap, ws);
+    case 4:
+      return coop_launch(permute_2d_fused_kernel<LT, VB, 4>, work, s, permute, lengths, T, Tp, B,
+                         out_lengths, values, out_values, weights, out_weights, cap, ws);
+    case 8:
+      return coop_launch(permute_2d_fused_kernel<LT, VB, 8>, work, s, permute, lengths, T, Tp, B,
+                         out_lengths, values, out_values, weights, out_weights, cap, ws);
+    default:
+      return B200_EINVAL;
+  }
+}
+
+template <typename LT>
+static int permute_2d_fused_v(int value_bytes, int weight_bytes, cudaStream_t s, int64_t work,
+                              const int32_t* permute, const LT* lengths, int32_t T, int32_t Tp,
+                              int32_t B, LT* out_lengths, const void* values, void* out_values,
+                              const void* weights, void* out_weights, int64_t cap, int64_t* ws) {
+#define B200_PF(VB)                                                                                 \
+  return permute_2d_fused_w<LT, VB>(weight_bytes, s, work, permute, lengths, T, Tp, B, out_lengths, \
+                                    values, out_values, weights, out_weights, cap, ws)
+  switch (value_bytes) {
+    case 1:
+      B200_PF(1);
+    case 2:
+      B200_PF(2);
+    case 4:
+      B200_PF(4);
+    case 8:
+      B200_PF(8);
+    default:
+      return B200_EINVAL;
+  }
+#undef B200_PF
+}
+
+extern "C" int b200_permute_2d_fused(const int32_t* permute, const void* lengths, int lengths_dtype,
+                                     int32_t T, int32_t Tp, int32_t B, void* out_lengths,
+                                     const void* values, void* out_values, int value_bytes,
+                                     const void* weights, void* out_weights, int weight_bytes,
+                                     int64_t out_capacity, void* ws, void* stream) {
+  if (T < 0 || Tp < 0 || B < 0 || out_capacity < 0) return B200_EINVAL;
+  if (T > kPermMaxFeatures || Tp > kPermMaxFeatures) return B200_EUNSUPPORTED;
+  if (Tp == 0 || B == 0) return B200_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t nlen = (int64_t)(T > Tp ? T : Tp) * B;
+  const int64_t work = nlen > out_capacity ? nlen : out_capacity;
+  if (lengths_dtype == B200_I32)
+    return permute_2d_fused_v<int32_t>(value_bytes, weight_bytes, s, work, permute,
+                                       (const int32_t*)lengths, T, Tp, B, (int32_t*)out_lengths, values,
+                                       out_values, weights, out_weights, out_capacity, (int64_t*)ws);
+  if (lengths_dtype == B200_I64)
+    return permute_2d_fused_v<int64_t>(value_bytes, weight_bytes, s, work, permute,
+                                       (const int64_t*)lengths, T, Tp, B, (int64_t*)out_lengths, values,
+                                       out_values, weights, out_weights, out_capacity, (int64_t*)ws);
+  return B200_EINVAL;
+}
+
 extern "C" int b200_expand_into_jagged_permute(const int32_t* permute, const void* input_offsets,
                                                const void* output_offsets, int dtype,
                                                int64_t permute_size, void* output_permute,
@@ -698,6 +991,12 @@ static int bucketize_launch(const void* lengths, const void* indices, const void
                             void* unbucketize_permute, int64_t* offsets, int64_t* new_offsets,
                             int64_t* ws, cudaStream_t s) {
   const int64_t TB = (int64_t)T * B;
+  if (TB > 0 && N <= 8 * TB && N < 0x7fffffffLL)  // short bags: thread per bag, int32 positions
+    return coop_launch(block_bucketize_short_kernel<offset_t, index_t>, TB * W, s,
+                       (const offset_t*)lengths, (const index_t*)indices, (const index_t*)block_sizes,
+                       T, B, W, weights, (offset_t*)new_lengths, (index_t*)new_indices, new_weights,
+                       (index_t*)new_pos, (index_t*)unbucketize_permute, offsets,
+                       (int32_t*)new_offsets, ws);
   const bool warp_per_row = TB > 0 && (N / TB) >= 16;
   const int64_t work = warp_per_row ? TB * 32 : (TB * W > N ? TB * W : N);
   return coop_launch(block_bucketize_kernel<offset_t, index_t>, work, s, (const offset_t*)lengths,

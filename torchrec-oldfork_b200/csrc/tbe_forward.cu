@@ -85,7 +85,7 @@ template <typename W, typename O, int EPV, int NV, bool PEER>
 __global__ void __launch_bounds__(kFwdThreads)
 tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ weights_offsets,
                    const int32_t* __restrict__ D_offsets, int32_t T, int32_t B, int32_t total_D,
-                   int32_t tiles_per_table, const void* __restrict__ indices,
+                   int32_t tiles_per_table, int32_t bpt, const void* __restrict__ indices,
                    const void* __restrict__ offsets, bool idx64,
                    const float* __restrict__ psw, bool mean, O* __restrict__ out, FwdPeerDst peer) {
   constexpr int kStages = FwdRing<NV>::kStages;
@@ -97,8 +97,8 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
   const int64_t tile = (int64_t)blockIdx.x * kFwdWarps + warp;
   if (tile >= (int64_t)T * tiles_per_table) return;
   const int t = (int)(tile / tiles_per_table);
-  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
-  const int nb = min(32, B - b0);
+  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * bpt;
+  const int nb = min(bpt, B - b0);  // bags of this tile (lane k <-> bag k; lanes >= nb are idle)
   const int D_begin = D_offsets[t];
   const int D = D_offsets[t + 1] - D_begin;
   const W* __restrict__ wtab = weights + weights_offsets[t];
@@ -265,7 +265,10 @@ static int launch_forward_nv(const void* weights, const int64_t* weights_offsets
                              int32_t max_D, const void* indices, const void* offsets, bool idx64,
                              const float* psw, bool mean, void* output, const FwdPeerDst* peer,
                              cudaStream_t s) {
-  const int tiles_per_table = (B + 31) / 32;
+  // bags per warp tile: 32, fewer when the batch is too small to fill 148 SMs x 48 warps
+  int bpt = 32;
+  while (bpt > 4 && (int64_t)T * ceil_div(B, bpt) < (int64_t)kNumSMs * 48) bpt >>= 1;
+  const int tiles_per_table = (int)ceil_div(B, bpt);
   const int64_t tiles = (int64_t)T * tiles_per_table;
   const int64_t grid = ceil_div(tiles, kFwdThreads / 32);
   if (grid == 0) return B200_OK;
@@ -275,12 +278,12 @@ static int launch_forward_nv(const void* weights, const int64_t* weights_offsets
   if (peer)                                                                                     \
     tbe_forward_kernel<W, O, EPV, NV, true>                                                      \
         <<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>(               \
-            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table,       \
+            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table, bpt,  \
             indices, offsets, idx64, psw, mean, nullptr, *peer);                                 \
   else                                                                                          \
     tbe_forward_kernel<W, O, EPV, NV, false>                                                     \
         <<<(unsigned)grid, kFwdThreads, kFwdWarps * FwdRing<NV>::kWarpBytes, s>>>(               \
-            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table,       \
+            (const W*)weights, weights_offsets, D_offsets, T, B, total_D, tiles_per_table, bpt,  \
             indices, offsets, idx64, psw, mean, (O*)output, FwdPeerDst{})
   if (vecs <= 1)
     B200_FWD_LAUNCH(1);
@@ -315,6 +318,12 @@ static int launch_forward_out(int output_dtype, const void* weights, const int64
   }
 }
 
+// tbe_forward_packed.cu: rows of <= 256 bytes, several rows per warp instruction
+int launch_forward_packed(int weight_dtype, int output_dtype, bool all_D_mult8, const void* weights,
+                          const int64_t* wo, const int32_t* Do, int32_t T, int32_t B, int32_t total_D,
+                          int32_t max_D, const void* indices, const void* offsets, bool idx64,
+                          const float* psw, bool mean, void* out, cudaStream_t s);
+
 }  // namespace b200
 
 static int tbe_forward_impl(const void* weights, int weight_dtype,
@@ -331,6 +340,12 @@ static int tbe_forward_impl(const void* weights, int weight_dtype,
   const bool idx64 = index_dtype == B200_I64;
   const bool mean = pooling_mode == B200_POOL_MEAN;
   cudaStream_t s = (cudaStream_t)stream;
+  if (!peer) {
+    const int r = launch_forward_packed(weight_dtype, output_dtype, all_D_mult8 != 0, weights,
+                                        weights_offsets, D_offsets, T, B, total_D, max_D, indices,
+                                        offsets, idx64, per_sample_weights, mean, output, s);
+    if (r != B200_EUNSUPPORTED) return r;
+  }
   switch (weight_dtype) {
     case B200_F32:
       return launch_forward_out<float, 4>(output_dtype, weights, weights_offsets, D_offsets, T, B,

@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(kI8Threads)
 tbe_int8_forward_kernel(const uint8_t* __restrict__ weights,
                         const int64_t* __restrict__ weights_offsets,
                         const int32_t* __restrict__ D_offsets, int32_t T, int32_t B,
-                        int32_t total_D, int32_t tiles_per_table, int32_t row_alignment,
+                        int32_t total_D, int32_t tiles_per_table, int32_t bpt, int32_t row_alignment,
                         const void* __restrict__ indices, const void* __restrict__ offsets,
                         bool idx64, const float* __restrict__ psw, bool mean,
                         O* __restrict__ out) {
@@ -42,8 +42,8 @@ tbe_int8_forward_kernel(const uint8_t* __restrict__ weights,
   const int64_t tile = (int64_t)blockIdx.x * (kI8Threads / 32) + (threadIdx.x >> 5);
   if (tile >= (int64_t)T * tiles_per_table) return;
   const int t = (int)(tile / tiles_per_table);
-  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
-  const int nb = min(32, B - b0);
+  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * bpt;
+  const int nb = min(bpt, B - b0);  // bags of this tile (lane k <-> bag k; lanes >= nb are idle)
   const int D_begin = D_offsets[t];
   const int D = D_offsets[t + 1] - D_begin;
   const int64_t row_bytes = ((int64_t)(D + 4) + row_alignment - 1) / row_alignment * row_alignment;
@@ -202,11 +202,11 @@ quantize_rowwise_8bit_sbhalf_kernel(const float* __restrict__ in, int64_t nrows,
 template <typename O>
 static int int8_launch(int vecs, unsigned grid, cudaStream_t s, const uint8_t* weights,
                        const int64_t* wo, const int32_t* Do, int32_t T, int32_t B, int32_t total_D,
-                       int32_t tiles, int32_t align, const void* indices, const void* offsets,
+                       int32_t tiles, int32_t bpt, int32_t align, const void* indices, const void* offsets,
                        bool idx64, const float* psw, bool mean, void* out) {
 #define B200_I8(NV)                                                                           \
   tbe_int8_forward_kernel<O, NV><<<grid, kI8Threads, 0, s>>>(weights, wo, Do, T, B, total_D,  \
-                                                            tiles, align, indices, offsets,  \
+                                                            tiles, bpt, align, indices, offsets, \
                                                             idx64, psw, mean, (O*)out)
   if (vecs <= 1)
     B200_I8(1);
@@ -244,7 +244,11 @@ extern "C" int b200_tbe_int8_forward(const uint8_t* weights, const int64_t* weig
   if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
   if (row_alignment < 16 || (row_alignment % 16) != 0 || (total_D % 4) != 0) return B200_EINVAL;
   if (T == 0 || B == 0) return B200_OK;
-  const int tiles = (B + 31) / 32;
+  // bags per warp tile: 32 for big batches; small inference batches (cfg5: 26 x 4096 bags) get
+  // smaller tiles so that the grid still fills 148 SMs x 64 warps
+  int bpt = 32;
+  while (bpt > 4 && (int64_t)T * ceil_div(B, bpt) < (int64_t)kNumSMs * 64) bpt >>= 1;
+  const int tiles = (int)ceil_div(B, bpt);
   const unsigned grid = (unsigned)ceil_div((int64_t)T * tiles, kI8Threads / 32);
   const int vecs = (int)ceil_div(max_D + 4, 16 * 32);
   cudaStream_t s = (cudaStream_t)stream;
@@ -252,11 +256,11 @@ extern "C" int b200_tbe_int8_forward(const uint8_t* weights, const int64_t* weig
   const bool mean = pooling_mode == B200_POOL_MEAN;
   if (output_dtype == B200_F16)
     return int8_launch<__half>(vecs, grid, s, weights, weights_offsets, D_offsets, T, B, total_D,
-                               tiles, row_alignment, indices, offsets, idx64, per_sample_weights,
-                               mean, output);
+                               tiles, bpt, row_alignment, indices, offsets, idx64,
+                               per_sample_weights, mean, output);
   if (output_dtype == B200_F32)
     return int8_launch<float>(vecs, grid, s, weights, weights_offsets, D_offsets, T, B, total_D,
-                              tiles, row_alignment, indices, offsets, idx64, per_sample_weights,
-                              mean, output);
+                              tiles, bpt, row_alignment, indices, offsets, idx64,
+                              per_sample_weights, mean, output);
   return B200_EUNSUPPORTED;
 }

@@ -203,6 +203,19 @@ int b200_interaction_backward(const float* dense, const float* sparse, const flo
 int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsum /*[W+1]*/,
                           int32_t W, int32_t B_local, int forward, float scale, void* stream);
 
+/* ---------------------------------------------------------------- dense-layer glue
+ *
+ * Backward of the ReLU + bias of one Linear+ReLU layer (torchrec/modules/mlp.py Perceptron :19-79;
+ * PyTorch: threshold_backward + sum(dim=0)) in ONE pass over the gradient:
+ *   grad_pre[b, n] = grad_out[b, n] * (out[b, n] > 0),  grad_bias[n] = sum_b grad_pre[b, n].
+ * grad_out / out are [B, N] fp32 with row strides in elements (multiples of 4); grad_pre is dense
+ * [B, N]; N % 4 == 0, N <= 1024.  Deterministic (per-CTA partial sums added in a fixed order in
+ * `scratch`, b200_relu_bias_grad_scratch_bytes(N) bytes).  The layer's GEMMs stay on cuBLAS. */
+size_t b200_relu_bias_grad_scratch_bytes(int32_t N);
+int b200_relu_bias_grad(const float* grad_out, int64_t grad_out_stride, const float* out,
+                        int64_t out_stride, int64_t B, int32_t N, float* grad_pre,
+                        float* grad_bias, float* scratch, void* stream);
+
 /* ---------------------------------------------------------------- fused lookup + exchange (NVLink peer memory)
  *
  * One process per GPU; every rank maps its peers' buffers (CUDA IPC / symmetric memory) and passes

@@ -237,6 +237,66 @@ def test_interaction_row_pitch_and_pitched_linear():
     assert torch.count_nonzero(wf[:, width:]) == 0 and lin.weight.stride() == (480, 1)
 
 
+@pytest.mark.parametrize("B,N", [(1, 4), (70, 96), (4097, 128), (3000, 1024), (513, 512), (100, 20)])
+def test_relu_bias_grad_kernel(B, N):
+    """One-pass ReLU backward + bias gradient against threshold_backward + sum(0)."""
+    from b200_sparse import ops
+    torch.manual_seed(B + N)
+    y = torch.relu(torch.randn(B, N, device="cuda"))
+    gy = torch.randn(B, N, device="cuda")
+    g, gb = ops.relu_bias_grad(gy, y)
+    ref = gy * (y > 0)
+    assert torch.equal(g, ref)  # a select, no arithmetic: bit-exact
+    torch.testing.assert_close(gb, ref.sum(0), rtol=1e-5, atol=1e-4 * max(1.0, B ** 0.5))
+    g2, gb2 = ops.relu_bias_grad(gy, y)
+    assert torch.equal(gb, gb2)  # deterministic
+    # strided (row-pitched) inputs are consumed in place
+    pad = torch.randn(B, N + 4, device="cuda")
+    g3, gb3 = ops.relu_bias_grad(pad[:, :N], y)
+    assert torch.equal(g3, pad[:, :N] * (y > 0))
+
+
+def test_fused_perceptron_matches_linear_relu():
+    """MLP with the fused bias+ReLU epilogue / one-pass backward against nn.Linear + relu + autograd
+    (reference torchrec/modules/mlp.py semantics), including the row-pitched 479-wide first layer."""
+    from torchrec.modules.mlp import MLP, mark_zero_padded
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+    B, K, sizes = 257, 479, [64, 128, 32]
+    mlp = MLP(K, sizes, device=torch.device("cuda"))
+    refs = []
+    k = K
+    for i, n in enumerate(sizes):
+        lin = torch.nn.Linear(k, n, device="cuda")
+        with torch.no_grad():
+            lin.weight.copy_(mlp._mlp[i]._linear.weight)
+            lin.bias.copy_(mlp._mlp[i]._linear.bias)
+        refs.append(lin)
+        k = n
+    buf = torch.zeros(B, 480, device="cuda")
+    buf[:, :K].normal_()
+    for pitched in (False, True):
+        x = buf[:, :K] if pitched else buf[:, :K].contiguous()
+        x = x.detach().requires_grad_(True)
+        xin = mark_zero_padded(x) if pitched else x
+        y = mlp(xin)
+        xr = buf[:, :K].contiguous().requires_grad_(True)
+        h = xr
+        for lin in refs:
+            h = torch.relu(lin(h))
+        gy = torch.randn_like(y)
+        for m in list(mlp.parameters()) + [p for lin in refs for p in lin.parameters()]:
+            m.grad = None
+        y.backward(gy)
+        h.backward(gy)
+        torch.testing.assert_close(y, h, rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(x.grad, xr.grad, rtol=1e-4, atol=1e-5)
+        for i, lin in enumerate(refs):
+            torch.testing.assert_close(mlp._mlp[i]._linear.weight.grad, lin.weight.grad, rtol=1e-4, atol=1e-4)
+            torch.testing.assert_close(mlp._mlp[i]._linear.bias.grad, lin.bias.grad, rtol=1e-4, atol=1e-4)
+    torch.backends.cuda.matmul.allow_tf32 = True
+
+
 def test_train_pipeline_sparse_dist_matches_sequential(pg):
     """TrainPipelineSparseDist (H2D | input dist | step, three batches in flight) produces the same losses
     and weights as stepping through the same pinned host batches one by one."""

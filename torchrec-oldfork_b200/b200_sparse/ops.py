@@ -536,6 +536,27 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     return gd, gs
 
 
+# ------------------------------------------------------------------------ dense-layer glue
+def relu_bias_grad(grad_out: torch.Tensor, out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(grad_out * (out > 0), its column sums) in one pass - backward of ReLU + bias of a Linear+ReLU layer."""
+    dev = _need_cuda(grad_out, out)
+    if grad_out.dtype != torch.float32 or out.dtype != torch.float32 or grad_out.dim() != 2:
+        raise TypeError("relu_bias_grad expects 2-D float32 tensors")
+    if grad_out.stride(1) != 1 or grad_out.stride(0) % 4 or grad_out.data_ptr() % 16:
+        grad_out = grad_out.contiguous()
+    if out.stride(1) != 1 or out.stride(0) % 4 or out.data_ptr() % 16:
+        out = out.contiguous()
+    B, N = grad_out.shape
+    g = torch.empty((B, N), dtype=torch.float32, device=dev)
+    gb = torch.empty(N, dtype=torch.float32, device=dev)
+    scratch = torch.empty(lib.b200_relu_bias_grad_scratch_bytes(N) // 4, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        KernelProfile.launches += 2
+        check(lib.b200_relu_bias_grad(_p(grad_out), grad_out.stride(0), _p(out), out.stride(0), B, N, _p(g), _p(gb),
+                                      _p(scratch), _stream(dev)), "b200_relu_bias_grad")
+    return g, gb
+
+
 # ------------------------------------------------------------------------ pooled a2a layout
 def pooled_a2a_recat(src: torch.Tensor, dim_cumsum: torch.Tensor, B_local: int, forward: bool,
                      scale: float = 1.0) -> torch.Tensor:

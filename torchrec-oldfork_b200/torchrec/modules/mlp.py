@@ -22,6 +22,43 @@ def _pitch(width: int) -> int:
     return (width + 3) // 4 * 4
 
 
+def _fusable(x: torch.Tensor, out_features: int, bias) -> bool:
+    return (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and bias is not None and
+            out_features % 4 == 0 and out_features <= 1024 and x.shape[0] > 0)
+
+
+class _LinearReLUFn(torch.autograd.Function):
+    """relu(x W^T + b).  Forward: one cuBLASLt GEMM with the bias + ReLU epilogue
+    (torch._addmm_activation).  Backward: ReLU mask and bias gradient in one pass over grad
+    (b200_relu_bias_grad) instead of threshold_backward + sum(0); the two GEMMs stay on cuBLAS.
+    `pitch` > 0: x and W are views of zero-padded buffers with that row pitch (RowPitchedLinear)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, pitch: int):
+        K = x.shape[1]
+        if pitch:
+            x = x.as_strided((x.shape[0], pitch), (pitch, 1), x.storage_offset())
+            weight = weight.as_strided((weight.shape[0], pitch), (pitch, 1), weight.storage_offset())
+        elif not x.is_contiguous():
+            x = x.contiguous()
+        y = torch._addmm_activation(bias, x, weight.t(), use_gelu=False)
+        ctx.save_for_backward(x, weight, y)
+        ctx.K = K
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        from b200_sparse import ops as _b200
+        x, weight, y = ctx.saved_tensors
+        g, gb = _b200.relu_bias_grad(gy, y)
+        gx = gw = None
+        if ctx.needs_input_grad[0]:
+            gx = (g @ weight)[:, :ctx.K]  # pitched: the pad column is g . 0 = 0
+        if ctx.needs_input_grad[1]:
+            gw = (g.t() @ x)[:, :ctx.K]
+        return gx, gw, (gb if ctx.needs_input_grad[2] else None), None
+
+
 class _PitchedLinearFn(torch.autograd.Function):
     """y = x W^T + b on the pitch-wide buffers behind x [B, K] and W [N, K] (pad columns are zero)."""
 
@@ -73,13 +110,25 @@ class RowPitchedLinear(nn.Linear):
         self._repitch()
         return r
 
-    def forward(self, input: torch.Tensor) -> torch.Tensor:
+    def _pitched_input(self, input: torch.Tensor) -> bool:
         Kp = _pitch(self.in_features)
-        if (Kp != self.in_features and input.is_cuda and input.dim() == 2 and input.dtype == torch.float32 and
+        return (Kp != self.in_features and input.is_cuda and input.dim() == 2 and input.dtype == torch.float32 and
                 getattr(input, ZERO_PADDED_ATTR, False) and input.stride(1) == 1 and input.stride(0) == Kp and
-                input.storage_offset() % 4 == 0 and self._pitched()):
+                input.storage_offset() % 4 == 0 and self._pitched())
+
+    def forward(self, input: torch.Tensor) -> torch.Tensor:
+        if self._pitched_input(input):
             return _PitchedLinearFn.apply(input, self.weight, self.bias)
         return F.linear(input, self.weight, self.bias)
+
+    def forward_relu(self, input: torch.Tensor) -> torch.Tensor:
+        """relu(linear(input)) with the bias + ReLU fused into the GEMM epilogue and a one-pass backward."""
+        if _fusable(input, self.out_features, self.bias):
+            if self._pitched_input(input):
+                return _LinearReLUFn.apply(input, self.weight, self.bias, _pitch(self.in_features))
+            if self.weight.is_contiguous():
+                return _LinearReLUFn.apply(input, self.weight, self.bias, 0)
+        return torch.relu(self.forward(input))
 
 
 class Perceptron(nn.Module):
@@ -92,6 +141,8 @@ class Perceptron(nn.Module):
         self._activation_fn = activation
 
     def forward(self, input: torch.Tensor) -> torch.Tensor:
+        if self._activation_fn is torch.relu or isinstance(self._activation_fn, nn.ReLU):
+            return self._linear.forward_relu(input)
         return self._activation_fn(self._linear(input))
 
 

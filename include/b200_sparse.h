@@ -203,6 +203,16 @@ int b200_interaction_backward(const float* dense, const float* sparse, const flo
 int b200_pooled_a2a_recat(const float* src, float* dst, const int32_t* dim_cumsum /*[W+1]*/,
                           int32_t W, int32_t B_local, int forward, float scale, void* stream);
 
+/* Sequence (non-pooled, PoolingMode.NONE) embeddings - split_embedding_nobag_codegen_forward /
+ * backward kernels of the reference (codegen/embedding_forward_split_template.cu `nobag` variants).
+ * out[p] = indices[p] + hash_size_cumsum[t(p)], t(p) = the feature whose id range
+ * [offsets[t*B], offsets[(t+1)*B]) holds position p.  With all tables of one dim D laid back to
+ * back this is the row number in ONE virtual table, and the sequence lookup / fused backward are
+ * b200_tbe_forward / b200_tbe_sort_indices / b200_tbe_backward with T = 1, B = N, L = 1. */
+int b200_linearize_seq_indices(const void* indices, const void* offsets, int index_dtype,
+                               const int64_t* hash_size_cumsum /*[T+1]*/, int32_t T, int32_t B,
+                               int64_t N, int64_t* out, void* stream);
+
 /* ---------------------------------------------------------------- dense-layer glue
  *
  * Backward of the ReLU + bias of one Linear+ReLU layer (torchrec/modules/mlp.py Perceptron :19-79;

@@ -75,6 +75,50 @@ def test_tbe_module_vs_embedding_bag(opt, pooling, weighted):
         torch.testing.assert_close(psw_all.grad, torch.cat([p.grad for p in ref_psw]), rtol=1e-4, atol=1e-4)
 
 
+@pytest.mark.parametrize("opt", ["EXACT_SGD", "EXACT_ROWWISE_ADAGRAD"])
+@pytest.mark.parametrize("wp", ["FP32", "FP16"])
+@pytest.mark.parametrize("shared", [False, True])
+def test_tbe_sequence_mode_vs_embedding(opt, wp, shared):
+    """PoolingMode.NONE (sequence embeddings): [N, D] rows and the fused update against nn.Embedding +
+    autograd + the closed-form optimizer (fbgemm nobag kernels; torchrec EmbeddingCollection's lookup)."""
+    from fbgemm_gpu.split_embedding_configs import SparseType
+    from fbgemm_gpu.split_table_batched_embeddings_ops import PoolingMode
+    torch.manual_seed(5)
+    rows, D, B, L = [40, 9, 300], 32, 37, 5
+    ftm = [0, 1, 1, 2] if shared else [0, 1, 2]  # feature -> table (a shared table serves two features)
+    T = len(ftm)
+    lr, eps = 0.1, 1e-4
+    m = _tbe(rows, [D] * len(rows), opt, learning_rate=lr, eps=eps, pooling_mode=PoolingMode.NONE,
+             feature_table_map=ftm, weights_precision=getattr(SparseType, wp), stochastic_rounding=False)
+    m.init_embedding_weights_uniform(-1.0, 1.0)
+    embs = [torch.nn.Embedding(r, D).cuda() for r in rows]
+    for e, w in zip(embs, m.split_embedding_weights()):
+        e.weight.data.copy_(w.float())
+    lengths = torch.randint(0, L + 1, (T, B))
+    lengths[1] = 0  # an empty feature in the middle
+    idx = [torch.randint(0, rows[ftm[f]], (int(lengths[f].sum()),)) for f in range(T)]
+    indices = torch.cat(idx).cuda()
+    offsets = torch.cat([torch.zeros(1, dtype=torch.long), lengths.view(-1).cumsum(0)]).cuda()
+    out = m(indices, offsets)
+    assert out.shape == (indices.numel(), D)
+    ref = torch.cat([embs[ftm[f]](idx[f].cuda()) for f in range(T)], 0)
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+    go = torch.randn_like(out)
+    out.backward(go)
+    ref.backward(go)
+    tol = 1e-4 if wp == "FP32" else 1e-2
+    for t, (e, w) in enumerate(zip(embs, m.split_embedding_weights())):
+        g = e.weight.grad if e.weight.grad is not None else torch.zeros_like(e.weight)
+        if opt == "EXACT_SGD":
+            exp = e.weight.data - lr * g
+        else:
+            state = g.pow(2).mean(dim=1)
+            exp = torch.addcdiv(e.weight.data, g, (state.sqrt() + eps).unsqueeze(1), value=-lr)
+            touched = torch.unique(torch.cat([idx[f] for f in range(T) if ftm[f] == t])).cuda()
+            torch.testing.assert_close(m.split_optimizer_states()[t][0][touched], state[touched], rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(w.float(), exp, rtol=tol, atol=tol)
+
+
 def test_kjt_reference_vectors():
     # torchrec/sparse/tests/test_jagged_tensor.py: test_permute :671, test_split :577, test_to_dict :549
     from torchrec.sparse.jagged_tensor import KeyedJaggedTensor

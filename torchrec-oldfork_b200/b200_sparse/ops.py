@@ -536,6 +536,24 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     return gd, gs
 
 
+# ------------------------------------------------------------------------ sequence embeddings
+def linearize_seq_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cumsum: torch.Tensor,
+                          B: int) -> torch.Tensor:
+    """int64 [N]: indices[p] + hash_size_cumsum[feature of position p] (table-major ids)."""
+    dev = _need_cuda(indices, offsets, hash_size_cumsum)
+    if indices.dtype != offsets.dtype:
+        raise TypeError("indices and offsets must share a dtype")
+    T = hash_size_cumsum.numel() - 1
+    N = indices.numel()
+    out = torch.empty(N, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        KernelProfile.launches += 1
+        check(lib.b200_linearize_seq_indices(_p(indices.contiguous()), _p(offsets.contiguous()),
+                                             _idx_dt(indices, "indices"), _p(hash_size_cumsum), T, int(B), N,
+                                             _p(out), _stream(dev)), "b200_linearize_seq_indices")
+    return out
+
+
 # ------------------------------------------------------------------------ dense-layer glue
 def relu_bias_grad(grad_out: torch.Tensor, out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """(grad_out * (out > 0), its column sums) in one pass - backward of ReLU + bias of a Linear+ReLU layer."""

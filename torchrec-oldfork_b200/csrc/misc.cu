@@ -79,7 +79,42 @@ pooled_a2a_recat_kernel(const float* __restrict__ src, float* __restrict__ dst,
   }
 }
 
+// Sequence (non-pooled) embeddings, PoolingMode.NONE: every id is its own output row.  All tables
+// of such a module share one dim D and sit back to back in the flat weight buffer, so table t's row
+// r is row hash_size_cumsum[t] + r of ONE virtual table: after this linearisation the sequence
+// lookup / backward are the pooled kernels with T = 1, B = N, one id per bag (no second kernel zoo).
+// Position p belongs to the feature t with offsets[t*B] <= p < offsets[(t+1)*B] (table-major ids).
+__global__ void __launch_bounds__(256)
+linearize_seq_kernel(const void* __restrict__ indices, const void* __restrict__ offsets, bool idx64,
+                     const int64_t* __restrict__ hash_size_cumsum, int32_t T, int32_t B, int64_t N,
+                     int64_t* __restrict__ out) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < N;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    int lo = 0, hi = T;  // largest t with offsets[t*B] <= p
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (load_index(offsets, (int64_t)mid * B, idx64) <= p) lo = mid; else hi = mid;
+    }
+    out[p] = load_index(indices, p, idx64) + hash_size_cumsum[lo];
+  }
+}
+
 }  // namespace b200
+
+extern "C" int b200_linearize_seq_indices(const void* indices, const void* offsets, int index_dtype,
+                                          const int64_t* hash_size_cumsum, int32_t T, int32_t B,
+                                          int64_t N, int64_t* out, void* stream) {
+  using namespace b200;
+  if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
+  if (T <= 0 || B < 0 || N < 0) return B200_EINVAL;
+  if (N == 0) return B200_OK;
+  int64_t grid = ceil_div(N, 256);
+  if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
+  linearize_seq_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
+      indices, offsets, index_dtype == B200_I64, hash_size_cumsum, T, B, N, out);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
 
 extern "C" const char* b200_error_string(int code) {
   switch (code) {

@@ -11,7 +11,7 @@
 namespace b200 {
 
 constexpr int kMlpThreads = 256;
-constexpr int kMlpMaxParts = 1184;  // 148 SMs x 8 row chunks
+constexpr int kMlpMaxParts = 592;  // 148 SMs x 4 row chunks
 
 // Thread t owns float4 column (t % C4) and rows r0 + (t / C4) + k * (256 / C4) of the CTA's chunk;
 // N <= 1024 so C4 <= 256 (C4 is rounded up to a power of two that divides 256).
@@ -58,14 +58,27 @@ relu_bgrad_kernel(const float* __restrict__ grad_out, int64_t go_stride, const f
   }
 }
 
+// 32 columns per CTA, 8 slices of the partial rows per column; slices are added in a fixed order.
 __global__ void __launch_bounds__(256)
 bgrad_finish_kernel(const float* __restrict__ partials, int32_t parts, int32_t N,
                     float* __restrict__ grad_bias) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+  __shared__ float s[8][33];
+  const int cx = threadIdx.x & 31, sy = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + cx;
   float a = 0.f;
-  for (int p = 0; p < parts; ++p) a += partials[(int64_t)p * N + n];
-  grad_bias[n] = a;
+  if (n < N) {
+    const int per = (parts + 7) >> 3;
+    const int p0 = sy * per, p1 = min(parts, p0 + per);
+#pragma unroll 8
+    for (int p = p0; p < p1; ++p) a += partials[(int64_t)p * N + n];
+  }
+  s[sy][cx] = a;
+  __syncthreads();
+  if (sy == 0 && n < N) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) a += s[k][cx];
+    grad_bias[n] = a;
+  }
 }
 
 }  // namespace b200
@@ -95,7 +108,7 @@ extern "C" int b200_relu_bias_grad(const float* grad_out, int64_t grad_out_strid
   relu_bgrad_kernel<<<(unsigned)parts, kMlpThreads, 0, s>>>(grad_out, grad_out_stride, out, out_stride, B, N,
                                                              C4, rows_per_cta, grad_pre, scratch);
   B200_LAUNCH_CHECK();
-  bgrad_finish_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, s>>>(scratch, (int32_t)parts, N, grad_bias);
+  bgrad_finish_kernel<<<(unsigned)ceil_div(N, 32), 256, 0, s>>>(scratch, (int32_t)parts, N, grad_bias);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

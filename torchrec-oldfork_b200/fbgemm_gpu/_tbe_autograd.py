@@ -40,6 +40,8 @@ _lib.define(
     "b200_tbe_grad_indice_weights(Tensor grad_output, Tensor dev_weights, Tensor weights_offsets, "
     "Tensor D_offsets, Tensor indices, Tensor offsets) -> Tensor")
 
+_lib.define("b200_linearize_seq_indices(Tensor indices, Tensor offsets, Tensor hash_size_cumsum, int B) -> Tensor")
+
 _OUT_DT = {SparseType.FP32.as_int(): torch.float32, SparseType.FP16.as_int(): torch.float16}
 
 
@@ -69,6 +71,7 @@ def _giw_cuda(grad_output, dev_weights, weights_offsets, D_offsets, indices, off
     return ops.tbe_grad_indice_weights(grad_output, dev_weights, weights_offsets, D_offsets, indices, offsets)
 
 
+_lib.impl("b200_linearize_seq_indices", lambda i, o, h, B: ops.linearize_seq_indices(i, o, h, B), "CUDA")
 _lib.impl("b200_tbe_forward", _fwd_cuda, "CUDA")
 _lib.impl("b200_tbe_sort_indices", _sort_cuda, "CUDA")
 _lib.impl("b200_tbe_backward", _bwd_cuda, "CUDA")

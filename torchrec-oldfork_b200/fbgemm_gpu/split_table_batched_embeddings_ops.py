@@ -133,8 +133,8 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
                 "only EmbeddingLocation.DEVICE + ComputeDevice.CUDA tables are built (HBM-resident, "
                 "sm_100a); HOST/MANAGED/MANAGED_CACHING placements and the CPU kernels are out of scope"
             )
-        if pooling_mode == PoolingMode.NONE:
-            raise NotImplementedError("PoolingMode.NONE (sequence embeddings) is out of scope")
+        if pooling_mode == PoolingMode.NONE and len(set(dims)) != 1:
+            raise ValueError("PoolingMode.NONE (sequence embeddings) needs one embedding dim for all tables")
         if optimizer not in (OptimType.EXACT_SGD, OptimType.EXACT_ROWWISE_ADAGRAD):
             raise NotImplementedError(f"optimizer {optimizer} is not built; use EXACT_SGD or EXACT_ROWWISE_ADAGRAD")
         if weights_precision not in (SparseType.FP32, SparseType.FP16, SparseType.BF16):
@@ -197,11 +197,29 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
             self.register_buffer("momentum1_dev", torch.zeros(0, device=dev, dtype=torch.float32))
             self.register_buffer("momentum1_offsets", torch.zeros(T, **i64))
         self.step = 0
+        self._seq_view: Optional["_SequenceView"] = None
+        if pooling_mode == PoolingMode.NONE:
+            self.total_D = dims[0]  # output is [N, D]
+            self.register_buffer("seq_D_offsets", torch.tensor([0, dims[0]], device=dev, dtype=torch.int32))
+            self.register_buffer("seq_hash_size_cumsum", torch.tensor([0, table_hash_cumsum[-1]], **i64))
+            self.register_buffer("seq_zero_offset", torch.zeros(1, **i64))
+            self._seq_view = _SequenceView(self)
 
     # ------------------------------------------------------------------ forward
     def forward(self, indices: Tensor, offsets: Tensor, per_sample_weights: Optional[Tensor] = None,
                 feature_requires_grad: Optional[Tensor] = None) -> Tensor:
         indices, offsets = self.prepare_indices(indices, offsets)
+        if self._seq_view is not None:
+            # sequence embeddings: [N, D], one row per id (reference `nobag` kernels).  The ids are
+            # rebased into ONE virtual table (all tables share D and are contiguous) and the pooled
+            # kernels run with T = 1, B = N, L = 1: same gather, same sorted fused backward.
+            if per_sample_weights is not None:
+                raise ValueError("PoolingMode.NONE takes no per_sample_weights")
+            T = self.D_offsets.numel() - 1
+            B = (offsets.numel() - 1) // T
+            lin = torch.ops.fbgemm.b200_linearize_seq_indices(indices, offsets, self.hash_size_cumsum, B)
+            seq_offsets = torch.arange(lin.numel() + 1, device=lin.device, dtype=torch.int64)
+            return _tbe_autograd.lookup(self._seq_view, lin, seq_offsets, None, None)
         return _tbe_autograd.lookup(self, indices, offsets, per_sample_weights, feature_requires_grad)
 
     def prepare_indices(self, indices: Tensor, offsets: Tensor) -> Tuple[Tensor, Tensor]:
@@ -258,6 +276,27 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
 
     def reset_cache_states(self) -> None:
         return None
+
+
+class _SequenceView:
+    """The attributes _tbe_autograd.lookup reads, describing a PoolingMode.NONE module as ONE table of
+    sum(rows) rows pooled with one id per bag.  Buffers are read through the owner at call time so that
+    .to() / load_state_dict on the owner stay visible; optimizer_args is the owner's object."""
+
+    def __init__(self, owner: "SplitTableBatchedEmbeddingBagsCodegen") -> None:
+        self._o = owner
+
+    pooling_mode = PoolingMode.SUM
+
+    def __getattr__(self, name: str):
+        o = self.__dict__["_o"]
+        if name in ("weights_offsets", "momentum1_offsets"):
+            return o.seq_zero_offset
+        if name == "D_offsets":
+            return o.seq_D_offsets
+        if name == "hash_size_cumsum":
+            return o.seq_hash_size_cumsum
+        return getattr(o, name)
 
 
 class DenseTableBatchedEmbeddingBagsCodegen(nn.Module):

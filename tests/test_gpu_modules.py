@@ -233,6 +233,21 @@ def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     assert r.returncode == 0 and f"exchange={exchange}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
+@pytest.mark.parametrize("world", [1, 2])
+def test_sharded_sequence_embeddings_vs_unsharded(world):
+    """EmbeddingCollection under DistributedModelParallel (table-wise + row-wise sequence sharding,
+    SequenceEmbeddingAllToAll, fused SGD) equals nn.Embedding + SGD on the global batch."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29631",
+                        os.path.join(here, "dist_seq_worker.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and f"SEQ PARITY OK world={world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
 def test_interaction_row_pitch_and_pitched_linear():
     """InteractionArch output sits at a 16-byte row pitch with zero padding, and RowPitchedLinear consumes
     it with the same results/gradients as nn.Linear on a dense copy (fan-in 479 -> 480-wide GEMM)."""

@@ -107,9 +107,13 @@ class BaseBatchedEmbeddingBag(nn.Module):
 
 
 class BatchedFusedEmbeddingBag(BaseBatchedEmbeddingBag, FusedOptimizerModule):
+    _sequence = False  # BatchedFusedEmbedding: PoolingMode.NONE, output [sum lengths, D]
+
     def __init__(self, config: GroupedEmbeddingConfig, pg: Optional[dist.ProcessGroup] = None,
                  device: Optional[torch.device] = None, fused_params: Optional[Dict[str, Any]] = None) -> None:
         super().__init__(config, pg, device)
+        if self._sequence:
+            self._pooling = PoolingMode.NONE
         if device is None or device.type != "cuda":
             raise RuntimeError(
                 "BatchedFusedEmbeddingBag runs on the sm_100a kernels only; got device "
@@ -138,3 +142,12 @@ class BatchedFusedEmbeddingBag(BaseBatchedEmbeddingBag, FusedOptimizerModule):
     def named_buffers(self, prefix: str = "", recurse: bool = True):
         for t, w in zip(self._config.embedding_tables, self.emb_module.split_embedding_weights()):
             yield (f"{prefix}.{t.name}.weight" if prefix else f"{t.name}.weight"), w
+
+
+class BatchedFusedEmbedding(BatchedFusedEmbeddingBag):
+    """Non-pooled (sequence) twin (reference BatchedFusedEmbedding :459-496): same buffers, fused optimizer
+    and state_dict; the lookup returns one [D] row per id."""
+    _sequence = True
+
+    def forward(self, features: KeyedJaggedTensor) -> torch.Tensor:
+        return self.emb_module(indices=features.values(), offsets=features.offsets())

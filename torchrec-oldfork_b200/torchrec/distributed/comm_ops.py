@@ -200,3 +200,58 @@ def reduce_scatter_pooled(inputs, group: Optional[dist.ProcessGroup] = None) -> 
     req = _Request(group)
     req.dummy = ReduceScatter_Req.apply(group, req, embs)
     return _AwaitTensor(ReduceScatter_Wait, req)
+
+
+# ------------------------------------------------------------------ sequence all-to-all (non-pooled)
+class All2All_Seq(Function):
+    """Sequence-embedding all-to-all (reference alltoall_sequence :259, All2All_Seq_Req :608 / _Wait :701).
+
+    Input rows [sum lengths, D] are feature-major ((local feature, source rank, sample) bags, the order the
+    KJT all-to-all delivered the ids in); they are regrouped rank-major with ONE permute_2D_sparse_data
+    launch over float payloads (lengths x D), sent back to the ranks that own the samples, and arrive as
+    (owner rank, feature, sample) = global feature order.  Backward is the transposed exchange followed by
+    the inverse regrouping.  No 1/W scaling: a sequence row has exactly one consumer."""
+
+    @staticmethod
+    def forward(ctx, pg, embs: torch.Tensor, forward_recat: torch.Tensor, backward_recat: torch.Tensor,
+                lengths_after: torch.Tensor, input_splits: List[int], output_splits: List[int]) -> torch.Tensor:
+        W = dist.get_world_size(pg)
+        D = embs.shape[1]
+        local_T = lengths_after.shape[0]
+        send = embs.contiguous().view(-1)
+        permuted_lengths = None
+        if local_T > 0 and forward_recat.numel() > 0:
+            lens_d = (lengths_after * D).view(forward_recat.numel(), -1)
+            permuted_lengths, send, _ = torch.ops.fbgemm.permute_2D_sparse_data(
+                forward_recat, lens_d, send, None, send.numel())
+        # rows this rank RECEIVED ids for go back where they came from: splits are swapped
+        in_splits = [n * D for n in output_splits]
+        out_splits = [n * D for n in input_splits]
+        recv = send.new_empty(sum(out_splits))
+        dist.all_to_all_single(recv, send, output_split_sizes=out_splits, input_split_sizes=in_splits, group=pg)
+        ctx.pg, ctx.D, ctx.permuted_lengths, ctx.backward_recat = pg, D, permuted_lengths, backward_recat
+        ctx.in_splits, ctx.out_splits = in_splits, out_splits
+        return recv.view(-1, D)
+
+    @staticmethod
+    def backward(ctx, grad_out: torch.Tensor):
+        send = grad_out.contiguous().view(-1)
+        recv = send.new_empty(sum(ctx.in_splits))
+        dist.all_to_all_single(recv, send, output_split_sizes=ctx.in_splits, input_split_sizes=ctx.out_splits,
+                               group=ctx.pg)
+        if ctx.permuted_lengths is not None:
+            _, recv, _ = torch.ops.fbgemm.permute_2D_sparse_data(
+                ctx.backward_recat, ctx.permuted_lengths, recv, None, recv.numel())
+        return None, recv.view(-1, ctx.D), None, None, None, None, None
+
+
+def alltoall_sequence(a2a_sequence_embs_tensor: torch.Tensor, forward_recat_tensor: torch.Tensor,
+                      backward_recat_tensor: torch.Tensor, lengths_after_sparse_data_all2all: torch.Tensor,
+                      input_splits: List[int], output_splits: List[int],
+                      group: Optional[dist.ProcessGroup] = None) -> Awaitable[torch.Tensor]:
+    """[T_local * B_global * L, D] rows on every rank -> the rows of MY samples, global feature order."""
+    group = group if group is not None else dist.distributed_c10d._get_default_group()
+    if dist.get_world_size(group) <= 1:
+        return NoWait(a2a_sequence_embs_tensor)
+    return NoWait(All2All_Seq.apply(group, a2a_sequence_embs_tensor, forward_recat_tensor, backward_recat_tensor,
+                                    lengths_after_sparse_data_all2all, input_splits, output_splits))

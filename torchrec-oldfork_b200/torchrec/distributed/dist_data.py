@@ -16,7 +16,7 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
-from torchrec.distributed.comm_ops import alltoall_pooled, reduce_scatter_pooled
+from torchrec.distributed.comm_ops import alltoall_pooled, alltoall_sequence, reduce_scatter_pooled
 from torchrec.distributed.types import Awaitable, NoWait
 from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
 
@@ -54,6 +54,9 @@ class KJTAllToAllIndicesAwaitable(Awaitable[KeyedJaggedTensor]):
         self._workers = dist.get_world_size(pg)
         self._batch_size_per_rank = batch_size_per_rank
         self._length_per_key = length_per_key
+        # ids sent to / received from each rank: the sequence output dist sends one row back per id
+        self._in_lengths_per_worker = list(in_lengths_per_worker)
+        self._out_lengths_per_worker = list(out_lengths_per_worker)
         self._works: List = []
         self._values: Optional[torch.Tensor] = None
         self._weights: Optional[torch.Tensor] = None
@@ -192,3 +195,41 @@ class PooledEmbeddingsReduceScatter(nn.Module):
 
     def forward(self, local_embs: torch.Tensor) -> PooledEmbeddingsAwaitable:
         return PooledEmbeddingsAwaitable(reduce_scatter_pooled(local_embs, self._pg))
+
+
+class SequenceEmbeddingsAwaitable(Awaitable[torch.Tensor]):
+    def __init__(self, tensor_awaitable: Awaitable[torch.Tensor], unbucketize_permute_tensor: Optional[torch.Tensor],
+                 embedding_dim: int) -> None:
+        super().__init__()
+        self._tensor_awaitable = tensor_awaitable
+        self._unbucketize_permute_tensor = unbucketize_permute_tensor
+        self._embedding_dim = embedding_dim
+
+    def _wait_impl(self) -> torch.Tensor:
+        ret = self._tensor_awaitable.wait()
+        if self._unbucketize_permute_tensor is not None:  # row-wise: back to the pre-bucketize id order
+            ret = torch.index_select(ret.view(-1, self._embedding_dim), 0, self._unbucketize_permute_tensor)
+        return ret
+
+
+class SequenceEmbeddingAllToAll(nn.Module):
+    """Sends every looked-up row back to the rank that owns its sample (reference :841-932)."""
+
+    def __init__(self, pg: dist.ProcessGroup, features_per_rank: List[int],
+                 device: Optional[torch.device] = None) -> None:
+        super().__init__()
+        self._pg = pg
+        W, mine = dist.get_world_size(pg), features_per_rank[dist.get_rank(pg)]
+        self.register_buffer("_forward_recat_tensor",
+                             torch.tensor([j + i * W for j in range(W) for i in range(mine)], device=device,
+                                          dtype=torch.int32), persistent=False)
+        self.register_buffer("_backward_recat_tensor",
+                             torch.tensor([i + j * mine for i in range(mine) for j in range(W)], device=device,
+                                          dtype=torch.int32), persistent=False)
+
+    def forward(self, local_embs: torch.Tensor, lengths: torch.Tensor, input_splits: List[int],
+                output_splits: List[int], unbucketize_permute_tensor: Optional[torch.Tensor] = None
+                ) -> SequenceEmbeddingsAwaitable:
+        aw = alltoall_sequence(local_embs, self._forward_recat_tensor, self._backward_recat_tensor, lengths,
+                               input_splits, output_splits, self._pg)
+        return SequenceEmbeddingsAwaitable(aw, unbucketize_permute_tensor, local_embs.shape[1])

@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
-from torchrec.distributed.batched_embedding_kernel import BatchedFusedEmbeddingBag
+from torchrec.distributed.batched_embedding_kernel import BatchedFusedEmbedding, BatchedFusedEmbeddingBag
 from torchrec.distributed.embedding_sharding import BaseEmbeddingLookup
 from torchrec.distributed.embedding_types import (
     EmbeddingComputeKernel, GroupedEmbeddingConfig, SparseFeatures)
@@ -80,3 +80,49 @@ class GroupedPooledEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Te
     def fused_optimizer(self) -> KeyedOptimizer:
         return CombinedOptimizer([m.fused_optimizer for m in self._all_modules()
                                   if isinstance(m, FusedOptimizerModule)])
+
+
+class GroupedEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Tensor], FusedOptimizerModule):
+    """Sequence (non-pooled) lookups (reference GroupedEmbeddingsLookup :59-207): one table-batched
+    PoolingMode.NONE module per kernel group; rows are concatenated in feature order, [sum lengths, D]."""
+
+    def __init__(self, grouped_configs: List[GroupedEmbeddingConfig], device: Optional[torch.device] = None,
+                 pg: Optional[dist.ProcessGroup] = None, fused_params: Optional[Dict[str, Any]] = None) -> None:
+        super().__init__()
+        for cfg in grouped_configs:
+            if cfg.compute_kernel != EmbeddingComputeKernel.BATCHED_FUSED:
+                raise NotImplementedError(f"compute kernel {cfg.compute_kernel} is not built; only BATCHED_FUSED")
+        self._emb_modules = nn.ModuleList(
+            [BatchedFusedEmbedding(c, pg=pg, device=device, fused_params=fused_params) for c in grouped_configs])
+        self._id_list_feature_splits = [c.num_features() for c in grouped_configs]
+        self.grouped_configs = grouped_configs
+        self._device = device
+        self._dim = grouped_configs[0].embedding_tables[0].local_cols if grouped_configs else 0
+
+    def forward(self, sparse_features: SparseFeatures) -> torch.Tensor:
+        kjt = sparse_features.id_list_features
+        if not self._emb_modules:
+            # a rank without tables still joins the output all-to-all and its backward
+            return torch.empty((0, self._dim), device=self._device, requires_grad=torch.is_grad_enabled())
+        assert kjt is not None
+        parts = kjt.split(self._id_list_feature_splits) if len(self._emb_modules) > 1 else [kjt]
+        outs = [m(f) for m, f in zip(self._emb_modules, parts)]
+        return outs[0] if len(outs) == 1 else torch.cat(outs, dim=0)
+
+    def state_dict(self, destination=None, prefix: str = "", keep_vars: bool = False) -> Dict[str, Any]:
+        if destination is None:
+            destination = {}
+        for m in self._emb_modules:
+            m.state_dict(destination, prefix, keep_vars)
+        return destination
+
+    def named_parameters(self, prefix: str = "", recurse: bool = True):
+        yield from ()
+
+    def named_buffers(self, prefix: str = "", recurse: bool = True):
+        for m in self._emb_modules:
+            yield from m.named_buffers(prefix, recurse)
+
+    @property
+    def fused_optimizer(self) -> KeyedOptimizer:
+        return CombinedOptimizer([m.fused_optimizer for m in self._emb_modules])

@@ -39,8 +39,6 @@ class DefaultDataParallelWrapper(DataParallelWrapper):
         pg = env.process_group
         if pg is None or env.world_size <= 1:
             return
-        if not any(p.requires_grad for p in dmp._dmp_wrapped_module.parameters()):
-            return
         # Everything under a ShardedModule is model-parallel: the table shards are updated by the fused
         # backward, and the number of lookup modules (hence of their autograd placeholders) differs from
         # rank to rank.  DDP must see the same dense parameter list everywhere (reference :96-104).
@@ -51,6 +49,9 @@ class DefaultDataParallelWrapper(DataParallelWrapper):
                     full = ".".join(x for x in (mod_name, sub_name) if x)
                     for n, _ in list(sub._parameters.items()) + list(sub._buffers.items()):
                         ignore.append(f"{full}.{n}" if full else n)
+        ignored = set(ignore)
+        if not any(p.requires_grad for n, p in dmp._dmp_wrapped_module.named_parameters() if n not in ignored):
+            return  # sparse-only model (e.g. a bare EmbeddingCollection): nothing is data-parallel
         DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(dmp._dmp_wrapped_module, ignore)
         dmp._dmp_wrapped_module = DistributedDataParallel(
             module=dmp._dmp_wrapped_module.to(device),

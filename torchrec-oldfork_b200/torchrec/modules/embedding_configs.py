@@ -40,6 +40,8 @@ def dtype_to_data_type(dtype: torch.dtype) -> DataType:
 
 
 def pooling_type_to_pooling_mode(pooling_type: PoolingType) -> PoolingMode:
+    if pooling_type == PoolingType.NONE:
+        return PoolingMode.NONE
     if pooling_type not in _POOL:
         raise Exception(f"Invalid pooling type {pooling_type}")
     return _POOL[pooling_type][0]

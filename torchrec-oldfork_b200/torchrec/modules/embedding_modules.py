@@ -10,8 +10,9 @@ from typing import Dict, List, Optional
 import torch
 import torch.nn as nn
 
-from torchrec.modules.embedding_configs import EmbeddingBagConfig, PoolingType, pooling_type_to_str
-from torchrec.sparse.jagged_tensor import KeyedJaggedTensor, KeyedTensor
+from torchrec.modules.embedding_configs import (
+    DataType, EmbeddingBagConfig, EmbeddingConfig, PoolingType, pooling_type_to_str)
+from torchrec.sparse.jagged_tensor import JaggedTensor, KeyedJaggedTensor, KeyedTensor
 
 
 def ebc_get_embedding_names(tables: List[EmbeddingBagConfig]) -> List[str]:
@@ -77,3 +78,41 @@ class EmbeddingBagCollection(EmbeddingBagCollectionInterface):
     @property
     def is_weighted(self) -> bool:
         return self._is_weighted
+
+
+class EmbeddingCollection(nn.Module):
+    """Collection of NON-pooled (sequence) embeddings (reference :204-348): KJT [F x B x L] in,
+    Dict[feature, JaggedTensor] out, each JaggedTensor holding one [D] row per id.  One nn.Embedding per
+    table; all tables share one embedding dim.  This is the semantic reference that
+    DistributedModelParallel replaces by ShardedEmbeddingCollection (sm_100a sequence lookup)."""
+
+    def __init__(self, tables: List[EmbeddingConfig], device: Optional[torch.device] = None) -> None:
+        super().__init__()
+        self.embeddings: nn.ModuleDict = nn.ModuleDict()
+        self.embedding_configs = tables
+        self.embedding_dim: int = -1
+        uses: Dict[str, int] = {}
+        for cfg in tables:
+            if cfg.name in self.embeddings:
+                raise ValueError(f"Duplicate table name {cfg.name}")
+            if self.embedding_dim < 0:
+                self.embedding_dim = cfg.embedding_dim
+            if self.embedding_dim != cfg.embedding_dim:
+                raise ValueError("All tables in a EmbeddingCollection are required to have same embedding dimension.")
+            dtype = torch.float32 if cfg.data_type == DataType.FP32 else torch.float16
+            self.embeddings[cfg.name] = nn.Embedding(num_embeddings=cfg.num_embeddings,
+                                                     embedding_dim=cfg.embedding_dim, device=device, dtype=dtype)
+            if not cfg.feature_names:
+                cfg.feature_names = [cfg.name]
+            for f in cfg.feature_names:
+                uses[f] = uses.get(f, 0) + 1
+        self.embedding_names_by_table: List[List[str]] = [
+            [f + "@" + cfg.name if uses[f] > 1 else f for f in cfg.feature_names] for cfg in tables]
+
+    def forward(self, features: KeyedJaggedTensor) -> Dict[str, JaggedTensor]:
+        out: Dict[str, JaggedTensor] = {}
+        for cfg, names, emb in zip(self.embedding_configs, self.embedding_names_by_table, self.embeddings.values()):
+            for feature, name in zip(cfg.feature_names, names):
+                f = features[feature]
+                out[name] = JaggedTensor(values=emb(f.values()), lengths=f.lengths())
+        return out

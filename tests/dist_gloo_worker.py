@@ -122,6 +122,33 @@ def check_reduce_scatter(rank: int, world: int) -> None:
     torch.testing.assert_close(x.grad, exp_g, rtol=1e-6, atol=1e-7)
 
 
+def check_sequence_all2all(rank: int, world: int) -> None:
+    """Non-pooled rows go back to the rank that owns the sample, in its local (key, sample, id) order, and
+    gradients make the reverse trip (torchrec/distributed/tests/test_dist_data.py SeqEmbeddingsAllToAllTest)."""
+    from torchrec.distributed.dist_data import KJTAllToAll, SequenceEmbeddingAllToAll
+    keys, splits, B, D = ["f0", "f1", "f2"], [2, 1], 3, 4
+    scale = torch.arange(1, D + 1, dtype=torch.float32)
+    mine = make_kjt(rank, keys, B, 100)
+    indices_aw = KJTAllToAll(dist.group.WORLD, splits)(mine).wait()
+    got = indices_aw.wait()
+    # "lookup": row of id v = v * [1..D]; rows are in the received (key, source rank, sample) order
+    local_embs = (got.values().float().unsqueeze(1) * scale).requires_grad_(True)
+    m = SequenceEmbeddingAllToAll(dist.group.WORLD, splits)
+    out = m(local_embs, got.lengths().view(-1, got.stride()), indices_aw._in_lengths_per_worker,
+            indices_aw._out_lengths_per_worker).wait()
+    exp = mine.values().float().unsqueeze(1) * scale  # my own ids, key-major: exactly the local KJT order
+    torch.testing.assert_close(out, exp, rtol=0, atol=0)
+    # upstream gradient of the row of id v on rank r: v * [1..D] + 1000 r
+    (out * (exp + 1000.0 * rank)).sum().backward()
+    lo = sum(splits[:rank])
+    inputs = [make_kjt(r, keys, B, 100) for r in range(world)]
+    rows = []
+    for k in keys[lo:lo + splits[rank]]:
+        for r in range(world):
+            rows.append(inputs[r][k].values().float().unsqueeze(1) * scale + 1000.0 * r)
+    torch.testing.assert_close(local_embs.grad, torch.cat(rows), rtol=0, atol=0)
+
+
 def main() -> None:
     import cpu_ops
     cpu_ops.register()
@@ -131,6 +158,7 @@ def main() -> None:
     check_row_wise_input_dist(rank, world)
     check_pooled_all2all(rank, world)
     check_reduce_scatter(rank, world)
+    check_sequence_all2all(rank, world)
     dist.barrier()
     if rank == 0:
         print(f"GLOO DIST OK world={world}")

@@ -98,6 +98,13 @@ BWD_CASES = [
     ([1, 2], [64, 64], 1500, 2),
     ([500, 40, 9], [8, 32, 256], 200, 10),
     ([20, 5], [1024, 512], 64, 5),
+    # narrow rows -> several sorted positions per warp step (4 / 8 / 16 lanes per row), with short and
+    # very long runs (tiny tables) crossing steps, warps and CTAs
+    ([3000, 50, 4], [32, 32, 32], 700, 3),
+    ([100, 100000], [64, 64], 2000, 1),
+    ([2000, 3], [16, 16], 900, 5),
+    ([7, 5000], [128, 128], 600, 4),
+    ([1, 40000], [8, 24], 1200, 2),
 ]
 
 

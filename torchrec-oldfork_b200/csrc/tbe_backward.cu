@@ -22,6 +22,8 @@
 //     finishes them, again in fixed order.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -272,6 +274,163 @@ __device__ __forceinline__ void load_wslot(const unsigned char* p, float (&f)[EP
   }
 }
 
+// ---- narrow rows (D <= 16 * EPV): several sorted positions per warp instruction -------------------
+// With one position per step the tile loop costs ~150 issue slots per position whatever the row
+// width, so at dim 32 / 64 (SURVEY cfg4) the kernel is issue-bound at a quarter of what HBM allows.
+// Here a row is owned by a group of LPR lanes (EPV elements each) and the R = 32 / LPR groups of the
+// warp take R consecutive sorted positions per step:
+//   * gradient rows (and, for positions that complete a run, the weight row + momentum) of step s+1
+//     are loaded into registers while step s is reduced (two steps in flight per lane);
+//   * rows of one run are adjacent groups: a segmented inclusive scan across groups (log2 R shuffle
+//     rounds) gives every run end its sum inside the step, the run still open from earlier steps
+//     is a carry replicated in every group;
+//   * all runs that end in a step apply the optimizer at once, each by its own group.
+// Leading / trailing partial runs leave through the same interface as the other two paths
+// (sH[warp] and `acc` in the one-row-per-warp layout, which for D <= EPV * LPR is group 0's layout).
+template <typename W, int EPV>
+struct BwdRawW {
+  static constexpr int kWords = (int)(EPV * sizeof(W) / 4);
+  uint32_t r[kWords];
+  __device__ __forceinline__ void load(const W* p) {
+    if constexpr (kWords == 4) {
+      const uint4 v = ld_16(p);
+      r[0] = v.x, r[1] = v.y, r[2] = v.z, r[3] = v.w;
+    } else {
+      const uint2 v = ld_8(p);
+      r[0] = v.x, r[1] = v.y;
+    }
+  }
+  __device__ __forceinline__ void unpack(float (&f)[EPV]) const {
+    if constexpr (sizeof(W) == 4) {
+#pragma unroll
+      for (int i = 0; i < EPV; ++i) f[i] = __uint_as_float(r[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < kWords; ++i) ElemCvt<W>::unpack2(r[i], f[2 * i], f[2 * i + 1]);
+    }
+  }
+};
+
+template <typename W, int EPV, int OPT, int LPR>
+__device__ __forceinline__ void bwd_packed_tile(const int lane, const unsigned Hm, const unsigned Em,
+                                                const unsigned Cm, const float* gptr, W* wptr,
+                                                float* mptr, const float scale, const bool scaled,
+                                                const int D0, const float lr, const float eps,
+                                                float* sH_warp, float (&acc)[1][EPV]) {
+  constexpr int R = 32 / LPR;
+  constexpr unsigned kRMask = (1u << R) - 1u;
+  const int gl = lane & (LPR - 1);
+  const int g = lane / LPR;
+  const bool act = EPV * gl < D0;
+  const float inv_D = 1.0f / (float)D0;
+  float carry[EPV];
+#pragma unroll
+  for (int e = 0; e < EPV; ++e) carry[e] = 0.f;
+
+  float gx[2][EPV];
+  BwdRawW<W, EPV> wr[2];
+  float mo[2] = {0.f, 0.f};
+  W* wpb[2] = {nullptr, nullptr};
+  float* mpb[2] = {nullptr, nullptr};
+  float spb[2] = {1.f, 1.f};
+
+  auto issue = [&](int s, int buf) {
+    const int p = s * R + g;
+    const float* gp = reinterpret_cast<const float*>(__shfl_sync(kFull, (unsigned long long)gptr, p));
+    wpb[buf] = reinterpret_cast<W*>(__shfl_sync(kFull, (unsigned long long)wptr, p));
+    if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD)
+      mpb[buf] = reinterpret_cast<float*>(__shfl_sync(kFull, (unsigned long long)mptr, p));
+    spb[buf] = scaled ? __shfl_sync(kFull, scale, p) : 1.f;
+    const bool fin = (Cm >> p) & 1u;
+    if (act) {
+      load_grad<EPV>(gp + EPV * gl, gx[buf]);
+      if (fin) wr[buf].load(wpb[buf] + EPV * gl);
+    } else {
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) gx[buf][e] = 0.f;
+    }
+    if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+      if (fin && gl == 0) mo[buf] = *mpb[buf];
+    }
+  };
+
+  issue(0, 0);
+#pragma unroll 2
+  for (int s = 0; s < LPR; ++s) {  // 32 / R steps
+    const int buf = s & 1;
+    if (s + 1 < LPR) issue(s + 1, buf ^ 1);
+    float x[EPV];
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) x[e] = scaled ? gx[buf][e] * spb[buf] : gx[buf][e];
+    const int p = s * R + g;
+    int f = (int)((Hm >> p) & 1u);
+    // segmented inclusive scan over the R groups (segments start at run heads)
+#pragma unroll
+    for (int d = LPR; d < 32; d <<= 1) {
+      float y[EPV];
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) y[e] = __shfl_up_sync(kFull, x[e], d);
+      const int fy = __shfl_up_sync(kFull, f, d);
+      if (lane >= d && !f) {
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) x[e] += y[e];
+        f |= fy;
+      }
+    }
+    if (!f) {  // the segment began before this step: add the open run
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) x[e] += carry[e];
+    }
+    const unsigned emb = (Em >> (s * R)) & kRMask;
+    const unsigned cmb = (Cm >> (s * R)) & kRMask;
+    if (emb) {  // warp-uniform: some run ends in this step
+      if (cmb) {
+        const bool my_fin = (cmb >> g) & 1u;
+        float mult = lr;
+        if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
+          float ss = 0.f;
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) ss = fmaf(x[e], x[e], ss);  // idle lanes hold 0
+#pragma unroll
+          for (int o = LPR / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(kFull, ss, o);
+          float m_new = mo[buf] + ss * inv_D;
+          if (my_fin && gl == 0) *mpb[buf] = m_new;
+          m_new = __shfl_sync(kFull, m_new, g * LPR);
+          float r;
+          asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(m_new));
+          mult = __fdividef(lr, r + eps);
+        }
+        if (my_fin && act) {
+          float w[EPV];
+          wr[buf].unpack(w);
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) w[e] = fmaf(x[e], -mult, w[e]);
+          store_vec<W, EPV, false>(wpb[buf] + EPV * gl, w);
+        }
+      }
+      const unsigned lead = emb & ~cmb;
+      if (lead) {  // the run that entered the tile ends here: its partial sum leaves through sH
+        const int gE = __ffs(lead) - 1;
+        float tmp[1][EPV];
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) {
+          const float v = __shfl_sync(kFull, x[e], gE * LPR + gl);
+          tmp[0][e] = lane < LPR ? v : 0.f;
+        }
+        row_store<EPV, 1>(sH_warp, tmp, lane);
+      }
+    }
+    const bool last_ends = (emb >> (R - 1)) & 1u;
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) {
+      const float c = __shfl_sync(kFull, x[e], (R - 1) * LPR + gl);
+      carry[e] = last_ends ? 0.f : c;
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < EPV; ++e) acc[0][e] = lane < LPR ? carry[e] : 0.f;
+}
+
 template <typename K>
 struct BwdArgs {
   const float* grad;
@@ -299,12 +458,13 @@ struct BwdArgs {
   const int32_t* src_col;
   int32_t B_src;
   float grad_scale;  // 1/W of the sharded path (GRADIENT_DIVISION), 1 otherwise
+  int32_t pack_rows;  // narrow rows: several positions per warp step (bwd_packed_tile)
   float* part_rows;  // [numCTAs][2][ROW]  (0 = leading partial H, 1 = trailing partial T)
   BwdMeta* meta;     // [numCTAs]
   int32_t num_ctas;
 };
 
-template <typename W, typename K, int EPV, int NV, int OPT>
+template <typename W, typename K, int EPV, int NV, int OPT, bool PACKED>
 __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const BwdArgs<K> a) {
   constexpr int ROW = NV * EPV * 32;
   constexpr int kStages = BwdRing<EPV, NV>::kStages;
@@ -403,7 +563,25 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
   // ~140 (the generic loop below is issue-bound, not HBM-bound).
   const int D0 = __shfl_sync(kFull, Dt, 0);
   const bool fast = nvalid == 32 && __all_sync(kFull, Dt == D0);
-  if (fast) {
+  bool packed = false;
+  if constexpr (PACKED) {  // host: NV == 1 and max_D <= 8 * EPV (4 or 8 lanes per row; with 16 lanes
+    // only two positions fit a step and the one-row path below is faster)
+    if (fast && D0 <= EPV * 8) {
+      packed = true;
+      W* const wp = weights + woff;
+      float* const mp = (OPT == B200_OPT_ROWWISE_ADAGRAD) ? a.momentum1 + moff : nullptr;
+      if (D0 <= EPV * 4)
+        bwd_packed_tile<W, EPV, OPT, 4>(lane, Hm, Em, Cm, gptr, wp, mp, scale, scaled, D0, a.lr, a.eps,
+                                        sH + warp * ROW, acc);
+      else
+        bwd_packed_tile<W, EPV, OPT, 8>(lane, Hm, Em, Cm, gptr, wp, mp, scale, scaled, D0, a.lr, a.eps,
+                                        sH + warp * ROW, acc);
+      open_head = Hm ? 31 - __clz(Hm) : -1;
+    }
+  }
+  if (packed) {
+    // done: acc / open_head / sH are set as the stitching code below expects
+  } else if (fast) {
     unsigned long long* const mg = s_ptr[warp][0];
     unsigned long long* const mw = s_ptr[warp][1];
     unsigned long long* const mm = s_ptr[warp][2];
@@ -726,7 +904,19 @@ static int launch_backward(const BwdArgs<K>& a, cudaStream_t s) {
   constexpr int ROW = NV * EPV * 32;
   const size_t smem = sizeof(float) * kBwdWarps * ROW +
                       (size_t)kBwdWarps * BwdRing<EPV, NV>::kStages * BwdRing<EPV, NV>::kStageBytes;
-  auto tile = tbe_backward_tile_kernel<W, K, EPV, NV, OPT>;
+  if constexpr (NV == 1) {
+    if (a.pack_rows) {  // narrow rows: several sorted positions per warp step
+      auto ptile = tbe_backward_tile_kernel<W, K, EPV, 1, OPT, true>;
+      if (smem > 48 * 1024)
+        B200_CUDA_TRY(cudaFuncSetAttribute(ptile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      ptile<<<a.num_ctas, kBwdThreads, smem, s>>>(a);
+      B200_LAUNCH_CHECK();
+      tbe_backward_combine_kernel<W, K, EPV, NV, OPT><<<(a.num_ctas + 3) / 4, 128, 0, s>>>(a);
+      B200_LAUNCH_CHECK();
+      return B200_OK;
+    }
+  }
+  auto tile = tbe_backward_tile_kernel<W, K, EPV, NV, OPT, false>;
   if (smem > 48 * 1024)
     B200_CUDA_TRY(cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   tile<<<a.num_ctas, kBwdThreads, smem, s>>>(a);
@@ -739,7 +929,11 @@ static int launch_backward(const BwdArgs<K>& a, cudaStream_t s) {
 template <typename W, typename K, int EPV, int OPT>
 static int dispatch_nv(const BwdArgs<K>& a, int max_D, cudaStream_t s) {
   const int vecs = (int)ceil_div(max_D, EPV * 32);
-  if (vecs <= 1) return launch_backward<W, K, EPV, 1, OPT>(a, s);
+  if (vecs <= 1) {
+    BwdArgs<K> b = a;
+    b.pack_rows = (a.pack_rows && max_D <= EPV * 8) ? 1 : 0;
+    return launch_backward<W, K, EPV, 1, OPT>(b, s);
+  }
   if (vecs <= 2) return launch_backward<W, K, EPV, 2, OPT>(a, s);
   if (vecs <= 4) return launch_backward<W, K, EPV, 4, OPT>(a, s);
   if (vecs <= 8) return launch_backward<W, K, EPV, 8, OPT>(a, s);
@@ -772,6 +966,14 @@ static int dispatch_w(const BwdArgs<K>& a, int weight_dtype, bool mult8, int opt
 }
 
 static inline int64_t bwd_num_ctas(int64_t N) { return ceil_div(N, kBwdTile); }
+// B200_BWD_PACK=0 disables the narrow-row packed path (A/B measurements only)
+static inline int bwd_pack_rows() {
+  static const int v = [] {
+    const char* e = getenv("B200_BWD_PACK");
+    return e ? atoi(e) : 1;
+  }();
+  return v;
+}
 static inline size_t bwd_row_floats(int max_D) {
   // the widest instantiation that can be chosen for this max_D (EPV=4 or 8, NV rounded up)
   int vecs4 = (int)ceil_div(max_D, 4 * 32);
@@ -867,6 +1069,7 @@ static int tbe_backward_impl(const float* grad_output, int64_t grad_stride,
   ARGS.src_col = src_col;                                  \
   ARGS.B_src = B_src;                                      \
   ARGS.grad_scale = grad_scale;                            \
+  ARGS.pack_rows = bwd_pack_rows();                        \
   ARGS.part_rows = part_rows;                              \
   ARGS.meta = meta;                                        \
   ARGS.num_ctas = (int32_t)ctas;

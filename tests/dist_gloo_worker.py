@@ -45,6 +45,55 @@ def check_kjt_all2all(rank: int, world: int) -> None:
                 assert torch.equal(got[k].weights(), torch.cat([i[k].weights() for i in inputs]))
 
 
+def check_kjt_all2all_variable_batch(rank: int, world: int) -> None:
+    """Each rank brings its own batch size (test_dist_data.py KJTAllToAllTest, variable_batch_size=True):
+    key k of the output holds rank 0's samples, then rank 1's, ..."""
+    from torchrec.distributed.dist_data import KJTAllToAll
+    keys, splits = ["f0", "f1", "f2"], [2, 1]
+    for batch_sizes in ([3, 5], [4, 1], [2, 2]):
+        for weighted in (False, True):
+            mine = make_kjt(rank, keys, batch_sizes[rank], 100, weighted)
+            got = KJTAllToAll(dist.group.WORLD, splits, variable_batch_size=True)(mine).wait().wait()
+            lo = sum(splits[:rank])
+            my_keys = keys[lo:lo + splits[rank]]
+            assert got.keys() == my_keys and got.stride() == sum(batch_sizes), (got.stride(), batch_sizes)
+            inputs = [make_kjt(r, keys, batch_sizes[r], 100, weighted) for r in range(world)]
+            for k in my_keys:
+                exp_l = torch.cat([i[k].lengths() for i in inputs])
+                assert torch.equal(got[k].lengths(), exp_l), (k, got[k].lengths(), exp_l)
+                assert torch.equal(got[k].values(), torch.cat([i[k].values() for i in inputs]))
+                if weighted:
+                    assert torch.equal(got[k].weights(), torch.cat([i[k].weights() for i in inputs]))
+
+
+def check_pooled_all2all_variable_batch(rank: int, world: int) -> None:
+    """PooledEmbeddingsAllToAllTest with batch_size_per_rank: rank r receives its own B_r samples."""
+    from torchrec.distributed import comm_ops
+    from torchrec.distributed.dist_data import PooledEmbeddingsAllToAll
+    dims, batch_sizes = [8, 4], [3, 5]
+    B_global, offs = sum(batch_sizes), [0, 3, 8]
+
+    def inp(r):
+        g = torch.Generator().manual_seed(150 + r)
+        return torch.randn(B_global, dims[r], generator=g)
+
+    x = inp(rank).requires_grad_(True)
+    out = PooledEmbeddingsAllToAll(dist.group.WORLD, dims)(x, batch_size_per_rank=batch_sizes).wait()
+    exp = torch.cat([inp(r)[offs[rank]:offs[rank + 1]] for r in range(world)], dim=1)
+    torch.testing.assert_close(out, exp, rtol=0, atol=0)
+
+    def wgt(r):
+        g = torch.Generator().manual_seed(170 + r)
+        return torch.randn(batch_sizes[r], sum(dims), generator=g)
+
+    (out * wgt(rank)).sum().backward()
+    lo = sum(dims[:rank])
+    exp_g = torch.cat([wgt(r)[:, lo:lo + dims[rank]] for r in range(world)], dim=0)
+    if comm_ops.GRADIENT_DIVISION:
+        exp_g = exp_g / world
+    torch.testing.assert_close(x.grad, exp_g, rtol=1e-6, atol=1e-7)
+
+
 def check_row_wise_input_dist(rank: int, world: int) -> None:
     from torchrec.distributed.dist_data import KJTAllToAll
     from torchrec.distributed.embedding_sharding import bucketize_kjt_before_all2all
@@ -149,16 +198,61 @@ def check_sequence_all2all(rank: int, world: int) -> None:
     torch.testing.assert_close(local_embs.grad, torch.cat(rows), rtol=0, atol=0)
 
 
+def check_sharded_tensor_state(rank: int, world: int) -> None:
+    """Checkpoint format (reference batched_embedding_kernel.py:160-246, embedding_kernel.get_state_dict):
+    a row-wise table becomes a ShardedTensor of the global shape whose local shard VIEWS the live rows;
+    momentum1 is sharded along the same rows; an empty shard (fewer rows than ranks) is legal; loading
+    copies shard to shard."""
+    from torch.distributed._shard.sharded_tensor import ShardedTensor
+    from torchrec.distributed.embedding_kernel import copy_state, local_tensor, sharded_tensor_from_local
+    from torchrec.distributed.sharding.rw_sharding import row_wise_shard_sizes
+    from torchrec.distributed.types import ShardMetadata
+    from torchrec.optim.keyed import KeyedOptimizer
+    D = 4
+    for rows in (5, 1):
+        sizes = row_wise_shard_sizes(rows, world)
+        offs = [sum(sizes[:r]) for r in range(world)]
+        metas = [ShardMetadata([offs[r], 0], [sizes[r], D], f"rank:{r}/cuda:{r}") for r in range(world)]
+        live = torch.full((sizes[rank], D), float(rank + 1))
+        mom = torch.arange(sizes[rank], dtype=torch.float32) + 10 * rank
+        w = sharded_tensor_from_local(live, metas[rank], metas, [rows, D], dist.group.WORLD)
+        m = sharded_tensor_from_local(mom, metas[rank], metas, [rows, D], dist.group.WORLD, rowwise=True)
+        assert isinstance(w, ShardedTensor) and tuple(w.size()) == (rows, D) and tuple(m.size()) == (rows,)
+        assert [tuple(x.shard_sizes) for x in w.metadata().shards_metadata] == [(n, D) for n in sizes]
+        assert [tuple(x.shard_offsets) for x in m.metadata().shards_metadata] == [(o,) for o in offs]
+        assert local_tensor(w).data_ptr() == live.data_ptr() or live.numel() == 0  # a view, not a copy
+        local_tensor(w).mul_(2.0)
+        assert torch.equal(live, torch.full((sizes[rank], D), 2.0 * (rank + 1)))
+        # load from a tensor of the local shape and from another ShardedTensor
+        copy_state(w, torch.zeros(sizes[rank], D))
+        assert float(live.abs().sum()) == 0.0
+        src = sharded_tensor_from_local(torch.ones(sizes[rank], D), metas[rank], metas, [rows, D], dist.group.WORLD)
+        copy_state(w, src)
+        assert torch.equal(live, torch.ones(sizes[rank], D))
+        # optimizer checkpoint: state keyed by the parameter's name, momentum loaded shard to shard
+        opt = KeyedOptimizer({"t.weight": w}, {w: {"t.momentum1": m}}, [{"params": [w], "lr": 0.1}])
+        sd = opt.state_dict()
+        assert list(sd["state"]) == ["t.weight"] and isinstance(sd["state"]["t.weight"]["t.momentum1"], ShardedTensor)
+        new_m = sharded_tensor_from_local(torch.full((sizes[rank],), 7.0), metas[rank], metas, [rows, D],
+                                          dist.group.WORLD, rowwise=True)
+        opt.load_state_dict({"state": {"t.weight": {"t.momentum1": new_m}},
+                             "param_groups": [{"params": ["t.weight"], "lr": 0.5}]})
+        assert torch.equal(mom, torch.full((sizes[rank],), 7.0)) and opt.param_groups[0]["lr"] == 0.5
+
+
 def main() -> None:
     import cpu_ops
     cpu_ops.register()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dist.init_process_group("gloo", rank=rank, world_size=world)
     check_kjt_all2all(rank, world)
+    check_kjt_all2all_variable_batch(rank, world)
+    check_pooled_all2all_variable_batch(rank, world)
     check_row_wise_input_dist(rank, world)
     check_pooled_all2all(rank, world)
     check_reduce_scatter(rank, world)
     check_sequence_all2all(rank, world)
+    check_sharded_tensor_state(rank, world)
     dist.barrier()
     if rank == 0:
         print(f"GLOO DIST OK world={world}")

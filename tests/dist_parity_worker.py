@@ -57,12 +57,31 @@ def main() -> None:
         o = sum(sizes[:rank])
         return full[o:o + sizes[rank]]
 
+    from torch.distributed._shard.sharded_tensor import ShardedTensor
+    from torchrec.distributed.embedding_kernel import local_tensor
     gsd = glob.state_dict()
-    for k, v in dmp.state_dict().items():
+    lsd = dmp.state_dict()
+    # checkpoint format: every sharded table is a ShardedTensor of the GLOBAL shape whose
+    # metadata lists one shard per owning rank and whose local shard views the live table
+    for i, (r, s) in enumerate(zip(rows, sharding)):
+        st = lsd[f"sparse_arch.embedding_bag_collection.embedding_bags.t{i}.weight"]
+        assert isinstance(st, ShardedTensor) and tuple(st.size()) == (r, D), (type(st), st.size())
+        metas = st.metadata().shards_metadata
+        assert len(metas) == (1 if s == "table_wise" else world), (s, len(metas))
+        assert sum(m.shard_sizes[0] for m in metas) == r
+        own = [m for m in metas if m.placement.rank() == rank]
+        assert len(st.local_shards()) == len(own)
+    # load: the unsharded weights cut to my shards, through DistributedModelParallel.load_state_dict
+    to_load = {}
+    for k, v in lsd.items():
         if "embedding_bags" in k:
-            v.copy_(shard_of(k.split(".")[-2], gsd[k]))
+            sh = shard_of(k.split(".")[-2], gsd[k])
+            if sh is not None:
+                to_load[k] = sh.clone()
         else:
-            v.copy_(gsd[k])
+            to_load[k] = gsd[k].clone()
+    res = dmp.load_state_dict(to_load)
+    assert not res.missing_keys and not res.unexpected_keys, res
     batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
                                        manual_seed=100 + rank))).to(dev)
     # global batch = concatenation of the per-rank batches along the batch dim
@@ -94,6 +113,7 @@ def main() -> None:
     bad = []
     for k, v in dmp.state_dict().items():
         exp = shard_of(k.split(".")[-2], gsd[k]) if "embedding_bags" in k else gsd[k]
+        v = local_tensor(v)
         err = float((v - exp).abs().max()) if v.numel() else 0.0
         if err > 1e-4:
             bad.append(f"{k}: max abs diff {err:.3e}")

@@ -69,9 +69,10 @@ def main() -> None:
         o = sum(sizes[:rank])
         return full[o:o + sizes[rank]]
 
+    from torchrec.distributed.embedding_kernel import local_tensor
     gsd = glob.state_dict()
     for k, v in dmp.state_dict().items():
-        v.copy_(shard_of(k.split(".")[-2], gsd[k]))
+        local_tensor(v).copy_(shard_of(k.split(".")[-2], gsd[k]))
 
     # per-rank jagged batch; min(rows) = 5 keeps f0's ids valid for both of its tables
     g = torch.Generator().manual_seed(100 + rank)
@@ -112,6 +113,7 @@ def main() -> None:
     bad = []
     for k, v in dmp.state_dict().items():
         exp = shard_of(k.split(".")[-2], gsd[k])
+        v = local_tensor(v)
         err = float((v - exp).abs().max()) if v.numel() else 0.0
         if err > 1e-5:
             bad.append(f"{k}: max abs diff {err:.3e}")

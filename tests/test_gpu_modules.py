@@ -172,8 +172,9 @@ def test_sharded_vs_unsharded_one_step(pg, sharding):
     # copy weights global -> local
     gsd = glob.state_dict()
     lsd = dmp.state_dict()
+    from torchrec.distributed.embedding_kernel import local_tensor
     for k, v in lsd.items():
-        v.data.copy_(gsd[k])
+        local_tensor(v).data.copy_(gsd[k])
     batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=3, num_dense=13,
                                        manual_seed=3))).to(dev)
     dense_opt_g = torch.optim.SGD(glob.parameters(), lr=lr)
@@ -187,7 +188,7 @@ def test_sharded_vs_unsharded_one_step(pg, sharding):
         pg_, pl_ = glob(batch.dense_features, batch.sparse_features), dmp(batch.dense_features, batch.sparse_features)
     torch.testing.assert_close(pl_, pg_, rtol=1e-4, atol=1e-4)
     for k, v in dmp.state_dict().items():
-        torch.testing.assert_close(v, glob.state_dict()[k], rtol=1e-4, atol=1e-5, msg=k)
+        torch.testing.assert_close(local_tensor(v), glob.state_dict()[k], rtol=1e-4, atol=1e-5, msg=k)
 
 
 def test_quantized_ebc():
@@ -246,6 +247,21 @@ def test_sharded_sequence_embeddings_vs_unsharded(world):
                         "--master-addr", "127.0.0.1", "--master-port", "29631",
                         os.path.join(here, "dist_seq_worker.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and f"SEQ PARITY OK world={world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_sharded_variable_batch_size_vs_unsharded(world):
+    """Table-wise sharded EmbeddingBagCollection with a different batch size on every rank and step
+    (KJTAllToAll variable_batch_size, permute_1D recat, ragged pooled all-to-all) equals the unsharded model."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29651",
+                        os.path.join(here, "dist_vb_worker.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and f"VB PARITY OK world={world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
 def test_interaction_row_pitch_and_pitched_linear():
@@ -384,10 +400,9 @@ def test_train_pipeline_sparse_dist_matches_sequential(pg):
 
     a, opt_a = build()
     b, opt_b = build()
-    with torch.no_grad():
-        for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
-            assert ka == kb
-            vb.copy_(va)
+    from torchrec.distributed.embedding_kernel import local_tensor
+    res = b.load_state_dict(a.state_dict())  # ShardedTensor -> ShardedTensor for the tables
+    assert not res.missing_keys and not res.unexpected_keys, res
     ds = iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
                                manual_seed=5))
     host = [next(ds).pin_memory() for _ in range(5)]
@@ -410,4 +425,4 @@ def test_train_pipeline_sparse_dist_matches_sequential(pg):
     assert len(pipe_losses) == len(host)
     np.testing.assert_allclose(pipe_losses, seq_losses, rtol=1e-5, atol=1e-6)
     for (k, va), (_, vb) in zip(a.state_dict().items(), b.state_dict().items()):
-        torch.testing.assert_close(vb, va, rtol=1e-5, atol=1e-6, msg=k)
+        torch.testing.assert_close(local_tensor(vb), local_tensor(va), rtol=1e-5, atol=1e-6, msg=k)

@@ -165,3 +165,90 @@ def test_world2_gloo_sharded_data_movement():
                         "--master-addr", "127.0.0.1", "--master-port", "29741",
                         os.path.join(HERE, "dist_gloo_worker.py")], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and "GLOO DIST OK world=2" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+# ---------------------------------------------------------------- binary Criteo datapipe
+def test_binary_criteo_utils_known_answers(tmp_path):
+    """get_file_idx_to_row_range / load_npy_range against the reference's own expectations
+    (torchrec/datasets/tests/test_criteo.py:164-193) and the fixture the reference class produced."""
+    import numpy as np
+    from golden_cases import CRITEO_PATH
+    from torchrec.datasets.criteo import BinaryCriteoUtils
+    expected = [{0: (0, 13), 1: (0, 2)}, {1: (3, 16), 2: (0, 2)}, {2: (3, 19)}]
+    z = np.load(CRITEO_PATH)
+    for r in range(3):
+        got = BinaryCriteoUtils.get_file_idx_to_row_range(lengths=[14, 17, 20], rank=r, world_size=3)
+        assert got == expected[r]
+        assert [[k, a, b] for k, (a, b) in sorted(got.items())] == z[f"row_range/rank{r}"].tolist()
+    full = np.random.default_rng(0).random((10, 13), dtype=np.float32)
+    path = str(tmp_path / "dense.npy")
+    np.save(path, full)
+    assert BinaryCriteoUtils.get_shape_from_npy(path) == (10, 13)
+    for mmap in (False, True):
+        np.testing.assert_array_equal(BinaryCriteoUtils.load_npy_range(path, 2, 4, mmap_mode=mmap), full[2:6])
+    with pytest.raises(ValueError, match="out of bounds"):
+        BinaryCriteoUtils.load_npy_range(path, 10, 1)
+    with pytest.raises(ValueError, match="exceeds number of available rows"):
+        BinaryCriteoUtils.load_npy_range(path, 8, 3)
+
+
+@pytest.mark.parametrize("mmap_mode", [False, True])
+def test_binary_criteo_datapipe_matches_reference_fixture(tmp_path, mmap_mode):
+    """Every batch of every rank equals, bit for bit, what the reference's InMemoryBinaryCriteoIterDataPipe
+    produced from the same seeded day files (fixture: tests/golden/make_golden_criteo.py)."""
+    import numpy as np
+    from golden_cases import CRITEO_CASES, CRITEO_PATH, write_criteo_days
+    from torchrec.datasets.criteo import CAT_FEATURE_COUNT, INT_FEATURE_COUNT, InMemoryBinaryCriteoIterDataPipe
+    z = np.load(CRITEO_PATH)
+    for ci, (rows_per_file, batch_size, world, use_hashes, seed) in enumerate(CRITEO_CASES):
+        folder = tmp_path / f"case{ci}"
+        folder.mkdir()
+        dense, sparse, labels = write_criteo_days(str(folder), rows_per_file, seed)
+        hashes = [3 * i + 2 for i in range(CAT_FEATURE_COUNT)] if use_hashes else None
+        lens = set()
+        for rank in range(world):
+            pipe = InMemoryBinaryCriteoIterDataPipe(dense, sparse, labels, batch_size=batch_size, rank=rank,
+                                                    world_size=world, hashes=hashes, mmap_mode=mmap_mode)
+            batches = list(pipe)
+            pre = f"case{ci}/rank{rank}"
+            assert len(batches) == len(pipe) == int(z[f"{pre}/num_batches"])
+            lens.add(len(batches))
+            for b, batch in enumerate(batches):
+                kjt = batch.sparse_features
+                assert tuple(batch.dense_features.shape) == (batch_size, INT_FEATURE_COUNT)
+                assert tuple(batch.labels.shape) == (batch_size,) and kjt.stride() == batch_size
+                for got, name in ((batch.dense_features, "dense"), (kjt.values(), "values"),
+                                  (batch.labels, "labels")):
+                    exp = z[f"{pre}/{name}"][b]
+                    assert got.numpy().dtype == exp.dtype, (name, got.dtype, exp.dtype)
+                    np.testing.assert_array_equal(got.numpy(), exp, err_msg=f"{pre} batch {b} {name}")
+                np.testing.assert_array_equal(kjt.lengths().numpy(), z[f"{pre}/lengths"])
+                np.testing.assert_array_equal(kjt.offsets().numpy(), z[f"{pre}/offsets"])
+                assert kjt.keys() == z[f"{pre}/keys"].tolist()
+                if hashes is not None:
+                    v = kjt.values().view(CAT_FEATURE_COUNT, batch_size)
+                    assert bool((v < torch.tensor(hashes).view(-1, 1)).all())
+        assert len(lens) == 1  # every rank serves the same number of batches
+
+
+def test_binary_criteo_datapipe_shuffle_batches(tmp_path):
+    """shuffle_batches permutes the rows INSIDE each batch, dense / ids / labels in unison."""
+    import numpy as np
+    from golden_cases import write_criteo_days
+    from torchrec.datasets.criteo import CAT_FEATURE_COUNT, InMemoryBinaryCriteoIterDataPipe
+    dense, sparse, labels = write_criteo_days(str(tmp_path), [11, 30, 7], 9)
+    plain = list(InMemoryBinaryCriteoIterDataPipe(dense, sparse, labels, batch_size=12, rank=0, world_size=1))
+    np.random.seed(0)
+    shuf = list(InMemoryBinaryCriteoIterDataPipe(dense, sparse, labels, batch_size=12, rank=0, world_size=1,
+                                                 shuffle_batches=True))
+    assert len(plain) == len(shuf) == 4
+    moved = False
+    for p, s in zip(plain, shuf):
+        rows_p = np.concatenate([p.dense_features.numpy(), p.sparse_features.values().view(CAT_FEATURE_COUNT, -1).T.numpy(),
+                                 p.labels.numpy()[:, None]], axis=1)
+        rows_s = np.concatenate([s.dense_features.numpy(), s.sparse_features.values().view(CAT_FEATURE_COUNT, -1).T.numpy(),
+                                 s.labels.numpy()[:, None]], axis=1)
+        order = np.lexsort(rows_p.T[::-1]), np.lexsort(rows_s.T[::-1])
+        np.testing.assert_array_equal(rows_p[order[0]], rows_s[order[1]])
+        moved |= not np.array_equal(rows_p, rows_s)
+    assert moved

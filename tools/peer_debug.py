@@ -7,6 +7,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "torchrec-oldfork_b200"))
+from torchrec.distributed.embedding_kernel import local_tensor  # noqa: E402
 
 
 def main():
@@ -42,7 +43,7 @@ def main():
     a, b = build(True), build(False)
     with torch.no_grad():
         for (k, va), (_, vb) in zip(a.state_dict().items(), b.state_dict().items()):
-            vb.copy_(va)
+            local_tensor(vb).copy_(local_tensor(va))
     batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
                                        manual_seed=100 + rank))).to(dev)
     os.environ["B200_PEER_DIST"] = "1"   # read at the first forward

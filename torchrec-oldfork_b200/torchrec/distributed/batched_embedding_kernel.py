@@ -16,6 +16,7 @@ from fbgemm_gpu.split_table_batched_embeddings_ops import (
     ComputeDevice, EmbeddingLocation, PoolingMode, SplitTableBatchedEmbeddingBagsCodegen)
 from torch import nn
 
+from torchrec.distributed.embedding_kernel import get_state_dict, load_state_dict_into, table_sharded_tensor
 from torchrec.distributed.embedding_types import GroupedEmbeddingConfig, ShardedEmbeddingTable
 from torchrec.modules.embedding_configs import data_type_to_sparse_type, pooling_type_to_pooling_mode
 from torchrec.optim.fused import FusedOptimizer, FusedOptimizerModule
@@ -25,7 +26,9 @@ from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
 class EmbeddingFusedOptimizer(FusedOptimizer):
     """Exposes the TBE module's in-place optimizer: params are the per-table weight views, state is
     `<table>.momentum1` for rowwise Adagrad; step()/zero_grad() only push the learning rate
-    (reference :250-257)."""
+    (reference :250-257).  With a process group both are ShardedTensors over the table's shards
+    (reference :160-246: weights with the table's metadata, momentum1 sharded along the rows) whose
+    local shard is the live view; without one (unsharded use) they are the views themselves."""
 
     def __init__(self, config: GroupedEmbeddingConfig, emb_module: SplitTableBatchedEmbeddingBagsCodegen,
                  pg: Optional[dist.ProcessGroup] = None) -> None:
@@ -37,10 +40,15 @@ class EmbeddingFusedOptimizer(FusedOptimizer):
         opt_states = emb_module.split_optimizer_states()
         for table, w, st in zip(config.embedding_tables, weights, opt_states):
             name = f"{table.name}.weight"
+            sharded = pg is not None and table.global_metadata is not None and table.local_metadata is not None
+            if sharded:
+                w = table_sharded_tensor(table, w, pg)
             params[name] = w
             state[w] = {}
             if emb_module.optimizer == EmbOptimType.EXACT_ROWWISE_ADAGRAD:
-                state[w][f"{table.name}.momentum1"] = st[0]
+                m1 = st[0]
+                state[w][f"{table.name}.momentum1"] = (table_sharded_tensor(table, m1, pg, rowwise=True)
+                                                       if sharded else m1)
         param_group = {"params": list(params.values()), "lr": emb_module.optimizer_args.learning_rate}
         super().__init__(params, state, [param_group])
 
@@ -84,12 +92,17 @@ class BaseBatchedEmbeddingBag(nn.Module):
                                per_sample_weights=features.weights_or_none())
 
     def state_dict(self, destination=None, prefix: str = "", keep_vars: bool = False) -> Dict[str, Any]:
+        """`<table>.weight` -> ShardedTensor whose local shard views the live table (reference :557-570 ->
+        embedding_kernel.get_state_dict); plain views without a process group."""
         self.flush()
-        if destination is None:
-            destination = {}
-        for t, w in zip(self._config.embedding_tables, self.emb_module.split_embedding_weights()):
-            destination[f"{prefix}{t.name}.weight"] = w
-        return destination
+        return get_state_dict(self._config.embedding_tables, self.emb_module.split_embedding_weights(), self._pg,
+                              destination, prefix)
+
+    def load_state_dict(self, state_dict, strict: bool = True):
+        missing, unexpected = load_state_dict_into([self], state_dict)
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"load_state_dict: missing keys {missing}, unexpected keys {unexpected}")
+        return missing, unexpected
 
     def split_embedding_weights(self) -> List[torch.Tensor]:
         return self.emb_module.split_embedding_weights()

@@ -64,16 +64,17 @@ class _AwaitTensor(Awaitable[torch.Tensor]):
 
 # ------------------------------------------------------------------ all-to-all (table-wise)
 class _A2AInfo:
-    def __init__(self, dim_sum_per_rank: List[int], B_global: int, B_local: int, D_local_sum: int) -> None:
-        self.dims, self.B_global, self.B_local, self.D_local_sum = dim_sum_per_rank, B_global, B_local, D_local_sum
+    def __init__(self, dim_sum_per_rank: List[int], batch_size_per_rank: List[int], B_local: int,
+                 D_local_sum: int) -> None:
+        self.dims, self.batch_sizes = dim_sum_per_rank, batch_size_per_rank
+        self.B_global, self.B_local, self.D_local_sum = sum(batch_size_per_rank), B_local, D_local_sum
 
 
 class All2All_Pooled_Req(Function):
     @staticmethod
     def forward(ctx, pg, req: _Request, info: _A2AInfo, embs: torch.Tensor) -> torch.Tensor:
-        W = dist.get_world_size(pg)
         send = embs.contiguous().view(-1)
-        in_splits = [info.D_local_sum * info.B_local] * W
+        in_splits = [info.D_local_sum * b for b in info.batch_sizes]  # rank r gets its B_r samples
         out_splits = [d * info.B_local for d in info.dims]
         recv = send.new_empty(sum(out_splits))
         req.work = dist.all_to_all_single(recv, send, output_split_sizes=out_splits,
@@ -108,10 +109,9 @@ class All2All_Pooled_Wait(Function):
     def backward(ctx, grad_out: torch.Tensor):
         req, pg = ctx.req, ctx.pg
         info: _A2AInfo = req.info
-        W = dist.get_world_size(pg)
         send = _recat(grad_out.contiguous(), info.dims, info.B_local, False)
         in_splits = [d * info.B_local for d in info.dims]
-        out_splits = [info.D_local_sum * info.B_local] * W
+        out_splits = [info.D_local_sum * b for b in info.batch_sizes]
         recv = send.new_empty(sum(out_splits))
         req.work = dist.all_to_all_single(recv, send, output_split_sizes=out_splits,
                                           input_split_sizes=in_splits, group=pg, async_op=True)
@@ -119,19 +119,26 @@ class All2All_Pooled_Wait(Function):
         return None, None, req.dummy.new_zeros(1)
 
 
-def alltoall_pooled(a2a_pooled_embs_tensor: torch.Tensor, dim_sum_per_rank: List[int],
-                    mode=None, group: Optional[dist.ProcessGroup] = None) -> Awaitable[torch.Tensor]:
-    """[B_global, D_local_sum] on every rank -> [B_local, sum_r D_r]."""
+def alltoall_pooled(a2a_pooled_embs_tensor: torch.Tensor, batch_size_per_rank: List[int],
+                    dim_sum_per_rank: List[int], dim_sum_per_rank_tensor: Optional[torch.Tensor] = None,
+                    cumsum_dim_sum_per_rank_tensor: Optional[torch.Tensor] = None,
+                    group: Optional[dist.ProcessGroup] = None) -> Awaitable[torch.Tensor]:
+    """[B_global, D_local_sum] on every rank -> [B_local, sum_r D_r] (reference :203-257, same
+    argument order).  batch_size_per_rank[r] samples go to rank r (B_global = their sum; the sizes
+    may differ between ranks).  The two *_tensor arguments feed the reference's fast recat kernel;
+    b200_pooled_a2a_recat builds its own column table, they are accepted and unused."""
     group = group if group is not None else dist.distributed_c10d._get_default_group()
     W = dist.get_world_size(group)
     if W <= 1:
         return NoWait(a2a_pooled_embs_tensor)
     B_global, D_local_sum = a2a_pooled_embs_tensor.shape
-    assert B_global % W == 0, "variable batch size per rank is out of scope"
+    assert len(batch_size_per_rank) == W and B_global == sum(batch_size_per_rank), (
+        f"batch_size_per_rank {batch_size_per_rank} does not add up to {B_global} rows")
     req = _Request(group)
     # the dummy output links Req and Wait in the autograd graph
     req.dummy = All2All_Pooled_Req.apply(
-        group, req, _A2AInfo(dim_sum_per_rank, B_global, B_global // W, D_local_sum), a2a_pooled_embs_tensor)
+        group, req, _A2AInfo(dim_sum_per_rank, list(batch_size_per_rank),
+                             batch_size_per_rank[dist.get_rank(group)], D_local_sum), a2a_pooled_embs_tensor)
     return _AwaitTensor(All2All_Pooled_Wait, req)
 
 

@@ -22,15 +22,31 @@ from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
 
 
 def _get_recat(local_split: int, num_splits: int, stagger: int = 1,
-               device: Optional[torch.device] = None) -> torch.Tensor:
+               device: Optional[torch.device] = None,
+               batch_size_per_rank: Optional[List[int]] = None) -> torch.Tensor:
     """Permutation taking (source rank, local feature) order to (local feature, source rank):
-    _get_recat(2, 4, 1) == [0, 2, 4, 6, 1, 3, 5, 7]; _get_recat(2, 4, 2) == [0, 4, 2, 6, 1, 5, 3, 7]."""
+    _get_recat(2, 4, 1) == [0, 2, 4, 6, 1, 3, 5, 7]; _get_recat(2, 4, 2) == [0, 4, 2, 6, 1, 5, 3, 7].
+
+    With `batch_size_per_rank` (variable batch size, reference :84-116) the segment permutation is
+    expanded to one entry per (feature, sample) length slot - segment (r, f) holds
+    batch_size_per_rank[r] slots - so permute_1D_sparse_data can apply it."""
     if local_split == 0:
         return torch.tensor([], device=device, dtype=torch.int32)
     per = num_splits // stagger
     rank_order = [x + per * y for x in range(per) for y in range(stagger)]
-    return torch.tensor([f + r * local_split for f in range(local_split) for r in rank_order],
-                        device=device, dtype=torch.int32)
+    recat = [f + r * local_split for f in range(local_split) for r in rank_order]
+    recat_t = torch.tensor(recat, device=device, dtype=torch.int32)
+    if batch_size_per_rank is None:
+        return recat_t
+    seg = [b for b in batch_size_per_rank for _ in range(local_split)]
+    in_off, out_off = [0], [0]
+    for b in seg:
+        in_off.append(in_off[-1] + b)
+    for r in recat:
+        out_off.append(out_off[-1] + seg[r])
+    return torch.ops.fbgemm.expand_into_jagged_permute(
+        recat_t, torch.tensor(in_off, device=device, dtype=torch.int32),
+        torch.tensor(out_off, device=device, dtype=torch.int32), out_off[-1])
 
 
 def _split_lengths(splits: List[int], keys: List[str], offset_per_key: List[int]) -> List[int]:
@@ -47,8 +63,10 @@ class KJTAllToAllIndicesAwaitable(Awaitable[KeyedJaggedTensor]):
 
     def __init__(self, pg, input: KeyedJaggedTensor, lengths: torch.Tensor, splits: List[int], keys: List[str],
                  recat: torch.Tensor, in_lengths_per_worker: List[int], out_lengths_per_worker: List[int],
-                 batch_size_per_rank: List[int], length_per_key: Optional[List[int]] = None) -> None:
+                 batch_size_per_rank: List[int], length_per_key: Optional[List[int]] = None,
+                 variable_batch_size: bool = False) -> None:
         super().__init__()
+        self._variable_batch_size = variable_batch_size
         self._pg, self._input, self._lengths, self._splits = pg, input, lengths, splits
         self._keys, self._recat = keys, recat
         self._workers = dist.get_world_size(pg)
@@ -83,35 +101,56 @@ class KJTAllToAllIndicesAwaitable(Awaitable[KeyedJaggedTensor]):
             w.wait()
         lengths, values, weights = self._lengths, self._values, self._weights
         if self._recat.numel() > 0:
-            rows = self._workers * self._splits[dist.get_rank(self._pg)]
-            lengths, values, weights = torch.ops.fbgemm.permute_2D_sparse_data(
-                self._recat, lengths.view(rows, -1), values, weights, values.numel())
-            lengths = lengths.view(-1)
+            if self._variable_batch_size:  # per-slot permutation (reference :248-255)
+                lengths, values, weights = torch.ops.fbgemm.permute_1D_sparse_data(
+                    self._recat, lengths.view(-1), values, weights, values.numel())
+            else:
+                rows = self._workers * self._splits[dist.get_rank(self._pg)]
+                lengths, values, weights = torch.ops.fbgemm.permute_2D_sparse_data(
+                    self._recat, lengths.view(rows, -1), values, weights, values.numel())
+                lengths = lengths.view(-1)
         return KeyedJaggedTensor(keys=self._keys, values=values, weights=weights, lengths=lengths,
                                  stride=sum(self._batch_size_per_rank), length_per_key=self._length_per_key)
 
 
 class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
-    """Phase 1: lengths exchange; wait() reads the receive sizes and starts phase 2."""
+    """Phase 1: lengths exchange; wait() reads the receive sizes and starts phase 2.
 
-    def __init__(self, pg, input: KeyedJaggedTensor, splits: List[int], keys: List[str], recat: torch.Tensor) -> None:
+    variable_batch_size (reference :321-345): the ranks first exchange their batch sizes (one int
+    each, read on the host - it sizes every later buffer), the recat permutation is rebuilt per
+    call with one slot per (feature, sample), and the lengths exchange has ragged receive splits."""
+
+    def __init__(self, pg, input: KeyedJaggedTensor, splits: List[int], keys: List[str], recat: torch.Tensor,
+                 stagger: int = 1, variable_batch_size: bool = False) -> None:
         super().__init__()
         self._pg, self._input, self._splits, self._keys, self._recat = pg, input, splits, keys, recat
         self._workers = dist.get_world_size(pg)
         self._local_split = splits[dist.get_rank(pg)]
+        self._variable_batch_size = variable_batch_size
         B = input.stride()
         self._batch_size_per_rank = [B] * self._workers
+        self._batch_size_per_rank_tensor: Optional[torch.Tensor] = None
         self._lengths = input.lengths()
         self._in_lengths_per_worker: List[int] = []
         self._work = None
         if self._workers == 1:
             return
         src = input.lengths().contiguous().view(-1)
-        self._lengths = src.new_empty(self._local_split * B * self._workers)
+        if variable_batch_size:
+            mine = torch.full((self._workers,), B, device=src.device, dtype=torch.int32)
+            theirs = torch.empty_like(mine)
+            dist.all_to_all_single(theirs, mine, output_split_sizes=[1] * self._workers,
+                                   input_split_sizes=[1] * self._workers, group=pg)
+            self._batch_size_per_rank_tensor = theirs
+            self._batch_size_per_rank = theirs.cpu().tolist()
+            self._recat = _get_recat(self._local_split, len(splits), stagger, src.device,
+                                     self._batch_size_per_rank)
+        self._output_split_sizes = [self._local_split * b for b in self._batch_size_per_rank]
+        self._lengths = src.new_empty(sum(self._output_split_sizes))
         # the lengths exchange has fixed split sizes; the (data-dependent) send sizes of the values
         # exchange are read in wait(), so issuing phase 1 never blocks the host
         self._work = dist.all_to_all_single(
-            self._lengths, src, output_split_sizes=[self._local_split * B] * self._workers,
+            self._lengths, src, output_split_sizes=self._output_split_sizes,
             input_split_sizes=[s * B for s in splits], group=pg, async_op=True)
 
     def _wait_impl(self) -> KJTAllToAllIndicesAwaitable:
@@ -123,7 +162,13 @@ class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
             self._work.wait()
             if self._local_split > 0:
                 # one D2H read: [W, F_local] totals -> receive splits and per-key totals
-                table = self._lengths.view(self._workers, self._local_split, -1).sum(dim=2).cpu()
+                if self._variable_batch_size:
+                    table = torch.stack([
+                        (c.view(self._local_split, -1).sum(dim=1) if c.numel()
+                         else c.new_zeros(self._local_split))
+                        for c in self._lengths.split(self._output_split_sizes)]).cpu()
+                else:
+                    table = self._lengths.view(self._workers, self._local_split, -1).sum(dim=2).cpu()
                 out_lengths_per_worker = table.sum(dim=1).tolist()
                 length_per_key = table.sum(dim=0).tolist()
             else:
@@ -131,19 +176,21 @@ class KJTAllToAllLengthsAwaitable(Awaitable[KJTAllToAllIndicesAwaitable]):
                 length_per_key = []
         return KJTAllToAllIndicesAwaitable(
             self._pg, self._input, self._lengths, self._splits, self._keys, self._recat,
-            self._in_lengths_per_worker, out_lengths_per_worker, self._batch_size_per_rank, length_per_key)
+            self._in_lengths_per_worker, out_lengths_per_worker, self._batch_size_per_rank, length_per_key,
+            self._variable_batch_size and self._workers > 1)
 
 
 class KJTAllToAll(nn.Module):
-    """Redistributes a KJT whose keys are ordered by destination rank (`splits[r]` keys to rank r)."""
+    """Redistributes a KJT whose keys are ordered by destination rank (`splits[r]` keys to rank r).
+    variable_batch_size: every rank may bring a different batch size; the output KJT has
+    stride sum_r B_r with rank r's samples at columns [sum_{q<r} B_q, +B_r) of every key."""
 
     def __init__(self, pg: dist.ProcessGroup, splits: List[int], device: Optional[torch.device] = None,
                  stagger: int = 1, variable_batch_size: bool = False) -> None:
         super().__init__()
         assert len(splits) == dist.get_world_size(pg)
-        if variable_batch_size:
-            raise NotImplementedError("variable batch size per rank is out of scope (SURVEY.md §8 f3)")
         self._pg, self._splits = pg, splits
+        self._stagger, self._variable_batch_size = stagger, variable_batch_size
         self._no_dist = all(s == 0 for s in splits)
         self._splits_cumsum = [0]
         for s in splits:
@@ -154,7 +201,8 @@ class KJTAllToAll(nn.Module):
     def forward(self, input: KeyedJaggedTensor) -> Awaitable[KJTAllToAllIndicesAwaitable]:
         rank = dist.get_rank(self._pg)
         keys = input.keys()[self._splits_cumsum[rank]:self._splits_cumsum[rank + 1]]
-        return KJTAllToAllLengthsAwaitable(self._pg, input, self._splits, keys, self._recat)
+        return KJTAllToAllLengthsAwaitable(self._pg, input, self._splits, keys, self._recat, self._stagger,
+                                           self._variable_batch_size)
 
 
 class PooledEmbeddingsAwaitable(Awaitable[torch.Tensor]):
@@ -177,7 +225,11 @@ class PooledEmbeddingsAllToAll(nn.Module):
 
     def forward(self, local_embs: torch.Tensor, batch_size_per_rank: Optional[List[int]] = None
                 ) -> PooledEmbeddingsAwaitable:
-        aw = PooledEmbeddingsAwaitable(alltoall_pooled(local_embs, self._dim_sum_per_rank, group=self._pg))
+        if batch_size_per_rank is None:
+            W = dist.get_world_size(self._pg)
+            batch_size_per_rank = [local_embs.shape[0] // W] * W
+        aw = PooledEmbeddingsAwaitable(
+            alltoall_pooled(local_embs, batch_size_per_rank, self._dim_sum_per_rank, group=self._pg))
         aw.callbacks.extend(self._callbacks)
         return aw
 

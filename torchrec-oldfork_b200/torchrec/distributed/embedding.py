@@ -190,6 +190,22 @@ class ShardedEmbeddingCollection(ShardedModule[SparseFeaturesList, List[torch.Te
             lookup.state_dict(destination, prefix + "embeddings.", keep_vars)
         return destination
 
+    def load_state_dict(self, state_dict, strict: bool = True):
+        """Loads `embeddings.<table>.weight` entries (ShardedTensor or local-shard tensors) into the live
+        tables (reference load_state_dict: per-lookup copy of the matching keys)."""
+        from torch.nn.modules.module import _IncompatibleKeys
+        from torchrec.distributed.embedding_kernel import filter_state_dict
+        sub = filter_state_dict(state_dict, "embeddings")
+        missing, seen = [], set()
+        for lookup in self._lookups:
+            m, u = lookup.load_state_dict(sub, strict)
+            missing.extend("embeddings." + k for k in m)
+            seen.update(k for k in sub if k not in u)
+        unexpected = ["embeddings." + k for k in sub if k not in seen]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"load_state_dict: missing keys {missing}, unexpected keys {unexpected}")
+        return _IncompatibleKeys(missing_keys=missing, unexpected_keys=unexpected)
+
     def named_parameters(self, prefix: str = "", recurse: bool = True):
         for lookup in self._lookups:
             yield from lookup.named_parameters(prefix + ("." if prefix else "") + "embeddings", recurse)

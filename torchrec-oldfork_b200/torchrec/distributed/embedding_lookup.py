@@ -69,6 +69,12 @@ class GroupedPooledEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Te
             m.state_dict(destination, prefix, keep_vars)
         return destination
 
+    def load_state_dict(self, state_dict, strict: bool = True):
+        """Copies into the live tables; entries may be ShardedTensors or tensors of the local shard shape
+        (reference _load_state_dict :50-74).  Returns (missing_keys, unexpected_keys)."""
+        from torchrec.distributed.embedding_kernel import load_state_dict_into
+        return load_state_dict_into(self._all_modules(), state_dict)
+
     def named_parameters(self, prefix: str = "", recurse: bool = True):
         yield from ()
 
@@ -115,6 +121,10 @@ class GroupedEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Tensor],
         for m in self._emb_modules:
             m.state_dict(destination, prefix, keep_vars)
         return destination
+
+    def load_state_dict(self, state_dict, strict: bool = True):
+        from torchrec.distributed.embedding_kernel import load_state_dict_into
+        return load_state_dict_into(list(self._emb_modules), state_dict)
 
     def named_parameters(self, prefix: str = "", recurse: bool = True):
         yield from ()

@@ -21,6 +21,8 @@ from torchrec.distributed.embedding_types import (
     EmbeddingComputeKernel, SparseFeatures, SparseFeaturesList)
 from torchrec.distributed.sharding.rw_sharding import RwPooledEmbeddingSharding
 from torchrec.distributed.sharding.tw_sharding import TwPooledEmbeddingSharding
+from torchrec.distributed.sharding.vb_sharding import VariableBatchShardingContext
+from torchrec.distributed.sharding.vb_tw_sharding import VariableBatchTwPooledEmbeddingSharding
 from torchrec.distributed.types import (
     Awaitable, LazyAwaitable, ModuleSharder, NoWait, ParameterSharding, ShardedModule, ShardedModuleContext,
     ShardingEnv, ShardingType)
@@ -34,7 +36,13 @@ EmbeddingInfo = Tuple[EmbeddingTableConfig, ParameterSharding, torch.Tensor]
 
 
 def create_embedding_bag_sharding(sharding_type: str, embedding_configs: List[EmbeddingInfo], env: ShardingEnv,
-                                  device: Optional[torch.device] = None) -> EmbeddingSharding:
+                                  device: Optional[torch.device] = None,
+                                  variable_batch_size: bool = False) -> EmbeddingSharding:
+    if variable_batch_size:
+        if sharding_type == ShardingType.TABLE_WISE.value:
+            return VariableBatchTwPooledEmbeddingSharding(embedding_configs, env, device)
+        raise ValueError(f"variable batch size per rank is built for table_wise sharding, not {sharding_type} "
+                         "(the reference has vb_tw_sharding / vb_cw_sharding only)")
     if sharding_type == ShardingType.TABLE_WISE.value:
         return TwPooledEmbeddingSharding(embedding_configs, env, device)
     if sharding_type == ShardingType.ROW_WISE.value:
@@ -105,11 +113,15 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
                                     FusedOptimizerModule):
     def __init__(self, module: EmbeddingBagCollectionInterface,
                  table_name_to_parameter_sharding: Dict[str, ParameterSharding], env: ShardingEnv,
-                 fused_params: Optional[Dict[str, Any]] = None, device: Optional[torch.device] = None) -> None:
+                 fused_params: Optional[Dict[str, Any]] = None, device: Optional[torch.device] = None,
+                 variable_batch_size: bool = False) -> None:
         super().__init__()
         by_type = create_embedding_configs_by_sharding(module, table_name_to_parameter_sharding, "embedding_bags.")
+        # variable_batch_size: every rank may feed a different batch size each step (vb_tw_sharding.py)
+        self._variable_batch_size = variable_batch_size
         self._sharding_type_to_sharding: Dict[str, EmbeddingSharding] = OrderedDict(
-            (st, create_embedding_bag_sharding(st, cfgs, env, device)) for st, cfgs in by_type.items())
+            (st, create_embedding_bag_sharding(st, cfgs, env, device, variable_batch_size))
+            for st, cfgs in by_type.items())
         self._is_weighted: bool = module.is_weighted
         self._device = device
         self._embedding_bag_configs = module.embedding_bag_configs
@@ -163,6 +175,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
             self._create_input_dist(features.keys())
             self._has_uninitialized_input_dist = False
         ctx.local_batch = features.stride()
+        ctx.vb_contexts = []
         with torch.no_grad():
             if self._has_features_permute:
                 features = features.permute(self._features_order, self._features_order_tensor)
@@ -171,7 +184,14 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
             for dist_module, f in zip(self._input_dists, shards):
                 sf = SparseFeatures(id_list_features=None if self._is_weighted else f,
                                     id_score_list_features=f if self._is_weighted else None)
-                awaitables.append(dist_module(sf))
+                aw = dist_module(sf)
+                if self._variable_batch_size:
+                    # the batch sizes were exchanged while the lengths all-to-all was being set up
+                    la = aw._b if self._is_weighted else aw._a
+                    ctx.vb_contexts.append(VariableBatchShardingContext(
+                        batch_size_per_rank=list(la._batch_size_per_rank),
+                        batch_size_per_rank_tensor=la._batch_size_per_rank_tensor))
+                awaitables.append(aw)
             return SparseFeaturesListAwaitable(awaitables)
 
     def compute(self, ctx: ShardedModuleContext, dist_input: SparseFeaturesList) -> List[torch.Tensor]:
@@ -180,6 +200,10 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
     def output_dist(self, ctx: ShardedModuleContext, output: List[torch.Tensor]) -> LazyAwaitable[KeyedTensor]:
         if self._has_uninitialized_output_dist:
             self._create_output_dist()
+        if self._variable_batch_size:
+            return EmbeddingBagCollectionAwaitable(
+                [d(e, c) for d, e, c in zip(self._output_dists, output, ctx.vb_contexts)],
+                self._embedding_dims, self._embedding_names)
         return EmbeddingBagCollectionAwaitable([d(e) for d, e in zip(self._output_dists, output)],
                                                self._embedding_dims, self._embedding_names)
 
@@ -187,7 +211,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         if not self._peer_checked:
             from torchrec.distributed import peer_dist
             self._peer_checked = True
-            if not self._is_weighted:
+            if not self._is_weighted and not self._variable_batch_size:
                 self._peer = peer_dist.try_build(self, self._env.process_group, self._device)
         return self._peer
 
@@ -195,6 +219,8 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
                                 ) -> LazyAwaitable[KeyedTensor]:
         if self._has_uninitialized_output_dist:
             self._create_output_dist()
+        if self._variable_batch_size:
+            return self.output_dist(ctx, self.compute(ctx, input))
         peer = self._peer_dist()
         if peer is not None:
             values = peer(input, ctx.local_batch)
@@ -211,6 +237,22 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         for lookup in self._lookups:
             lookup.state_dict(destination, prefix + "embedding_bags.", keep_vars)
         return destination
+
+    def load_state_dict(self, state_dict, strict: bool = True):
+        """Loads `embedding_bags.<table>.weight` entries (ShardedTensor or local-shard tensors) into the live
+        tables (reference load_state_dict: per-lookup copy of the matching keys)."""
+        from torch.nn.modules.module import _IncompatibleKeys
+        from torchrec.distributed.embedding_kernel import filter_state_dict
+        sub = filter_state_dict(state_dict, "embedding_bags")
+        missing, seen = [], set()
+        for lookup in self._lookups:
+            m, u = lookup.load_state_dict(sub, strict)
+            missing.extend("embedding_bags." + k for k in m)
+            seen.update(k for k in sub if k not in u)
+        unexpected = ["embedding_bags." + k for k in sub if k not in seen]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"load_state_dict: missing keys {missing}, unexpected keys {unexpected}")
+        return _IncompatibleKeys(missing_keys=missing, unexpected_keys=unexpected)
 
     def named_parameters(self, prefix: str = "", recurse: bool = True):
         for lookup in self._lookups:
@@ -237,12 +279,14 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
 
 
 class EmbeddingBagCollectionSharder(ModuleSharder[EmbeddingBagCollection]):
-    def __init__(self, fused_params: Optional[Dict[str, Any]] = None) -> None:
+    def __init__(self, fused_params: Optional[Dict[str, Any]] = None, variable_batch_size: bool = False) -> None:
         self._fused_params = fused_params
+        self._variable_batch_size = variable_batch_size
 
     def shard(self, module: EmbeddingBagCollection, params: Dict[str, ParameterSharding], env: ShardingEnv,
               device: Optional[torch.device] = None) -> ShardedEmbeddingBagCollection:
-        return ShardedEmbeddingBagCollection(module, params, env, self._fused_params, device)
+        return ShardedEmbeddingBagCollection(module, params, env, self._fused_params, device,
+                                             variable_batch_size=self._variable_batch_size)
 
     def shardable_parameters(self, module: EmbeddingBagCollection) -> Dict[str, nn.Parameter]:
         return {name.split(".")[0]: p for name, p in module.embedding_bags.named_parameters()}
@@ -252,6 +296,8 @@ class EmbeddingBagCollectionSharder(ModuleSharder[EmbeddingBagCollection]):
         return EmbeddingBagCollection
 
     def sharding_types(self, compute_device_type: str) -> List[str]:
+        if self._variable_batch_size:
+            return [ShardingType.TABLE_WISE.value]
         return [ShardingType.TABLE_WISE.value, ShardingType.ROW_WISE.value]
 
     def compute_kernels(self, sharding_type: str, compute_device_type: str) -> List[str]:

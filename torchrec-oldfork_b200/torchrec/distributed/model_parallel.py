@@ -165,6 +165,28 @@ class DistributedModelParallel(nn.Module, FusedOptimizerModule):
         return self.module.state_dict(destination=destination, prefix=prefix, keep_vars=keep_vars) \
             if destination is not None else self.module.state_dict(prefix=prefix, keep_vars=keep_vars)
 
+    def load_state_dict(self, state_dict, prefix: str = "", strict: bool = True):
+        """Sharded modules load their tables from ShardedTensors / local-shard tensors, everything else
+        goes through nn.Module._load_from_state_dict (reference :421-455)."""
+        from torch.nn.modules.module import _IncompatibleKeys
+        missing, unexpected = self._load_state_dict(self.module, state_dict, prefix, strict)
+        return _IncompatibleKeys(missing_keys=missing, unexpected_keys=unexpected)
+
+    def _load_state_dict(self, module: nn.Module, state_dict, prefix: str, strict: bool):
+        from torchrec.distributed.embedding_kernel import filter_state_dict
+        if isinstance(module, ShardedModule):
+            r = module.load_state_dict(state_dict, strict=strict)
+            return list(r.missing_keys), list(r.unexpected_keys)
+        missing, unexpected, errors = [], [], []
+        module._load_from_state_dict(state_dict, prefix, {}, strict, missing, unexpected, errors)
+        if errors:
+            raise RuntimeError("load_state_dict: " + "; ".join(errors))
+        for name, child in module.named_children():
+            m, u = self._load_state_dict(child, filter_state_dict(state_dict, prefix + name), "", strict)
+            missing.extend(m)
+            unexpected.extend(u)
+        return missing, unexpected
+
     def named_parameters(self, prefix: str = "", recurse: bool = True):
         yield from self.module.named_parameters(prefix, recurse)
 

@@ -11,6 +11,29 @@ from torch import optim
 OptimizerFactory = Callable[[List[torch.Tensor]], optim.Optimizer]
 
 
+def _copy_state(dst: torch.Tensor, src: torch.Tensor) -> None:
+    """In-place load of one state tensor; ShardedTensors are copied shard by shard (reference :188-205:
+    same number of local shards, same metadata)."""
+    from torch.distributed._shard.sharded_tensor import ShardedTensor
+    if isinstance(dst, ShardedTensor) or isinstance(src, ShardedTensor):
+        d = dst.local_shards() if isinstance(dst, ShardedTensor) else None
+        s = src.local_shards() if isinstance(src, ShardedTensor) else None
+        if d is not None and s is not None:
+            assert len(d) == len(s), f"{len(d)} local shards to load from {len(s)}"
+            for ds, ss in zip(d, s):
+                assert ds.metadata.shard_offsets == ss.metadata.shard_offsets and \
+                    ds.metadata.shard_sizes == ss.metadata.shard_sizes, (ds.metadata, ss.metadata)
+                ds.tensor.detach().copy_(ss.tensor)
+        elif d is not None:
+            assert len(d) == 1
+            d[0].tensor.detach().copy_(src)
+        else:
+            assert len(s) == 1
+            dst.detach().copy_(s[0].tensor)
+    else:
+        dst.detach().copy_(src)
+
+
 class KeyedOptimizer(optim.Optimizer):
     def __init__(self, params: Mapping[str, torch.Tensor], state: Mapping[Any, Any],
                  param_groups: Collection[Mapping[str, Any]]) -> None:
@@ -42,7 +65,7 @@ class KeyedOptimizer(optim.Optimizer):
             for k, v in new_state[name].items():
                 cur = self.state[p].get(k)
                 if isinstance(cur, torch.Tensor) and isinstance(v, torch.Tensor):
-                    cur.detach().copy_(v)
+                    _copy_state(cur, v)
                 else:
                     self.state[p][k] = v
         for g, ng in zip(self.param_groups, state_dict["param_groups"]):

@@ -150,6 +150,23 @@ int b200_tbe_backward(const float* grad_output, int64_t grad_stride, const void*
                       float* momentum1, const int64_t* momentum1_offsets, float learning_rate,
                       float eps, void* partial_scratch, void* stream);
 
+/* b200_tbe_backward with stochastic rounding of the updated fp16 / bf16 rows (the reference's
+ * `stochastic_rounding` optimizer argument, default true: embedding_backward_split_template.cu:367-
+ * 380, stochastic_rounding_vector in fbgemm_cuda_utils.cuh).  (sr_seed, sr_offset) is the Philox
+ * state of the step - the caller advances the offset every call, as at::PhiloxCudaState does;
+ * the random stream is keyed by the element's position in `weights`, so a run is reproducible.
+ * fp32 tables ignore it. */
+int b200_tbe_backward_sr(const float* grad_output, int64_t grad_stride, const void* sorted_keys,
+                         const int32_t* sorted_payload, const int32_t* bag_of_pos, int64_t N,
+                         int key_bits, void* weights, int weight_dtype,
+                         const int64_t* weights_offsets, const int32_t* D_offsets,
+                         const int64_t* hash_size_cumsum, int32_t T, int32_t B, int32_t max_D,
+                         int32_t all_D_mult8, const void* offsets, int index_dtype,
+                         const float* per_sample_weights, int pooling_mode, int optimizer,
+                         float* momentum1, const int64_t* momentum1_offsets, float learning_rate,
+                         float eps, void* partial_scratch, uint64_t sr_seed, uint64_t sr_offset,
+                         void* stream);
+
 /* split_embedding_codegen_grad_indice_weights_cuda
  * (fbgemm_gpu/codegen/embedding_backward_split_indice_weights_template.cu). */
 int b200_tbe_grad_indice_weights(const float* grad_output, int64_t grad_stride,

@@ -119,6 +119,35 @@ def test_tbe_sequence_mode_vs_embedding(opt, wp, shared):
         torch.testing.assert_close(w.float(), exp, rtol=tol, atol=tol)
 
 
+@pytest.mark.parametrize("wp", ["FP16", "BF16"])
+def test_tbe_module_stochastic_rounding_default(wp):
+    """16-bit tables round stochastically by default, like the reference's module (:200): many SGD steps of
+    1/8 ulp are lost entirely under round-to-nearest and accumulate to the fp32 result (in the mean) here;
+    torch.cuda.manual_seed makes the run reproducible."""
+    from fbgemm_gpu.split_embedding_configs import SparseType
+    rows, D, steps = 512, 64, 64
+    ulp = 2.0 ** -10 if wp == "FP16" else 2.0 ** -7
+    idx = torch.arange(rows, device="cuda")
+    offsets = torch.arange(rows + 1, device="cuda")
+
+    def run(sr, seed):
+        torch.cuda.manual_seed(seed)
+        m = _tbe([rows], [D], "EXACT_SGD", learning_rate=1.0, weights_precision=getattr(SparseType, wp),
+                 stochastic_rounding=sr)
+        m.split_embedding_weights()[0].fill_(1.5)
+        for _ in range(steps):
+            out = m(idx, offsets)
+            out.backward(torch.full_like(out, ulp / 8))
+        return m.split_embedding_weights()[0].float().clone()
+
+    assert bool((run(False, 1) == 1.5).all())            # round-to-nearest: every update vanishes
+    a = run(True, 1)
+    exp = 1.5 - steps * ulp / 8                           # the fp32 trajectory: 8 ulps down
+    assert abs(float(a.mean()) - exp) < 0.05 * ulp, (float(a.mean()), exp)
+    assert float((a - exp).abs().max()) < 8 * ulp
+    assert torch.equal(run(True, 1), a) and not torch.equal(run(True, 2), a)
+
+
 def test_kjt_reference_vectors():
     # torchrec/sparse/tests/test_jagged_tensor.py: test_permute :671, test_split :577, test_to_dict :549
     from torchrec.sparse.jagged_tensor import KeyedJaggedTensor

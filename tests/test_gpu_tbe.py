@@ -357,3 +357,59 @@ def test_peer_stage_reduce(ops):
     out2 = torch.full((B, pitch), 9.0, device="cuda")
     ops.peer_stage_reduce(st, W, B, Dw, out2, dev(col4), clear_stage=True)
     assert torch.equal(out2, out) and not st.any()
+
+
+# ------------------------------------------------------------------ stochastic rounding (fp16 / bf16 tables)
+@pytest.mark.parametrize("wdt,D,pattern", [
+    ("fp16", 32, "unique"),     # packed narrow-row tile (4 lanes per row)
+    ("fp16", 64, "unique"),     # packed narrow-row tile (8 lanes per row)
+    ("bf16", 128, "unique"),    # one-position-per-step ring path
+    ("fp16", 512, "unique"),    # two vectors per lane
+    ("fp16", 128, "pairs"),     # runs of two inside a warp tile
+    ("bf16", 64, "long_run"),   # one row hit by every id: partial sums cross warps / CTAs (combine kernel)
+    ("fp16", 36, "unique"),     # EPV = 4 rows
+])
+def test_backward_stochastic_rounding(ops, wdt, D, pattern):
+    """The reference's default for 16-bit tables (split_table_batched_embeddings_ops.py:200,
+    embedding_backward_split_template.cu:367-380).  Every weight starts at 1.5 and the SGD step moves it
+    down by a quarter of an ulp: round-to-nearest never changes the table, stochastic rounding moves each
+    element one ulp down with probability 1/4 (unbiased), reproducibly for a given (seed, offset)."""
+    tdt = torch.float16 if wdt == "fp16" else torch.bfloat16
+    ulp = 2.0 ** -10 if wdt == "fp16" else 2.0 ** -7
+    rows = 4096
+    if pattern == "unique":
+        ids, per_row = np.random.default_rng(1).permutation(rows).astype(np.int64), 1
+    elif pattern == "pairs":
+        ids, per_row = np.repeat(np.arange(rows // 2, dtype=np.int64), 2), 2
+    else:
+        ids, per_row = np.full(rows, 7, dtype=np.int64), rows
+    B = ids.size
+    touched = np.unique(ids)
+    offsets = np.arange(B + 1, dtype=np.int64)
+    Do = np.array([0, D], dtype=np.int32)
+    wo = np.array([0], dtype=np.int64)
+    hsc = np.array([0, rows], dtype=np.int64)
+    grad = np.full((B, D), 0.25 * ulp / per_row, dtype=np.float32)
+    srt = ops.tbe_sort_indices(dev(ids), dev(offsets), dev(hsc), 13, B, False)
+
+    def step(sr, seed=1234, offset=1):
+        w = torch.full((rows * D,), 1.5, dtype=tdt, device="cuda")
+        ops.tbe_backward(dev(grad), srt, w, dev(wo), dev(Do), dev(hsc), B, D, D % 8 == 0, dev(offsets), None,
+                         0, 0, None, None, 1.0, 0.0, sr, seed, offset)
+        return w.float().view(rows, D).cpu().numpy()
+
+    np.testing.assert_array_equal(step(False), np.full((rows, D), 1.5, dtype=np.float32))  # round to nearest
+    a = step(True)
+    untouched = np.setdiff1d(np.arange(rows), touched)
+    assert np.all(a[untouched] == 1.5)
+    moved = (1.5 - a[touched]) / ulp
+    assert np.all((moved == 0) | (moved == 1)), np.unique(moved)
+    n = moved.size
+    p = moved.mean()
+    sigma = (0.25 * 0.75 / n) ** 0.5
+    assert abs(p - 0.25) < 6 * sigma + 1e-9, (p, n)
+    if pattern == "unique":  # no structure along rows or columns
+        assert abs(moved.mean(axis=0) - 0.25).max() < 0.06 and abs(moved.mean(axis=1) - 0.25).max() < 0.5
+    np.testing.assert_array_equal(step(True), a)                 # same Philox state: same bits
+    assert not np.array_equal(step(True, offset=2), a)           # next step: a different draw
+    assert not np.array_equal(step(True, seed=99), a)

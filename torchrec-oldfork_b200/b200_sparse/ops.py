@@ -345,7 +345,10 @@ def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.T
                  B: int, max_D: int, all_D_mult8: bool, offsets: torch.Tensor,
                  per_sample_weights: Optional[torch.Tensor], pooling_mode: int, optimizer: int,
                  momentum1: Optional[torch.Tensor], momentum1_offsets: Optional[torch.Tensor],
-                 learning_rate: float, eps: float) -> None:
+                 learning_rate: float, eps: float, stochastic_rounding: bool = False, sr_seed: int = 0,
+                 sr_offset: int = 0) -> None:
+    """stochastic_rounding: fp16 / bf16 rows are rounded stochastically with the Philox stream
+    (sr_seed, sr_offset); the caller moves sr_offset every call.  fp32 tables ignore it."""
     dev = _need_cuda(grad_output, weights, weights_offsets, D_offsets, hash_size_cumsum, offsets)
     if grad_output.dtype != torch.float32:
         grad_output = grad_output.float()
@@ -358,6 +361,18 @@ def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.T
     scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
+    if stochastic_rounding and weights.dtype != torch.float32:
+        with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):
+            check(lib.b200_tbe_backward_sr(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
+                                           _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),
+                                           _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
+                                           _p(hash_size_cumsum), T, B, max_D, int(all_D_mult8), _p(offsets),
+                                           _idx_dt(offsets, "offsets"), _p(per_sample_weights),
+                                           int(pooling_mode), int(optimizer), _p(momentum1),
+                                           _p(momentum1_offsets), float(learning_rate), float(eps),
+                                           _p(scratch), int(sr_seed) & (2 ** 64 - 1),
+                                           int(sr_offset) & (2 ** 64 - 1), _stream(dev)), "b200_tbe_backward_sr")
+        return
     with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):  # tile kernel + cross-CTA combine
         check(lib.b200_tbe_backward(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
                                     _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),

@@ -1,5 +1,6 @@
 // Shared device helpers for the B200 sparse-path kernels (sm_100a only).
 #pragma once
+#include <type_traits>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -138,6 +139,69 @@ __device__ __forceinline__ void store_vec(O* p, const float (&f)[EPV]) {
       st_stream_8(p, v);
     else
       *reinterpret_cast<uint2*>(p) = v;
+  }
+}
+
+// ---- stochastic rounding of fp32 -> fp16 / bf16 (reference: stochastic_rounding_vector,
+// fbgemm_gpu/include/fbgemm_gpu/fbgemm_cuda_utils.cuh, Philox4x32-10 seeded from the CUDA generator).
+// Random bits are added below the last mantissa bit the 16-bit type keeps (13 for fp16, 16 for bf16)
+// and the remainder is cleared, so the value handed to the round-to-nearest pack is already
+// representable: P(round up) = discarded fraction / ulp.  Exact for normal fp16 values (like the
+// reference, fp16 subnormals fall back to round-to-nearest).
+struct SrArgs {
+  uint64_t seed;
+  uint64_t offset;
+  const void* base;  // first element of the weight buffer: vector index = (p - base) / EPV
+  int32_t on;
+};
+
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t h0 = __umulhi(0xD2511F53u, c.x), l0 = 0xD2511F53u * c.x;
+    const uint32_t h1 = __umulhi(0xCD9E8D57u, c.z), l1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(h1 ^ c.y ^ k.x, l1, h0 ^ c.w ^ k.y, l0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+template <typename W>
+__device__ __forceinline__ float sr_bits(float x, uint32_t r16) {
+  if constexpr (sizeof(W) == 2) {
+    constexpr bool kBf16 = std::is_same<W, __nv_bfloat16>::value;
+    constexpr uint32_t kMask = kBf16 ? 0xffffu : 0x1fffu;
+    const uint32_t u = __float_as_uint(x);
+    if ((u & 0x7f800000u) == 0x7f800000u) return x;  // inf / nan pass through
+    return __uint_as_float((u + (r16 & kMask)) & ~kMask);
+  } else {
+    return x;
+  }
+}
+
+// Perturbs the EPV fp32 values that are about to be stored at p (type W) so that the
+// round-to-nearest store rounds them stochastically.  One Philox call per vector.
+template <typename W, int EPV>
+__device__ __forceinline__ void sr_prepare(const SrArgs& sr, const W* p, float (&w)[EPV]) {
+  if constexpr (sizeof(W) == 2) {
+    if (sr.on) {
+      const uint64_t vec = (uint64_t)(p - reinterpret_cast<const W*>(sr.base)) / EPV;
+      const uint4 r = philox4x32_10(make_uint4((uint32_t)vec, (uint32_t)(vec >> 32), (uint32_t)sr.offset,
+                                               (uint32_t)(sr.offset >> 32)),
+                                    make_uint2((uint32_t)sr.seed, (uint32_t)(sr.seed >> 32)));
+      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+      if constexpr (EPV == 8) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          w[2 * i] = sr_bits<W>(w[2 * i], rr[i] & 0xffffu);
+          w[2 * i + 1] = sr_bits<W>(w[2 * i + 1], rr[i] >> 16);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = sr_bits<W>(w[i], rr[i] >> 16);
+      }
+    }
   }
 }
 

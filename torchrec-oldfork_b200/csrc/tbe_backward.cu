@@ -159,7 +159,7 @@ template <typename W, int EPV, int NV, int OPT, bool PREFETCHED>
 __device__ __forceinline__ void apply_update(float (&acc)[NV][EPV], float (&wv)[NV][EPV],
                                              float m_prefetched, W* __restrict__ wrow,
                                              float* __restrict__ mom, int D, int lane, float lr,
-                                             float eps) {
+                                             float eps, const SrArgs& sr) {
   float mult = lr;
   if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) {
     float ss = 0.f;
@@ -186,6 +186,7 @@ __device__ __forceinline__ void apply_update(float (&acc)[NV][EPV], float (&wv)[
       }
 #pragma unroll
       for (int e = 0; e < EPV; ++e) w[e] = fmaf(acc[v][e], -mult, w[e]);
+      sr_prepare<W, EPV>(sr, wrow + d, w);
       store_vec<W, EPV, false>(wrow + d, w);
     }
   }
@@ -316,7 +317,8 @@ __device__ __forceinline__ void bwd_packed_tile(const int lane, const unsigned H
                                                 const unsigned Cm, const float* gptr, W* wptr,
                                                 float* mptr, const float scale, const bool scaled,
                                                 const int D0, const float lr, const float eps,
-                                                float* sH_warp, float (&acc)[1][EPV]) {
+                                                const SrArgs& sr, float* sH_warp,
+                                                float (&acc)[1][EPV]) {
   constexpr int R = 32 / LPR;
   constexpr unsigned kRMask = (1u << R) - 1u;
   const int gl = lane & (LPR - 1);
@@ -405,6 +407,7 @@ __device__ __forceinline__ void bwd_packed_tile(const int lane, const unsigned H
           wr[buf].unpack(w);
 #pragma unroll
           for (int e = 0; e < EPV; ++e) w[e] = fmaf(x[e], -mult, w[e]);
+          sr_prepare<W, EPV>(sr, wpb[buf] + EPV * gl, w);
           store_vec<W, EPV, false>(wpb[buf] + EPV * gl, w);
         }
       }
@@ -459,6 +462,7 @@ struct BwdArgs {
   int32_t B_src;
   float grad_scale;  // 1/W of the sharded path (GRADIENT_DIVISION), 1 otherwise
   int32_t pack_rows;  // narrow rows: several positions per warp step (bwd_packed_tile)
+  SrArgs sr;          // stochastic rounding of 16-bit weight rows (off for fp32 tables)
   float* part_rows;  // [numCTAs][2][ROW]  (0 = leading partial H, 1 = trailing partial T)
   BwdMeta* meta;     // [numCTAs]
   int32_t num_ctas;
@@ -572,10 +576,10 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
       float* const mp = (OPT == B200_OPT_ROWWISE_ADAGRAD) ? a.momentum1 + moff : nullptr;
       if (D0 <= EPV * 4)
         bwd_packed_tile<W, EPV, OPT, 4>(lane, Hm, Em, Cm, gptr, wp, mp, scale, scaled, D0, a.lr, a.eps,
-                                        sH + warp * ROW, acc);
+                                        a.sr, sH + warp * ROW, acc);
       else
         bwd_packed_tile<W, EPV, OPT, 8>(lane, Hm, Em, Cm, gptr, wp, mp, scale, scaled, D0, a.lr, a.eps,
-                                        sH + warp * ROW, acc);
+                                        a.sr, sH + warp * ROW, acc);
       open_head = Hm ? 31 - __clz(Hm) : -1;
     }
   }
@@ -673,6 +677,7 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
               load_wslot<W, EPV>(st + kGradBytes + v * 512, w);
 #pragma unroll
               for (int e = 0; e < EPV; ++e) w[e] = fmaf(acc[v][e], -mult, w[e]);
+              sr_prepare<W, EPV>(a.sr, wrow + EPV * 32 * v, w);
               store_vec<W, EPV, false>(wrow + EPV * 32 * v, w);
             }
         } else {
@@ -779,7 +784,7 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
           }
         }
         apply_update<W, EPV, NV, OPT, true>(acc, wv, m_old, weights + wo, a.momentum1 + mo, Dp, lane,
-                                            a.lr, a.eps);
+                                            a.lr, a.eps, a.sr);
       } else {
         row_store<EPV, NV>(sH + warp * ROW, acc, lane);  // tail of a run from an earlier tile
       }
@@ -820,7 +825,7 @@ __global__ void __launch_bounds__(kBwdThreads) tbe_backward_tile_kernel(const Bw
     }
     if (finished) {
       apply_update<W, EPV, NV, OPT, false>(acc, dummy_w, 0.f, weights + rwo, a.momentum1 + rmo, rD,
-                                           lane, a.lr, a.eps);
+                                           lane, a.lr, a.eps, a.sr);
     } else {
       row_store<EPV, NV>(my_part + ROW, acc, lane);
       if (lane == 0) {
@@ -896,7 +901,7 @@ __global__ void __launch_bounds__(128) tbe_backward_combine_kernel(const BwdArgs
   float* mom = a.momentum1;
   if constexpr (OPT == B200_OPT_ROWWISE_ADAGRAD) mom += a.momentum1_offsets[t] + row;
   apply_update<W, EPV, NV, OPT, false>(acc, dummy_w, 0.f, weights + a.weights_offsets[t] + row * D,
-                                       mom, D, lane, a.lr, a.eps);
+                                       mom, D, lane, a.lr, a.eps, a.sr);
 }
 
 template <typename W, typename K, int EPV, int NV, int OPT>
@@ -1033,7 +1038,8 @@ static int tbe_backward_impl(const float* grad_output, int64_t grad_stride,
                                  float* momentum1, const int64_t* momentum1_offsets,
                                  float learning_rate, float eps, void* partial_scratch,
                                  const float* const* grad_bases, int32_t B_src,
-                                 const int32_t* src_col, float grad_scale, void* stream) {
+                                 const int32_t* src_col, float grad_scale, int32_t stochastic_rounding,
+                                 uint64_t sr_seed, uint64_t sr_offset, void* stream) {
   using namespace b200;
   if (N == 0 || T == 0 || B == 0) return B200_OK;
   if ((grad_stride & 3) != 0) return B200_EINVAL;
@@ -1070,6 +1076,10 @@ static int tbe_backward_impl(const float* grad_output, int64_t grad_stride,
   ARGS.B_src = B_src;                                      \
   ARGS.grad_scale = grad_scale;                            \
   ARGS.pack_rows = bwd_pack_rows();                        \
+  ARGS.sr.seed = sr_seed;                                  \
+  ARGS.sr.offset = sr_offset;                              \
+  ARGS.sr.base = weights;                                  \
+  ARGS.sr.on = (stochastic_rounding && weight_dtype != B200_F32) ? 1 : 0; \
   ARGS.part_rows = part_rows;                              \
   ARGS.meta = meta;                                        \
   ARGS.num_ctas = (int32_t)ctas;
@@ -1103,7 +1113,27 @@ extern "C" int b200_tbe_backward(const float* grad_output, int64_t grad_stride,
                            hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
                            per_sample_weights, pooling_mode, optimizer, momentum1,
                            momentum1_offsets, learning_rate, eps, partial_scratch, nullptr, 0,
-                           nullptr, 1.0f, stream);
+                           nullptr, 1.0f, 0, 0, 0, stream);
+}
+
+extern "C" int b200_tbe_backward_sr(const float* grad_output, int64_t grad_stride,
+                                    const void* sorted_keys, const int32_t* sorted_payload,
+                                    const int32_t* bag_of_pos, int64_t N, int key_bits, void* weights,
+                                    int weight_dtype, const int64_t* weights_offsets,
+                                    const int32_t* D_offsets, const int64_t* hash_size_cumsum,
+                                    int32_t T, int32_t B, int32_t max_D, int32_t all_D_mult8,
+                                    const void* offsets, int index_dtype,
+                                    const float* per_sample_weights, int pooling_mode, int optimizer,
+                                    float* momentum1, const int64_t* momentum1_offsets,
+                                    float learning_rate, float eps, void* partial_scratch,
+                                    uint64_t sr_seed, uint64_t sr_offset, void* stream) {
+  if (!grad_output) return B200_EINVAL;
+  return tbe_backward_impl(grad_output, grad_stride, sorted_keys, sorted_payload, bag_of_pos, N,
+                           key_bits, weights, weight_dtype, weights_offsets, D_offsets,
+                           hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
+                           per_sample_weights, pooling_mode, optimizer, momentum1,
+                           momentum1_offsets, learning_rate, eps, partial_scratch, nullptr, 0,
+                           nullptr, 1.0f, 1, sr_seed, sr_offset, stream);
 }
 
 extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_src, int32_t B_src,
@@ -1125,5 +1155,5 @@ extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_
                            hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
                            per_sample_weights, pooling_mode, optimizer, momentum1,
                            momentum1_offsets, learning_rate, eps, partial_scratch, grad_bases,
-                           B_src, src_col, grad_scale, stream);
+                           B_src, src_col, grad_scale, 0, 0, 0, stream);
 }

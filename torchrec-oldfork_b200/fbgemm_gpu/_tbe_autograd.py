@@ -35,7 +35,7 @@ _lib.define(
     "int total_hash_size_bits, Tensor(a!) dev_weights, Tensor weights_offsets, Tensor D_offsets, "
     "Tensor hash_size_cumsum, int B, int max_D, bool all_D_mult8, Tensor offsets, Tensor? indice_weights, "
     "int pooling_mode, int optimizer, Tensor(b!) momentum1, Tensor momentum1_offsets, float learning_rate, "
-    "float eps) -> ()")
+    "float eps, bool stochastic_rounding=False, int sr_seed=0, int sr_offset=0) -> ()")
 _lib.define(
     "b200_tbe_grad_indice_weights(Tensor grad_output, Tensor dev_weights, Tensor weights_offsets, "
     "Tensor D_offsets, Tensor indices, Tensor offsets) -> Tensor")
@@ -59,12 +59,14 @@ def _sort_cuda(indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weig
 
 def _bwd_cuda(grad_output, sorted_keys, sorted_payload, bag_of_pos, total_hash_size_bits, dev_weights,
               weights_offsets, D_offsets, hash_size_cumsum, B, max_D, all_D_mult8, offsets, indice_weights,
-              pooling_mode, optimizer, momentum1, momentum1_offsets, learning_rate, eps):
+              pooling_mode, optimizer, momentum1, momentum1_offsets, learning_rate, eps,
+              stochastic_rounding=False, sr_seed=0, sr_offset=0):
     srt = ops.SortedIndices(sorted_keys, sorted_payload, bag_of_pos if bag_of_pos.numel() else None,
                             sorted_keys.numel(), max(1, total_hash_size_bits), None)
     ops.tbe_backward(grad_output, srt, dev_weights, weights_offsets, D_offsets, hash_size_cumsum, B, max_D,
                      all_D_mult8, offsets, indice_weights, pooling_mode, optimizer,
-                     momentum1 if momentum1.numel() else None, momentum1_offsets, learning_rate, eps)
+                     momentum1 if momentum1.numel() else None, momentum1_offsets, learning_rate, eps,
+                     stochastic_rounding, sr_seed, sr_offset)
 
 
 def _giw_cuda(grad_output, dev_weights, weights_offsets, D_offsets, indices, offsets):
@@ -154,7 +156,7 @@ class _Lookup(torch.autograd.Function):
                 grad_output, keys, payload, bag, m.total_hash_size_bits, m.weights_dev, m.weights_offsets,
                 m.D_offsets, m.hash_size_cumsum, ctx.B, m.max_D, m._all_D_mult8, offsets, indice_weights,
                 int(m.pooling_mode), _OPT_CODE[m.optimizer], m.momentum1_dev, m.momentum1_offsets,
-                a.learning_rate, a.eps)
+                a.learning_rate, a.eps, *m._next_sr_state())
             ctx.sort_out = None
         return None, None, None, None, grad_iw, None
 

@@ -148,9 +148,9 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
         else:
             self.current_device = torch.device("cuda", torch.cuda.current_device())
         dev = self.current_device
-        if weights_precision != SparseType.FP32 and stochastic_rounding:
-            logging.warning("stochastic_rounding is not implemented; %s weights are written back with "
-                            "round-to-nearest-even", weights_precision)
+        # fp16 / bf16 rows are written back with stochastic rounding when asked (the reference's default,
+        # :200); the Philox state of a step is drawn from the device's CUDA generator, as the reference does
+        self._sr_on = bool(stochastic_rounding) and weights_precision != SparseType.FP32
         self.optimizer = optimizer
         self.optimizer_args = _OptimizerArgs(stochastic_rounding, gradient_clipping, max_gradient,
                                              learning_rate, eps)
@@ -266,6 +266,18 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
     def init_embedding_weights_uniform(self, min_val: float, max_val: float) -> None:
         for w in self.split_embedding_weights():
             w.uniform_(min_val, max_val)
+
+    def _next_sr_state(self):
+        """(stochastic_rounding, seed, offset) of this backward: the CUDA generator's Philox seed and a
+        fresh offset (the generator is advanced like at::PhiloxCudaState does, so runs are reproducible
+        under torch.cuda.manual_seed and independent between modules and steps)."""
+        if not self._sr_on:
+            return False, 0, 0
+        dev = self.current_device
+        gen = torch.cuda.default_generators[dev.index if dev.index is not None else torch.cuda.current_device()]
+        offset = gen.get_offset()
+        gen.set_offset(offset + 4)
+        return True, gen.initial_seed() & (2 ** 63 - 1), offset // 4 + 1
 
     def set_learning_rate(self, lr: float) -> None:
         self.optimizer_args.learning_rate = float(lr)

@@ -132,6 +132,8 @@ class PeerLookupDist:
             mods = list(lookup._emb_modules)
             if len(lookup._score_emb_modules):
                 raise NotImplementedError("weighted features take the NCCL path")
+            if any(getattr(m.emb_module, "_sr_on", False) for m in mods):
+                raise NotImplementedError("stochastic rounding of fp16/bf16 tables takes the NCCL path")
             parts: List[_Part] = []
             if isinstance(sharding, BaseTwEmbeddingSharding):
                 for m in mods:

@@ -64,7 +64,11 @@ def main() -> None:
     # checkpoint format: every sharded table is a ShardedTensor of the GLOBAL shape whose
     # metadata lists one shard per owning rank and whose local shard views the live table
     for i, (r, s) in enumerate(zip(rows, sharding)):
-        st = lsd[f"sparse_arch.embedding_bag_collection.embedding_bags.t{i}.weight"]
+        key = f"sparse_arch.embedding_bag_collection.embedding_bags.t{i}.weight"
+        if s == "table_wise" and ebc_plan[f"t{i}"].ranks[0] != rank:
+            assert key not in lsd  # a table-wise table is listed by its owner only
+            continue
+        st = lsd[key]
         assert isinstance(st, ShardedTensor) and tuple(st.size()) == (r, D), (type(st), st.size())
         metas = st.metadata().shards_metadata
         assert len(metas) == (1 if s == "table_wise" else world), (s, len(metas))

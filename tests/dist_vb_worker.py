@@ -77,23 +77,26 @@ def main() -> None:
     for step in range(2):
         kjt = batch(step, rank)
         torch.manual_seed(50 + step)
-        coef = torch.randn(sum(dims), device=dev)
+        coef = {k: torch.randn(d, device=dev) for k, d in zip(keys, dims)}
         out_l = dmp(kjt)
         out_l = out_l.wait() if hasattr(out_l, "wait") else out_l
         out_g = glob(kjt)
-        assert out_l.keys() == out_g.keys(), (out_l.keys(), out_g.keys())
-        assert out_l.values().shape == out_g.values().shape == (kjt.stride(), sum(dims))
-        torch.testing.assert_close(out_l.values(), out_g.values(), rtol=1e-5, atol=1e-6)
+        # the sharded module lists its keys in sharding order (owner rank by owner rank): compare per key
+        dl, dg = out_l.to_dict(), out_g.to_dict()
+        assert sorted(dl) == sorted(dg) == sorted(keys), (out_l.keys(), out_g.keys())
+        for k, d in zip(keys, dims):
+            assert dl[k].shape == dg[k].shape == (kjt.stride(), d), (k, dl[k].shape, dg[k].shape)
+            torch.testing.assert_close(dl[k], dg[k], rtol=1e-5, atol=1e-6)
         # one step; the sharded backward divides by W, so the global model averages over ranks
         opt_g.zero_grad()
-        (out_g.values() * coef).sum().backward()
+        sum((dg[k] * coef[k]).sum() for k in keys).backward()
         for p in glob.parameters():
             if p.grad is None:
                 p.grad = torch.zeros_like(p)
             dist.all_reduce(p.grad)
             p.grad.div_(world)
         opt_g.step()
-        (out_l.values() * coef).sum().backward()
+        sum((dl[k] * coef[k]).sum() for k in keys).backward()
         gsd = glob.state_dict()
         bad = []
         for k, v in dmp.state_dict().items():

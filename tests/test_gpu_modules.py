@@ -144,7 +144,7 @@ def test_tbe_module_stochastic_rounding_default(wp):
     a = run(True, 1)
     exp = 1.5 - steps * ulp / 8                           # the fp32 trajectory: 8 ulps down
     assert abs(float(a.mean()) - exp) < 0.05 * ulp, (float(a.mean()), exp)
-    assert float((a - exp).abs().max()) < 8 * ulp
+    assert float((a - exp).abs().max()) < 20 * ulp           # Binomial(64, 1/8): sigma = 2.6 ulps
     assert torch.equal(run(True, 1), a) and not torch.equal(run(True, 2), a)
 
 

@@ -211,6 +211,16 @@ int b200_interaction_backward(const float* dense, const float* sparse, const flo
                               int64_t grad_stride, int32_t B, int32_t F, int32_t D,
                               float* grad_dense, float* grad_sparse, void* stream);
 
+/* b200_interaction_backward whose sparse gradient leaves feature by feature: the row of feature f
+ * and sample s is stored at (float*)feat_base[f] + s * feat_pitch[f] (device arrays [F]; addresses
+ * 16-byte aligned, pitches in elements).  With peer-mapped addresses this is the backward
+ * all-to-all of table-wise sharded embeddings (comm_ops.py:585-640: recat copy + all_to_all_single)
+ * fused into the kernel that produces the gradient.  B200_EUNSUPPORTED when F + 1 > 32 or D % 32. */
+int b200_interaction_backward_scatter(const float* dense, const float* sparse, const float* grad_out,
+                                      int64_t grad_stride, int32_t B, int32_t F, int32_t D,
+                                      float* grad_dense, const int64_t* feat_base,
+                                      const int64_t* feat_pitch, void* stream);
+
 /* ---------------------------------------------------------------- sharded data movement */
 
 /* Receive-side layout change of PooledEmbeddingsAllToAll

@@ -30,7 +30,7 @@ def main() -> None:
     torch.backends.cuda.matmul.allow_tf32 = False
     rows = [50, 7, 1001, 3, 5, 300]          # 5 rows over W ranks exercises short / empty row shards
     sharding = ["table_wise", "row_wise", "row_wise", "table_wise", "row_wise", "table_wise"]
-    D, B, lr = 16, 32, 0.1
+    D, B, lr = 32, 32, 0.1  # D % 32 == 0: the tensor-core interaction kernels (and their gradient scatter) run
     keys = [f"f{i}" for i in range(len(rows))]
 
     def tables():
@@ -128,6 +128,11 @@ def main() -> None:
     mode = "peer" if sebc._peer is not None else "nccl"
     want = "nccl" if os.environ.get("B200_PEER_DIST", "1") == "0" else "peer"
     assert mode == want, f"exchange ran through {mode}, expected {want}"
+    if mode == "peer":  # table-wise gradients: pushed by the interaction backward, or pulled by the owners
+        pushed = sum(px.pushed_steps for px in sebc._peer._exchanges.values())
+        want_push = os.environ.get("B200_PEER_PUSH", "1") != "0"
+        assert (pushed > 0) == want_push, f"gradient push ran {pushed} times, expected push={want_push}"
+        mode = "peer" if want_push else "peer_pull"
     dist.barrier()
     if rank == 0:
         print(f"DIST PARITY OK world={world} exchange={mode}")

@@ -246,7 +246,7 @@ def test_quantized_ebc():
 
 
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("exchange", ["peer", "nccl"])
+@pytest.mark.parametrize("exchange", ["peer", "peer_pull", "nccl"])
 def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     """TW + RW over `world` GPUs (torchrun): the fused peer-memory exchange and the NCCL collectives both
     reproduce the unsharded model; skipped on a single-GPU box."""
@@ -255,9 +255,11 @@ def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     here = os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, B200_PEER_DIST="1" if exchange == "peer" else "0")
+    env = dict(os.environ, B200_PEER_DIST="0" if exchange == "nccl" else "1",
+               B200_PEER_PUSH="0" if exchange == "peer_pull" else "1")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-                        "--master-addr", "127.0.0.1", "--master-port", "29611" if exchange == "peer" else "29621",
+                        "--master-addr", "127.0.0.1", "--master-port",
+                        {"peer": "29611", "peer_pull": "29616", "nccl": "29621"}[exchange],
                         os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600,
                        env=env)
     assert r.returncode == 0 and f"exchange={exchange}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

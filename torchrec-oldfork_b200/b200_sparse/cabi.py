@@ -58,6 +58,7 @@ SIGNATURES = {
                                      _int, _p, _int, _p]),
     "b200_interaction_forward": (_int, [_p, _p, _i32, _i32, _i32, _p, _i64, _p]),
     "b200_interaction_backward": (_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p]),
+    "b200_interaction_backward_scatter": (_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p]),
     "b200_linearize_seq_indices": (_int, [_p, _p, _int, _p, _i32, _i32, _i64, _p, _p]),
     "b200_relu_bias_grad_scratch_bytes": (_sz, [_i32]),
     "b200_relu_bias_grad": (_int, [_p, _i64, _p, _i64, _i64, _i32, _p, _p, _p, _p]),

@@ -527,11 +527,29 @@ def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: boo
 # keeps the pooled-embedding gradient in symmetric memory so that other ranks can read it) registers
 # that buffer here; interaction_backward then writes grad_sparse straight into it instead of a fresh
 # tensor, which saves the consumer a [B, F*D] copy per step.
-_GRAD_SINKS: Dict[Tuple[int, int], torch.Tensor] = {}
+_GRAD_SINKS: Dict[Tuple[int, int], "GradSink"] = {}
 
 
-def register_grad_sink(buf: torch.Tensor) -> None:
-    _GRAD_SINKS[(buf.device.index, buf.numel())] = buf
+class GradSink:
+    """buf: the consumer's [B, F*D] gradient buffer.  feat_base / feat_pitch (int64 device tensors [F],
+    optional): per-feature destinations for b200_interaction_backward_scatter - the consumer may point
+    a feature at another GPU's buffer.  `scattered` tells the consumer which layout the last backward
+    used (True: per-feature destinations; False: everything in buf)."""
+
+    def __init__(self, buf: torch.Tensor, feat_base: Optional[torch.Tensor] = None,
+                 feat_pitch: Optional[torch.Tensor] = None, src: Optional[torch.Tensor] = None) -> None:
+        self.buf, self.feat_base, self.feat_pitch = buf, feat_base, feat_pitch
+        # scatter only the gradient of THIS tensor (the consumer's forward output, features in the
+        # order of feat_base): any other [B, F*D] input of the same size keeps the dense layout
+        self.src_ptr = src.data_ptr() if src is not None else None
+        self.scattered = False
+
+
+def register_grad_sink(buf: torch.Tensor, feat_base: Optional[torch.Tensor] = None,
+                       feat_pitch: Optional[torch.Tensor] = None, src: Optional[torch.Tensor] = None) -> GradSink:
+    sink = GradSink(buf, feat_base, feat_pitch, src)
+    _GRAD_SINKS[(buf.device.index, buf.numel())] = sink
+    return sink
 
 
 def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
@@ -544,8 +562,19 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
         grad_out = grad_out.contiguous()  # a row-pitched view is consumed in place
     gd = torch.empty_like(dense)
     sink = _GRAD_SINKS.get((dev.index, sparse.numel()))
-    gs = sink.view(sparse.shape) if sink is not None and sink.dtype == sparse.dtype else torch.empty_like(sparse)
+    if sink is not None and sink.buf.dtype != sparse.dtype:
+        sink = None
+    gs = sink.buf.view(sparse.shape) if sink is not None else torch.empty_like(sparse)
     with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
+        if sink is not None:
+            sink.scattered = False
+            if (sink.feat_base is not None and sink.feat_base.numel() == F and F + 1 <= 32 and D % 32 == 0
+                    and sparse.data_ptr() == sink.src_ptr):
+                check(lib.b200_interaction_backward_scatter(
+                    _p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D, _p(gd),
+                    _p(sink.feat_base), _p(sink.feat_pitch), _stream(dev)), "b200_interaction_backward_scatter")
+                sink.scattered = True
+                return gd, gs
         check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D,
                                             _p(gd), _p(gs), _stream(dev)), "b200_interaction_backward")
     return gd, gs

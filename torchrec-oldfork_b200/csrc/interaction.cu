@@ -369,12 +369,27 @@ interaction_forward_mma_kernel(const float* __restrict__ dense, const float* __r
 // kept in registers), X streamed in 64-column stages with row stride 72 (B-fragment loads are
 // conflict free).  grad_out rows ride in the same cp.async groups (4-byte copies: rows are only
 // 4-byte aligned).  Results leave as 8-byte stores that fill whole 32-byte sectors.
-template <bool FULL>  // FULL: 25 <= n <= 32 (four k-steps, both row tiles live)
+// SCATTER: the gradient row of feature f and sample s goes to (float*)feat_base[f] + s * feat_pitch[f]
+// instead of grad_sparse[s][f][:] - with NVLink peer mappings in feat_base this kernel IS the
+// backward all-to-all of table-wise sharded embeddings (every feature's gradient lands in its
+// owner's buffer while the tile is being computed; torchrec comm_ops.py:585-640 runs that as a
+// re-layout copy + NCCL all_to_all_single after the kernel).
+template <bool FULL, bool SCATTER>  // FULL: 25 <= n <= 32 (four k-steps, both row tiles live)
 __global__ void __launch_bounds__(kBwdMmaWarps * 32, 1)
 interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __restrict__ sparse,
                                 const float* __restrict__ grad_out, int64_t grad_stride, int32_t B,
                                 int32_t F, int32_t D, float* __restrict__ grad_dense,
-                                float* __restrict__ grad_sparse) {
+                                float* __restrict__ grad_sparse,
+                                const int64_t* __restrict__ feat_base,
+                                const int64_t* __restrict__ feat_pitch) {
+  __shared__ long long s_fbase[32];
+  __shared__ long long s_fpitch[32];
+  if constexpr (SCATTER) {
+    if (threadIdx.x < F) {
+      s_fbase[threadIdx.x] = feat_base[threadIdx.x];
+      s_fpitch[threadIdx.x] = feat_pitch[threadIdx.x];
+    }
+  }
   extern __shared__ __align__(16) float smem[];
   const int n = F + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -516,6 +531,9 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
               v.x += gcur[d];
               v.y += gcur[d + 1];
               *reinterpret_cast<float2*>(grad_dense + s * D + d) = v;
+            } else if constexpr (SCATTER) {
+              float* row = reinterpret_cast<float*>(s_fbase[i - 1]) + s * s_fpitch[i - 1];
+              *reinterpret_cast<float2*>(row + d) = v;
             } else {
               *reinterpret_cast<float2*>(grad_sparse + (s * F + (i - 1)) * (int64_t)D + d) = v;
             }
@@ -566,11 +584,12 @@ extern "C" int b200_interaction_forward(const float* dense, const float* sparse,
   return B200_OK;
 }
 
-extern "C" int b200_interaction_backward(const float* dense, const float* sparse,
-                                         const float* grad_out, int64_t grad_stride, int32_t B,
-                                         int32_t F, int32_t D, float* grad_dense,
-                                         float* grad_sparse, void* stream) {
+static int interaction_backward_impl(const float* dense, const float* sparse, const float* grad_out,
+                                     int64_t grad_stride, int32_t B, int32_t F, int32_t D,
+                                     float* grad_dense, float* grad_sparse, const int64_t* feat_base,
+                                     const int64_t* feat_pitch, void* stream) {
   using namespace b200;
+  const bool scatter = feat_base != nullptr;
   if (B == 0) return B200_OK;
   if (D <= 0 || (D & 3) || F < 0) return B200_EINVAL;
   if (grad_stride < D + (int64_t)(F + 1) * F / 2) return B200_EINVAL;
@@ -579,17 +598,21 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
     const int n_tri = n * (n - 1) / 2;
     const size_t per_warp = 2 * (size_t)n * (kBwdKC + 8) + 32 * 36 + 2 * (size_t)((D + n_tri + 3) & ~3);
     const size_t msmem = sizeof(float) * kBwdMmaWarps * per_warp + ((sizeof(uint16_t) * n_tri + 15) & ~(size_t)15);
-    if (msmem <= 227 * 1024) {
-      auto kern = n > 24 ? interaction_backward_mma_kernel<true> : interaction_backward_mma_kernel<false>;
+    if (msmem <= 226 * 1024) {
+      auto kern = scatter ? (n > 24 ? interaction_backward_mma_kernel<true, true>
+                                    : interaction_backward_mma_kernel<false, true>)
+                          : (n > 24 ? interaction_backward_mma_kernel<true, false>
+                                    : interaction_backward_mma_kernel<false, false>);
       B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
       int64_t mgrid = ceil_div(B, kBwdMmaWarps);
       if (mgrid > kNumSMs) mgrid = kNumSMs;
       kern<<<(unsigned)mgrid, kBwdMmaWarps * 32, msmem, (cudaStream_t)stream>>>(
-          dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
+          dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse, feat_base, feat_pitch);
       B200_LAUNCH_CHECK();
       return B200_OK;
     }
   }
+  if (scatter) return B200_EUNSUPPORTED;  // the caller falls back to the dense layout
   const size_t smem = sizeof(float) * kIxSamplesPerCta * (((size_t)n * (D + 4) + (size_t)n * (n + 1) + 3) & ~(size_t)3);
   if (smem > 200 * 1024) return B200_EUNSUPPORTED;
   B200_CUDA_TRY(cudaFuncSetAttribute(interaction_backward_kernel,
@@ -600,4 +623,22 @@ extern "C" int b200_interaction_backward(const float* dense, const float* sparse
       dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse);
   B200_LAUNCH_CHECK();
   return B200_OK;
+}
+
+extern "C" int b200_interaction_backward(const float* dense, const float* sparse,
+                                         const float* grad_out, int64_t grad_stride, int32_t B,
+                                         int32_t F, int32_t D, float* grad_dense,
+                                         float* grad_sparse, void* stream) {
+  return interaction_backward_impl(dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, grad_sparse,
+                                   nullptr, nullptr, stream);
+}
+
+extern "C" int b200_interaction_backward_scatter(const float* dense, const float* sparse,
+                                                 const float* grad_out, int64_t grad_stride, int32_t B,
+                                                 int32_t F, int32_t D, float* grad_dense,
+                                                 const int64_t* feat_base, const int64_t* feat_pitch,
+                                                 void* stream) {
+  if (!feat_base || !feat_pitch) return B200_EINVAL;
+  return interaction_backward_impl(dense, sparse, grad_out, grad_stride, B, F, D, grad_dense, nullptr,
+                                   feat_base, feat_pitch, stream);
 }

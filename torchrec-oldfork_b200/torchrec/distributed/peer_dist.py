@@ -12,9 +12,15 @@ forward   table-wise : b200_tbe_forward_peer stores the pooled row of global sam
                        b200_peer_stage_reduce sums the W slots in rank order (deterministic) into the
                        final buffer and zeroes what it read.  With one id per bag this moves 1/W of
                        what a reduce-scatter of dense partial sums moves.
-backward  both       : b200_tbe_backward_peer loads the gradient row of sample b from rank
-                       (b // B_local)'s gradient buffer while it streams the sorted ids, applies 1/W and
-                       the fused optimizer.  This is the reverse all-to-all and the all-gather at once.
+backward  table-wise : the kernel that PRODUCES the gradient of the pooled rows (the dot interaction's
+                       backward, b200_interaction_backward_scatter) stores every table-wise feature's rows
+                       straight into the owning rank's [B_global, D_owned] buffer: the reverse all-to-all
+                       happens inside the producer, and the fused optimizer kernel then reads local HBM.
+                       A model whose gradient arrives some other way takes the pull path below.
+          row-wise   : b200_tbe_backward_peer loads the gradient row of sample b from rank
+          (and pull)   (b // B_local)'s gradient buffer while it streams the sorted ids, applies 1/W and
+                       the fused optimizer (the all-gather, restricted to the rows this rank owns: with one
+                       id per bag 1/W of the all-gather's traffic).
 
 Three stream-ordered cross-rank barriers per step bracket the peer accesses; no pooled
 [B_global, D_local] tensor, no NCCL pass over the embeddings and no split/cat copy exist.
@@ -45,7 +51,9 @@ def peer_dist_wanted(pg: Optional[dist.ProcessGroup], device: Optional[torch.dev
 class PeerExchange:
     """Symmetric buffers of one sharded module for a given local batch size."""
 
-    def __init__(self, pg: dist.ProcessGroup, device: torch.device, B_local: int, total_D: int, rw_dim: int) -> None:
+    def __init__(self, pg: dist.ProcessGroup, device: torch.device, B_local: int, total_D: int, rw_dim: int,
+                 feat_cols: Optional[List[Tuple[int, int]]] = None,
+                 tw_map: Optional[List[Optional[Tuple[int, int]]]] = None, tw_pitch: int = 0) -> None:
         import torch.distributed._symmetric_memory as symm_mem
         self.W, self.rank = dist.get_world_size(pg), dist.get_rank(pg)
         self.B_local, self.total_D, self.rw_dim = B_local, total_D, rw_dim
@@ -63,7 +71,30 @@ class PeerExchange:
 
         self.out, self._h_out, out_ptrs = make((B_local, total_D))
         self.grad, self._h_grad, grad_ptrs = make((B_local, total_D))
-        _b200.register_grad_sink(self.grad)  # the dot-interaction backward writes its grad_sparse here
+        # Gradient push (table-wise features): gin[r * B_local + b, local col] on the OWNER holds the
+        # gradient of rank r's sample b.  feat_base / feat_pitch tell the producer where every feature's
+        # rows go: table-wise ones into the owner's gin, the rest into my own `grad` (pulled by the owners).
+        self.gin = self.gin_base = None
+        self.tw_pitch = tw_pitch
+        feat_base = feat_pitch = None
+        self.pushed_steps = 0
+        same_dim = feat_cols is not None and len({d for _c, d in feat_cols}) == 1
+        if tw_map is not None and tw_pitch > 0 and same_dim and os.environ.get("B200_PEER_PUSH", "1") != "0":
+            self.gin, self._h_gin, gin_ptrs = make((self.W * B_local, tw_pitch))
+            self.gin_base = torch.tensor([gin_ptrs[self.rank]], dtype=torch.int64, device=device)
+            fb, fp = [], []
+            for (col, _dim), tw in zip(feat_cols, tw_map):
+                if tw is None:
+                    fb.append(grad_ptrs[self.rank] + 4 * col)
+                    fp.append(total_D)
+                else:
+                    owner, local_col = tw
+                    fb.append(gin_ptrs[owner] + 4 * (self.rank * B_local * tw_pitch + local_col))
+                    fp.append(tw_pitch)
+            feat_base = torch.tensor(fb, dtype=torch.int64, device=device)
+            feat_pitch = torch.tensor(fp, dtype=torch.int64, device=device)
+        # the dot-interaction backward writes its grad_sparse here (and, feature by feature, to the owners)
+        self.sink = _b200.register_grad_sink(self.grad, feat_base, feat_pitch, self.out)
         self.out_bases = torch.tensor(out_ptrs, dtype=torch.int64, device=device)
         self.grad_bases = torch.tensor(grad_ptrs, dtype=torch.int64, device=device)
         self.stage = None
@@ -87,10 +118,12 @@ class PeerExchange:
 class _Part:
     """One table-batched lookup module with its column maps."""
 
-    __slots__ = ("tbe", "row_wise", "dst_col", "src_col", "n_features")
+    __slots__ = ("tbe", "row_wise", "dst_col", "src_col", "n_features", "gin_col")
 
-    def __init__(self, tbe, row_wise: bool, dst_col: torch.Tensor, src_col: torch.Tensor, n_features: int) -> None:
+    def __init__(self, tbe, row_wise: bool, dst_col: torch.Tensor, src_col: torch.Tensor, n_features: int,
+                 gin_col: Optional[torch.Tensor] = None) -> None:
         self.tbe, self.row_wise, self.dst_col, self.src_col, self.n_features = tbe, row_wise, dst_col, src_col, n_features
+        self.gin_col = gin_col  # table-wise: this module's feature columns inside my gin buffer
 
 
 class PeerLookupDist:
@@ -122,6 +155,8 @@ class PeerLookupDist:
                 self.embedding_dims.append(cfg.embedding_dim)
                 col += cfg.embedding_dim
         self._total_D = col
+        self._tw_of: Dict[str, Tuple[int, int]] = {}  # embedding name -> (owner rank, column in its gin)
+        self._tw_pitch = 0
         self._rw_dim = 0
         self._rw_col4: Optional[torch.Tensor] = None
 
@@ -136,9 +171,22 @@ class PeerLookupDist:
                 raise NotImplementedError("stochastic rounding of fp16/bf16 tables takes the NCCL path")
             parts: List[_Part] = []
             if isinstance(sharding, BaseTwEmbeddingSharding):
+                # every rank's table-wise features, in that rank's module order: the layout of its gin
+                tw_dims = []
+                for r, cfgs in enumerate(sharding._grouped_embedding_configs_per_rank):
+                    local = 0
+                    for cfg in cfgs:
+                        for n, d in zip(cfg.embedding_names(), cfg.embedding_dims()):
+                            self._tw_of[n] = (r, local)
+                            local += d
+                    tw_dims.append(local)
+                self._tw_pitch = max(tw_dims) if tw_dims else 0
+                base = 0
                 for m in mods:
                     c = cols(m.config.embedding_names())
-                    parts.append(_Part(m.emb_module, False, c, c, m.config.num_features()))
+                    gin_col = (m.emb_module.D_offsets[:-1] + base).to(torch.int32)
+                    parts.append(_Part(m.emb_module, False, c, c, m.config.num_features(), gin_col))
+                    base += m.emb_module.total_D
             elif isinstance(sharding, BaseRwEmbeddingSharding):
                 if self._rw_dim:
                     raise NotImplementedError("one row-wise sharding per module")
@@ -167,7 +215,14 @@ class PeerLookupDist:
     def exchange(self, B_local: int) -> PeerExchange:
         px = self._exchanges.get(B_local)
         if px is None:
-            px = PeerExchange(self._pg, self._device, B_local, self._total_D, self._rw_dim)
+            feat_cols = []
+            c0 = 0
+            for d in self.embedding_dims:
+                feat_cols.append((c0, d))
+                c0 += d
+            tw_map = [self._tw_of.get(n) for n in self.embedding_names]
+            px = PeerExchange(self._pg, self._device, B_local, self._total_D, self._rw_dim, feat_cols, tw_map,
+                              self._tw_pitch)
             self._exchanges[B_local] = px
         return px
 
@@ -241,9 +296,17 @@ class _PeerLookup(torch.autograd.Function):
     def backward(ctx, grad_out):
         from fbgemm_gpu import _tbe_autograd as ta
         px = ctx.px
+        pushed = px.sink.scattered
+        px.sink.scattered = False
         if grad_out.data_ptr() != px.grad.data_ptr() or not grad_out.is_contiguous():
+            if pushed:
+                raise RuntimeError(
+                    "the pooled embeddings' gradient was scattered to the owning ranks by its producer but autograd "
+                    "delivered a different tensor (the embeddings feed more than one consumer); set "
+                    "B200_PEER_PUSH=0 to use the pull exchange")
             px.grad.copy_(grad_out)  # producers that know the sink (ops.register_grad_sink) skip this pass
-        px.barrier()  # C: every rank's gradient buffer is complete
+        px.pushed_steps += int(pushed)
+        px.barrier()  # C: every rank's gradient buffer is complete / every pushed row has landed
         px.quiesced = True
         scale = 1.0 / px.W if comm_ops.GRADIENT_DIVISION else 1.0
         for (p, idx, off), (s, ev, B) in zip(ctx.work, ctx.sorts):
@@ -257,7 +320,11 @@ class _PeerLookup(torch.autograd.Function):
                 torch.cuda.current_stream(idx.device).wait_event(ev)
             keys, payload, _bag = s
             srt = _b200.SortedIndices(keys, payload, None, keys.numel(), max(1, m.total_hash_size_bits), None)
-            _b200.tbe_backward_peer(px.grad_bases, px.B_local, px.total_D, p.src_col, scale, srt, m.weights_dev,
+            if pushed and not p.row_wise:  # my features' gradients of all B_global samples are in my gin
+                bases, B_src, pitch, src_col = px.gin_base, px.W * px.B_local, px.tw_pitch, p.gin_col
+            else:
+                bases, B_src, pitch, src_col = px.grad_bases, px.B_local, px.total_D, p.src_col
+            _b200.tbe_backward_peer(bases, B_src, pitch, src_col, scale, srt, m.weights_dev,
                                     m.weights_offsets, m.D_offsets, m.hash_size_cumsum, B, m.max_D, m._all_D_mult8,
                                     off, None, int(m.pooling_mode), ta._OPT_CODE[m.optimizer],
                                     m.momentum1_dev if m.momentum1_dev.numel() else None, m.momentum1_offsets,

@@ -520,6 +520,10 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
         }
       }
       const int d = h * kBwdKC + 8 * nt + 2 * t;
+      // SCATTER: rows may live on another GPU, where 8-byte stores waste the link (measured: 2.8x the
+      // kernel time).  The finished 8-column block replaces the X block it was computed from (nobody
+      // reads those columns again) and the quarter sample leaves below as 128-byte row segments.
+      if constexpr (SCATTER) __syncwarp();  // every lane has loaded its B fragments of this block
 #pragma unroll
       for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
@@ -532,13 +536,22 @@ interaction_backward_mma_kernel(const float* __restrict__ dense, const float* __
               v.y += gcur[d + 1];
               *reinterpret_cast<float2*>(grad_dense + s * D + d) = v;
             } else if constexpr (SCATTER) {
-              float* row = reinterpret_cast<float*>(s_fbase[i - 1]) + s * s_fpitch[i - 1];
-              *reinterpret_cast<float2*>(row + d) = v;
+              *reinterpret_cast<float2*>(const_cast<float*>(st) + i * ld + 8 * nt + 2 * t) = v;
             } else {
               *reinterpret_cast<float2*>(grad_sparse + (s * F + (i - 1)) * (int64_t)D + d) = v;
             }
           }
         }
+    }
+    if constexpr (SCATTER) {
+      __syncwarp();
+      constexpr int kChunks = kBwdKC / 4;  // 16-byte chunks per row segment
+      for (int r = 1 + lane / kChunks; r < n; r += 32 / kChunks) {
+        const float4 v = *reinterpret_cast<const float4*>(st + r * ld + 4 * (lane % kChunks));
+        float* row = reinterpret_cast<float*>(s_fbase[r - 1]) + s * s_fpitch[r - 1];
+        *reinterpret_cast<float4*>(row + h * kBwdKC + 4 * (lane % kChunks)) = v;
+      }
+      // the next iteration's __syncwarp (before it refills this stage) orders these loads
     }
     if (++h == nch) {
       h = 0;

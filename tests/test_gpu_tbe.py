@@ -251,6 +251,63 @@ def test_interaction_fwd_bwd(ops, B, F, D):
     np.testing.assert_allclose(gs.cpu().numpy(), egs, rtol=1e-5, atol=1e-4)
 
 
+@pytest.mark.parametrize("B,F,D", [(65, 26, 128), (3001, 26, 128), (130, 8, 64), (1250, 30, 64), (40, 5, 32), (200, 15, 192)])
+def test_interaction_backward_scatter(ops, B, F, D):
+    """b200_interaction_backward_scatter (the table-wise gradient exchange fused into the producer): every
+    feature's rows land at its own base + sample * pitch - here local buffers standing in for the owners'
+    [B_global, D_owned] buffers on other GPUs, at a row offset like a non-zero rank's - and equal the dense
+    [B, F, D] result bit for bit (same arithmetic, different stores); dense gradient likewise."""
+    from b200_sparse.cabi import load
+    lib = load()
+    rng = np.random.default_rng(B + F)
+    dense = dev(rng.standard_normal((B, D)).astype(np.float32))
+    sparse = dev(rng.standard_normal((B, F, D)).astype(np.float32))
+    width = D + (F + 1) * F // 2
+    go = dev(rng.standard_normal((B, width)).astype(np.float32))
+    gd_ref, gs_ref = ops.interaction_backward(dense, sparse, go)
+    # features dealt round-robin to 3 "owners"; owner o holds [2 * B, D_o] and my samples start at row B
+    owners = [f % 3 for f in range(F)]
+    n_own = [owners.count(o) for o in range(3)]
+    bufs = [torch.full((2 * B, max(1, n) * D), float("nan"), device="cuda") for n in n_own]
+    seen = [0, 0, 0]
+    fb, fp = [], []
+    for f in range(F):
+        o = owners[f]
+        fb.append(bufs[o].data_ptr() + 4 * (B * bufs[o].shape[1] + seen[o] * D))
+        fp.append(bufs[o].shape[1])
+        seen[o] += 1
+    fb_t, fp_t = dev(np.array(fb, dtype=np.int64)), dev(np.array(fp, dtype=np.int64))
+    gd = torch.empty_like(dense)
+    rc = lib.b200_interaction_backward_scatter(dense.data_ptr(), sparse.data_ptr(), go.data_ptr(), go.stride(0), B, F, D,
+                                               gd.data_ptr(), fb_t.data_ptr(), fp_t.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    assert torch.equal(gd, gd_ref)
+    seen = [0, 0, 0]
+    for f in range(F):
+        o = owners[f]
+        got = bufs[o][B:, seen[o] * D:(seen[o] + 1) * D]
+        assert torch.equal(got, gs_ref[:, f, :]), f"feature {f}"
+        seen[o] += 1
+    for o in range(3):
+        assert bool(torch.isnan(bufs[o][:B]).all()), "rows of the other rank's samples must stay untouched"
+
+
+def test_interaction_backward_scatter_unsupported(ops):
+    """Shapes outside the tensor-core kernel (D % 32 != 0 or more than 31 features) are refused, not
+    silently computed in another layout: the caller keeps the dense path."""
+    from b200_sparse.cabi import load
+    lib = load()
+    for B, F, D in ((8, 4, 16), (8, 32, 64)):
+        dense, sparse = torch.zeros(B, D, device="cuda"), torch.zeros(B, F, D, device="cuda")
+        go = torch.zeros(B, D + (F + 1) * F // 2, device="cuda")
+        z = torch.zeros(F, dtype=torch.int64, device="cuda")
+        rc = lib.b200_interaction_backward_scatter(dense.data_ptr(), sparse.data_ptr(), go.data_ptr(), go.stride(0), B,
+                                                   F, D, dense.data_ptr(), z.data_ptr(), z.data_ptr(),
+                                                   torch.cuda.current_stream().cuda_stream)
+        assert rc == -2, rc
+
+
 # ---------------------------------------------------------------------------------------------
 # fused lookup + exchange entry points, exercised on ONE GPU with local buffers standing in for the
 # peers' (the multi-GPU run is tests/dist_parity_worker.py)

@@ -246,16 +246,7 @@ def main():
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--out", default="")
     ap.add_argument("--cfg4-only", default="", help="T,D,B,L: run one point of the cfg4 sweep")
-    ap.add_argument("--l2-gran", type=int, default=0, help="experiment: cudaLimitMaxL2FetchGranularity (bytes)")
     a = ap.parse_args()
-    if a.l2_gran:
-        import ctypes
-        torch.zeros(1, device=DEV)
-        rt = ctypes.CDLL("libcudart.so.12")
-        rc = rt.cudaDeviceSetLimit(5, ctypes.c_size_t(a.l2_gran))  # cudaLimitMaxL2FetchGranularity = 0x05
-        got = ctypes.c_size_t(0)
-        rt.cudaDeviceGetLimit(ctypes.byref(got), 5)
-        print(json.dumps({"l2_fetch_granularity_set_rc": rc, "now": got.value}), flush=True)
     secs = {"cfg2": sec_cfg2, "zipf": sec_zipf, "cfg4": lambda: sec_cfg4(a.quick, a.cfg4_only), "cfg5": sec_cfg5,
             "jagged": sec_jagged, "interaction": sec_interaction}
     for name in a.sections.split(","):

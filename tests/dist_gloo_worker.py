@@ -50,7 +50,7 @@ def check_kjt_all2all_variable_batch(rank: int, world: int) -> None:
     key k of the output holds rank 0's samples, then rank 1's, ..."""
     from torchrec.distributed.dist_data import KJTAllToAll
     keys, splits = ["f0", "f1", "f2"], [2, 1]
-    for batch_sizes in ([3, 5], [4, 1], [2, 2]):
+    for batch_sizes in ([3, 5], [4, 1], [2, 2], [0, 3]):  # a rank may arrive with an empty batch
         for weighted in (False, True):
             mine = make_kjt(rank, keys, batch_sizes[rank], 100, weighted)
             got = KJTAllToAll(dist.group.WORLD, splits, variable_batch_size=True)(mine).wait().wait()

@@ -9,8 +9,9 @@ batch i, instead of draining the queue in the middle of every step.
 
 The reference finds the sharded modules' inputs by FX-tracing the model; here every ShardedModule takes
 `sparse_features_fn(batch)` (default: `batch.sparse_features`), which covers DLRM-style models whose
-sharded collections all consume the batch's KeyedJaggedTensor.  The reference fork's hard-coded loss-log
-file (:538-543) is not reproduced.
+sharded collections all consume the batch's KeyedJaggedTensor.  The reference fork appends every step's
+losses to a hard-coded file on rank 0 (:538-543); here that is the optional `loss_log_path` argument
+(off by default: it costs a device -> host read per step).
 """
 from __future__ import annotations
 
@@ -25,6 +26,11 @@ from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
 
 In = TypeVar("In")
 Out = TypeVar("Out")
+
+
+def _rank() -> int:
+    import torch.distributed as dist
+    return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
 
 
 def _to_device(batch, device: torch.device, non_blocking: bool):
@@ -68,8 +74,10 @@ class TrainPipelineBase(Generic[In, Out]):
 
 class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
     def __init__(self, model: nn.Module, optimizer: torch.optim.Optimizer, device: torch.device,
-                 sparse_features_fn: Optional[Callable[[In], KeyedJaggedTensor]] = None) -> None:
+                 sparse_features_fn: Optional[Callable[[In], KeyedJaggedTensor]] = None,
+                 loss_log_path: Optional[str] = None) -> None:
         super().__init__(model, optimizer, device)
+        self._loss_log_path = loss_log_path
         if device.type != "cuda":
             raise RuntimeError("TrainPipelineSparseDist overlaps CUDA streams; use TrainPipelineBase on CPU")
         # high priority: the small bucketize / permute / reduction kernels whose results the host waits for
@@ -166,6 +174,9 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
             self._issue_sparse_data_dist(self._batch_ip1)
         losses, output = self._model(self._batch_i)
         if self._model.training:
+            if self._loss_log_path is not None and _rank() == 0:
+                with open(self._loss_log_path, "a") as f:  # same line format as the fork's log
+                    f.write(str(losses.detach().cpu().numpy().tolist()) + "\n")
             torch.sum(losses, dim=0).backward()
             self._optimizer.step()
         # ... phase 2: the host read of the receive sizes happens once the whole step of batch i is

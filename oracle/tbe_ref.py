@@ -190,3 +190,61 @@ def interaction_backward(dense, sparse, grad_out):
     dX = np.einsum("bij,bjd->bid", Gs, X)
     gd = dX[:, 0, :] + grad_out[:, :D]
     return gd.astype(np.float32), dX[:, 1:, :].astype(np.float32)
+
+
+# ---------------------------------------------------------------------------------------------
+# Stochastic rounding of fp32 -> fp16 / bf16 weight rows (reference: stochastic_rounding_vector /
+# stochastic_rounding_scalar, fbgemm_gpu/include/fbgemm_gpu/fbgemm_cuda_utils.cuh, driven by
+# embedding_backward_split_template.cu:367-380 with a Philox4x32-10 stream).  The generator is the
+# published Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11;
+# Random123 / cuRAND), pinned in tests/test_oracle_golden.py by the Random123 known-answer vectors.
+# ---------------------------------------------------------------------------------------------
+_PHILOX_M0, _PHILOX_M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
+_PHILOX_W0, _PHILOX_W1 = 0x9E3779B9, 0xBB67AE85
+
+
+def philox4x32_10(ctr, key):
+    """ctr: uint32 array [..., 4], key: two uint32 scalars (or arrays broadcastable to ctr[..., 0]).
+    Returns uint32 [..., 4]."""
+    c = [np.asarray(ctr)[..., i].astype(np.uint64) for i in range(4)]
+    k0 = np.asarray(key[0]).astype(np.uint64)
+    k1 = np.asarray(key[1]).astype(np.uint64)
+    mask = np.uint64(0xFFFFFFFF)
+    for r in range(10):
+        p0 = _PHILOX_M0 * c[0]
+        p1 = _PHILOX_M1 * c[2]
+        hi0, lo0 = p0 >> np.uint64(32), p0 & mask
+        hi1, lo1 = p1 >> np.uint64(32), p1 & mask
+        c = [hi1 ^ c[1] ^ k0, lo1, hi0 ^ c[3] ^ k1, lo0]
+        k0 = (k0 + np.uint64(_PHILOX_W0)) & mask
+        k1 = (k1 + np.uint64(_PHILOX_W1)) & mask
+    return np.stack([x.astype(np.uint32) for x in c], axis=-1)
+
+
+def stochastic_round(values, dtype, seed, offset, first_element, epv):
+    """What b200_tbe_backward_sr stores for the fp32 `values` (1-D, a whole number of EPV-element
+    vectors starting at element `first_element` of the weight buffer): fp32 bit patterns that are
+    exactly representable in `dtype` ("fp16": 13 low mantissa bits dropped, "bf16": 16).
+
+    One Philox call per vector: counter (vector index lo, hi, offset lo, hi), key (seed lo, hi).
+    EPV = 8: element 2i of the vector uses the low, 2i+1 the high 16 bits of word i; EPV = 4: element i
+    uses the high 16 bits of word i.  Random bits (masked to the dropped width) are added to the fp32
+    bit pattern and the dropped bits cleared; inf / nan pass through."""
+    v = np.ascontiguousarray(values, dtype=np.float32)
+    assert v.ndim == 1 and v.size % epv == 0 and first_element % epv == 0
+    nvec = v.size // epv
+    vec = np.arange(nvec, dtype=np.uint64) + np.uint64(first_element // epv)
+    ctr = np.stack([(vec & np.uint64(0xFFFFFFFF)).astype(np.uint32), (vec >> np.uint64(32)).astype(np.uint32),
+                    np.full(nvec, offset & 0xFFFFFFFF, dtype=np.uint32),
+                    np.full(nvec, (offset >> 32) & 0xFFFFFFFF, dtype=np.uint32)], axis=-1)
+    r = philox4x32_10(ctr, (np.uint32(seed & 0xFFFFFFFF), np.uint32((seed >> 32) & 0xFFFFFFFF)))  # [nvec, 4]
+    if epv == 8:
+        r16 = np.stack([r & np.uint32(0xFFFF), r >> np.uint32(16)], axis=-1).reshape(nvec, 8)
+    else:
+        assert epv == 4
+        r16 = r >> np.uint32(16)
+    mask = np.uint32(0xFFFF if dtype == "bf16" else 0x1FFF)
+    u = v.view(np.uint32).reshape(nvec, epv)
+    special = (u & np.uint32(0x7F800000)) == np.uint32(0x7F800000)
+    out = (u + (r16.astype(np.uint32) & mask)) & ~mask
+    return np.where(special, u, out).reshape(-1).view(np.float32)

@@ -470,3 +470,42 @@ def test_backward_stochastic_rounding(ops, wdt, D, pattern):
     np.testing.assert_array_equal(step(True), a)                 # same Philox state: same bits
     assert not np.array_equal(step(True, offset=2), a)           # next step: a different draw
     assert not np.array_equal(step(True, seed=99), a)
+
+
+@pytest.mark.parametrize("wdt,dims", [
+    ("fp16", [64, 128]),       # EPV 8: packed tile + ring path, two tables (vector index runs across tables)
+    ("bf16", [32, 512]),       # EPV 8: 4-lane packed rows + two vectors per lane
+    ("fp16", [36, 20]),        # EPV 4: one 32-bit Philox word per element
+    ("bf16", [256]),
+])
+def test_backward_stochastic_rounding_bits(ops, wdt, dims):
+    """Bit-exact against the oracle: SGD with lr = 1 (the fp32 update w - g has a single rounding), one id per
+    bag, every row touched once; the stored 16-bit rows must equal oracle.stochastic_round of the fp32
+    update for the same (seed, offset) - Philox4x32-10 (known-answer vectors in tests/test_oracle_golden.py)
+    keyed by the vector's position in the weight buffer."""
+    rng = np.random.default_rng(len(dims) * 100 + dims[0])
+    T, B = len(dims), 300
+    rows = [B] * T
+    w, wo, Do, hsc = build_tables(rng, rows, dims, wdt)
+    indices = np.concatenate([rng.permutation(B) for _ in range(T)]).astype(np.int64)
+    offsets = np.arange(T * B + 1, dtype=np.int64)
+    grad = (rng.standard_normal((B, int(Do[-1]))) * 0.01).astype(np.float32)
+    epv = 8 if all(d % 8 == 0 for d in dims) else 4
+    seed, offset = 0x1234_5678_9ABC, (7 << 32) + 3
+    # expected: per table, row r gets the gradient of the sample that looked it up
+    w32 = w.float().numpy()
+    exp = np.empty_like(w32)
+    for t in range(T):
+        D = dims[t]
+        wt = w32[wo[t]:wo[t] + rows[t] * D].reshape(rows[t], D)
+        g = np.empty_like(wt)
+        g[indices[t * B:(t + 1) * B]] = grad[:, Do[t]:Do[t + 1]]
+        upd = (wt - g).astype(np.float32).reshape(-1)
+        exp[wo[t]:wo[t] + rows[t] * D] = R.stochastic_round(upd, wdt, seed, offset, int(wo[t]), epv)
+    wg = w.cuda()
+    srt = ops.tbe_sort_indices(dev(indices), dev(offsets), dev(hsc), int(np.log2(sum(rows))) + 1, B, False)
+    ops.tbe_backward(dev(grad), srt, wg, dev(wo), dev(Do), dev(hsc), B, max(dims), epv == 8, dev(offsets), None,
+                     0, 0, None, None, 1.0, 0.0, True, seed, offset)
+    got = w_to_np(wg)
+    bad = np.flatnonzero(got != exp)
+    assert bad.size == 0, (bad[:8], got[bad[:8]], exp[bad[:8]])

@@ -228,3 +228,47 @@ class _OracleBackend:
 def test_oracle_matches_reference_cpu_kernel_fixtures():
     import golden_cases
     assert golden_cases.run_all(_OracleBackend) == 38
+
+
+def test_philox4x32_10_known_answers():
+    """Random123's known-answer vectors for philox4x32-10 (examples/kat_vectors: zero, all-ones and
+    digits-of-pi inputs) pin the generator the stochastic-rounding oracle - and through it the CUDA
+    kernel (tests/test_gpu_tbe.py::test_backward_stochastic_rounding_bits) - is built on."""
+    kat = [
+        ((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+        ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+        ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+         (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)),
+    ]
+    for ctr, key, exp in kat:
+        got = R.philox4x32_10(np.array(ctr, dtype=np.uint32), (np.uint32(key[0]), np.uint32(key[1])))
+        assert [int(x) for x in got] == list(exp), ([hex(int(x)) for x in got], [hex(x) for x in exp])
+    # vectorised call == one call per counter
+    ctrs = np.array([k[0] for k in kat], dtype=np.uint32)
+    many = R.philox4x32_10(ctrs, (np.uint32(7), np.uint32(9)))
+    for i in range(3):
+        np.testing.assert_array_equal(many[i], R.philox4x32_10(ctrs[i], (np.uint32(7), np.uint32(9))))
+
+
+def test_stochastic_round_properties():
+    """Results are representable in the 16-bit type, bracket the input by one ulp, are unbiased, and
+    reduce to the identity for values that are already representable."""
+    import torch
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(1 << 16).astype(np.float32)
+    x = (np.sign(x) * np.maximum(np.abs(x), 2.0 ** -10)).astype(np.float32)  # fp16 normal range (see oracle)
+    for dtype, tdt, keep in (("fp16", torch.float16, 13), ("bf16", torch.bfloat16, 16)):
+        for epv in (8, 4):
+            y = R.stochastic_round(x, dtype, seed=123, offset=5, first_element=64, epv=epv)
+            t = torch.from_numpy(y.copy())
+            assert torch.equal(t.to(tdt).float(), t)  # exactly representable: the later RN pack is exact
+            lo = (x.view(np.uint32) & ~np.uint32((1 << keep) - 1)).view(np.float32)   # truncation
+            ulp = np.abs((lo.view(np.uint32) + np.uint32(1 << keep)).view(np.float32) - lo)
+            assert np.all((y == lo) | (np.abs(y - lo) == ulp))
+            # unbiased: E[y] = x, error of the mean ~ ulp / sqrt(n)
+            assert abs(float(np.mean((y - x) / ulp))) < 0.01
+            again = R.stochastic_round(y, dtype, seed=9, offset=1, first_element=0, epv=epv)
+            np.testing.assert_array_equal(again, y)
+    z = np.array([np.inf, -np.inf, np.nan, 0.0, -0.0, 1.0, 65504.0, 1e-30], dtype=np.float32)
+    out = R.stochastic_round(z, "fp16", 1, 1, 0, 8)
+    assert np.isinf(out[0]) and np.isinf(out[1]) and np.isnan(out[2]) and out[3] == 0 and out[5] == 1.0

@@ -94,6 +94,74 @@ def check_pooled_all2all_variable_batch(rank: int, world: int) -> None:
     torch.testing.assert_close(x.grad, exp_g, rtol=1e-6, atol=1e-7)
 
 
+def check_vb_tw_dists(rank: int, world: int) -> None:
+    """The variable-batch table-wise dist modules end to end (vb_tw_sharding.py), with a stand-in lookup:
+    the "pooled embedding" of a bag is [sum of its ids, its length], so the output every rank gets back for
+    its own samples can be computed from its local input alone."""
+    from torchrec.distributed.embedding_types import SparseFeatures
+    from torchrec.distributed.sharding.vb_sharding import VariableBatchShardingContext
+    from torchrec.distributed.sharding.vb_tw_sharding import (
+        VariableBatchTwPooledEmbeddingDist, VariableBatchTwSparseFeaturesDist)
+    keys, splits, D = ["f0", "f1", "f2"], [2, 1], 2
+    for batch_sizes in ([3, 5], [6, 0]):
+        mine = make_kjt(rank, keys, batch_sizes[rank], 100)
+        in_dist = VariableBatchTwSparseFeaturesDist(dist.group.WORLD, splits, [0, 0])
+        out_dist = VariableBatchTwPooledEmbeddingDist(dist.group.WORLD, [s * D for s in splits])
+        lengths_aw = in_dist(SparseFeatures(id_list_features=mine, id_score_list_features=None))
+        sctx = VariableBatchShardingContext.from_lengths_awaitable(lengths_aw._a)
+        assert sctx.batch_size_per_rank == batch_sizes and sctx.global_batch_size == sum(batch_sizes)
+        assert sctx.rows_of(rank) == (sum(batch_sizes[:rank]), sum(batch_sizes[:rank + 1]))
+        got = lengths_aw.wait().wait().id_list_features
+        Bg = sum(batch_sizes)
+        assert got.stride() == Bg
+
+        def pooled(kjt, B):  # [B, n_keys * D]
+            cols = []
+            for k in kjt.keys():
+                jt = kjt[k]
+                off = jt.offsets().tolist()
+                v = jt.values().double()
+                cols.append(torch.stack([torch.stack([v[off[b]:off[b + 1]].sum(), torch.tensor(float(off[b + 1] - off[b]),
+                                                                                               dtype=torch.float64)])
+                                         for b in range(B)]) if B else torch.zeros(0, D, dtype=torch.float64))
+            return torch.cat(cols, dim=1).float() if cols else torch.zeros(B, 0)
+
+        out = out_dist(pooled(got, Bg), sctx).wait()
+        exp = pooled(mine, batch_sizes[rank])  # keys in destination-rank order == model order here
+        assert out.shape == exp.shape == (batch_sizes[rank], len(keys) * D)
+        torch.testing.assert_close(out, exp, rtol=0, atol=0)
+
+
+def check_vb_tw_sharding_factories(rank: int, world: int) -> None:
+    """VariableBatchTwPooledEmbeddingSharding builds the variable-batch dists from a table-wise plan
+    (the lookup it shares with TwPooledEmbeddingSharding needs the CUDA kernels and is covered on GPUs)."""
+    from torchrec.distributed.embeddingbag import create_embedding_bag_sharding
+    from torchrec.distributed.sharding.vb_tw_sharding import (
+        VariableBatchTwPooledEmbeddingDist, VariableBatchTwPooledEmbeddingSharding, VariableBatchTwSparseFeaturesDist)
+    from torchrec.distributed.types import ParameterSharding, ShardingEnv
+    from torchrec.modules.embedding_configs import EmbeddingTableConfig, PoolingType
+    infos = []
+    for i, (rows, dim, owner) in enumerate([(10, 8, 0), (20, 4, 1), (30, 8, 0)]):
+        cfg = EmbeddingTableConfig(num_embeddings=rows, embedding_dim=dim, name=f"t{i}", feature_names=[f"f{i}"],
+                                   pooling=PoolingType.SUM, is_weighted=False, has_feature_processor=False,
+                                   embedding_names=[f"f{i}"])
+        infos.append((cfg, ParameterSharding(sharding_type="table_wise", compute_kernel="batched_fused",
+                                             ranks=[owner]), None))
+    env = ShardingEnv.from_process_group(dist.group.WORLD)
+    sh = create_embedding_bag_sharding("table_wise", infos, env, torch.device("cpu"), variable_batch_size=True)
+    assert isinstance(sh, VariableBatchTwPooledEmbeddingSharding)
+    assert isinstance(sh.create_input_dist(), VariableBatchTwSparseFeaturesDist)
+    out = sh.create_output_dist()
+    assert isinstance(out, VariableBatchTwPooledEmbeddingDist) and out._dist._dim_sum_per_rank == [16, 4]
+    assert sh.id_list_feature_names() == ["f0", "f2", "f1"] and sh.embedding_dims() == [8, 8, 4]
+    try:
+        create_embedding_bag_sharding("row_wise", infos, env, torch.device("cpu"), variable_batch_size=True)
+    except ValueError as e:
+        assert "table_wise" in str(e)
+    else:
+        raise AssertionError("variable batch size with row-wise sharding must be refused")
+
+
 def check_row_wise_input_dist(rank: int, world: int) -> None:
     from torchrec.distributed.dist_data import KJTAllToAll
     from torchrec.distributed.embedding_sharding import bucketize_kjt_before_all2all
@@ -248,6 +316,8 @@ def main() -> None:
     check_kjt_all2all(rank, world)
     check_kjt_all2all_variable_batch(rank, world)
     check_pooled_all2all_variable_batch(rank, world)
+    check_vb_tw_dists(rank, world)
+    check_vb_tw_sharding_factories(rank, world)
     check_row_wise_input_dist(rank, world)
     check_pooled_all2all(rank, world)
     check_reduce_scatter(rank, world)

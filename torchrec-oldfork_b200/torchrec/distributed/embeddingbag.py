@@ -188,9 +188,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
                 if self._variable_batch_size:
                     # the batch sizes were exchanged while the lengths all-to-all was being set up
                     la = aw._b if self._is_weighted else aw._a
-                    ctx.vb_contexts.append(VariableBatchShardingContext(
-                        batch_size_per_rank=list(la._batch_size_per_rank),
-                        batch_size_per_rank_tensor=la._batch_size_per_rank_tensor))
+                    ctx.vb_contexts.append(VariableBatchShardingContext.from_lengths_awaitable(la))
                 awaitables.append(aw)
             return SparseFeaturesListAwaitable(awaitables)
 

@@ -80,9 +80,11 @@ class BaseTwEmbeddingSharding(EmbeddingSharding[SparseFeatures, torch.Tensor]):
 
 class TwSparseFeaturesDist(BaseSparseFeaturesDist[SparseFeatures]):
     def __init__(self, pg: dist.ProcessGroup, id_list_features_per_rank: List[int],
-                 id_score_list_features_per_rank: List[int], device: Optional[torch.device] = None) -> None:
+                 id_score_list_features_per_rank: List[int], device: Optional[torch.device] = None,
+                 variable_batch_size: bool = False) -> None:
         super().__init__()
-        self._dist = SparseFeaturesAllToAll(pg, id_list_features_per_rank, id_score_list_features_per_rank, device)
+        self._dist = SparseFeaturesAllToAll(pg, id_list_features_per_rank, id_score_list_features_per_rank, device,
+                                            variable_batch_size=variable_batch_size)
 
     def forward(self, sparse_features: SparseFeatures) -> Awaitable[Awaitable[SparseFeatures]]:
         return self._dist(sparse_features)

@@ -9,55 +9,49 @@ from fbgemm_gpu.split_embedding_configs import SparseType
 from fbgemm_gpu.split_table_batched_embeddings_ops import PoolingMode
 
 
-@unique
-class PoolingType(Enum):
-    SUM = "SUM"
-    MEAN = "MEAN"
-    NONE = "NONE"
+# name -> (bits per element, fbgemm SparseType value); INT4 / INT2 exist for configuration parity only
+_DATA_TYPES = {"FP32": (32, "fp32"), "FP16": (16, "fp16"), "INT8": (8, "int8"), "INT4": (4, "int4"), "INT2": (2, "int2")}
+# name -> (table-batched kernel mode, nn.EmbeddingBag mode string)
+_POOLINGS = {"SUM": (PoolingMode.SUM, "sum"), "MEAN": (PoolingMode.MEAN, "mean"), "NONE": (PoolingMode.NONE, None)}
 
-
-@unique
-class DataType(Enum):
-    FP32 = "FP32"
-    FP16 = "FP16"
-    INT8 = "INT8"
-    INT4 = "INT4"
-    INT2 = "INT2"
-
-
-DATA_TYPE_NUM_BITS: Dict[DataType, int] = {
-    DataType.FP32: 32, DataType.FP16: 16, DataType.INT8: 8, DataType.INT4: 4, DataType.INT2: 2}
-
-_POOL = {PoolingType.SUM: (PoolingMode.SUM, "sum"), PoolingType.MEAN: (PoolingMode.MEAN, "mean")}
+PoolingType = unique(Enum("PoolingType", {n: n for n in _POOLINGS}, module=__name__))
+DataType = unique(Enum("DataType", {n: n for n in _DATA_TYPES}, module=__name__))
+DATA_TYPE_NUM_BITS: Dict[DataType, int] = {DataType[n]: bits for n, (bits, _) in _DATA_TYPES.items()}
+_QUANTIZED_DTYPES = {torch.quint8: DataType.INT8, torch.qint8: DataType.INT8, torch.quint4x2: DataType.INT4,
+                     torch.quint2x4: DataType.INT2}
 
 
 def dtype_to_data_type(dtype: torch.dtype) -> DataType:
-    table = {torch.quint8: DataType.INT8, torch.qint8: DataType.INT8, torch.quint4x2: DataType.INT4,
-             torch.quint2x4: DataType.INT2}
-    if dtype not in table:
+    """Quantized torch dtype of a state_dict entry -> DataType (quant/embedding_modules.py)."""
+    found = _QUANTIZED_DTYPES.get(dtype)
+    if found is None:
         raise Exception(f"Invalid data type {dtype}")
-    return table[dtype]
+    return found
 
 
 def pooling_type_to_pooling_mode(pooling_type: PoolingType) -> PoolingMode:
-    if pooling_type == PoolingType.NONE:
-        return PoolingMode.NONE
-    if pooling_type not in _POOL:
+    entry = _POOLINGS.get(getattr(pooling_type, "name", None))
+    if entry is None:
         raise Exception(f"Invalid pooling type {pooling_type}")
-    return _POOL[pooling_type][0]
+    return entry[0]
 
 
 def pooling_type_to_str(pooling_type: PoolingType) -> str:
-    if pooling_type not in _POOL:
+    entry = _POOLINGS.get(getattr(pooling_type, "name", None))
+    if entry is None or entry[1] is None:
         raise ValueError(f"Unsupported pooling type {pooling_type}")
-    return _POOL[pooling_type][1]
+    return entry[1]
 
 
 def data_type_to_sparse_type(data_type: DataType) -> SparseType:
-    try:
-        return SparseType(data_type.value.lower())
-    except (ValueError, AttributeError):
+    entry = _DATA_TYPES.get(getattr(data_type, "name", None))
+    if entry is None:
         raise ValueError(f"Invalid DataType {data_type}")
+    return SparseType(entry[1])
+
+
+def _default_init_bound(num_embeddings: int) -> float:
+    return sqrt(1.0 / num_embeddings)
 
 
 @dataclass
@@ -70,11 +64,12 @@ class BaseEmbeddingConfig:
     weight_init_max: Optional[float] = None
     weight_init_min: Optional[float] = None
 
+    # uniform(-1/sqrt(rows), 1/sqrt(rows)) unless the config says otherwise (reference :95-106)
     def get_weight_init_max(self) -> float:
-        return sqrt(1 / self.num_embeddings) if self.weight_init_max is None else self.weight_init_max
+        return self.weight_init_max if self.weight_init_max is not None else _default_init_bound(self.num_embeddings)
 
     def get_weight_init_min(self) -> float:
-        return -sqrt(1 / self.num_embeddings) if self.weight_init_min is None else self.weight_init_min
+        return self.weight_init_min if self.weight_init_min is not None else -_default_init_bound(self.num_embeddings)
 
     def num_features(self) -> int:
         return len(self.feature_names)

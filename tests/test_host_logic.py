@@ -252,3 +252,58 @@ def test_binary_criteo_datapipe_shuffle_batches(tmp_path):
         np.testing.assert_array_equal(rows_p[order[0]], rows_s[order[1]])
         moved |= not np.array_equal(rows_p, rows_s)
     assert moved
+
+
+# ---------------------------------------------------------------- KJT / KeyedTensor vs the reference's own classes
+def test_kjt_ops_match_reference_fixture():
+    """offsets / per-key totals / permute (duplicates, drops) / split / to_dict / KeyedTensor.regroup equal what
+    the reference's own KeyedJaggedTensor and KeyedTensor produced on the same seeded inputs
+    (tests/golden/make_golden_kjt.py ran them over the reference's CPU kernels)."""
+    import numpy as np
+    from golden_cases import KJT_CASES, kjt_case_inputs
+    from torchrec.sparse.jagged_tensor import KeyedJaggedTensor, KeyedTensor
+    z = np.load(os.path.join(HERE, "golden", "kjt_ops.npz"))
+
+    def eq(got, key):
+        exp = z[key]
+        got = got.numpy() if isinstance(got, torch.Tensor) else np.asarray(got)
+        assert got.dtype == exp.dtype or exp.dtype.kind in "US", (key, got.dtype, exp.dtype)
+        np.testing.assert_array_equal(got, exp, err_msg=key)
+
+    for ci, case in enumerate(KJT_CASES):
+        keys, lengths, values, weights, stride = kjt_case_inputs(case)
+        k = KeyedJaggedTensor(keys=keys, values=torch.from_numpy(values), lengths=torch.from_numpy(lengths),
+                              weights=None if weights is None else torch.from_numpy(weights), stride=stride)
+        pre = f"case{ci}"
+        eq(k.offsets(), f"{pre}/offsets")
+        eq(np.array(k.length_per_key(), dtype=np.int64), f"{pre}/length_per_key")
+        eq(np.array(k.offset_per_key(), dtype=np.int64), f"{pre}/offset_per_key")
+        for pi, perm in enumerate(case["permutes"]):
+            p = k.permute(perm, torch.tensor(perm, dtype=torch.int32))
+            assert p.keys() == z[f"{pre}/permute{pi}/keys"].tolist()
+            eq(p.values(), f"{pre}/permute{pi}/values")
+            eq(p.lengths(), f"{pre}/permute{pi}/lengths")
+            eq(np.array(p.length_per_key(), dtype=np.int64), f"{pre}/permute{pi}/length_per_key")
+            if weights is not None:
+                eq(p.weights(), f"{pre}/permute{pi}/weights")
+        for si, seg in enumerate(case["splits"]):
+            parts = k.split(seg)
+            assert len(parts) == len(seg)
+            for part_i, part in enumerate(parts):
+                q = f"{pre}/split{si}/part{part_i}"
+                assert part.keys() == z[f"{q}/keys"].tolist() and part.stride() == int(z[f"{q}/stride"])
+                eq(part.values(), f"{q}/values")
+                eq(part.lengths(), f"{q}/lengths")
+                if weights is not None:
+                    eq(part.weights(), f"{q}/weights")
+        d = k.to_dict()
+        assert list(d) == keys
+        for key, j in d.items():
+            eq(j.values(), f"{pre}/dict/{key}/values")
+            eq(j.lengths(), f"{pre}/dict/{key}/lengths")
+            eq(j.offsets(), f"{pre}/dict/{key}/offsets")
+    kts = [KeyedTensor(keys=names, length_per_key=dims, values=torch.from_numpy(z[f"regroup/in_{names[0]}"]))
+           for names, dims in ((["a", "b", "c"], [3, 1, 4]), (["d", "e"], [2, 5]))]
+    outs = KeyedTensor.regroup(kts, [["b", "e"], ["a", "d", "c"], ["e", "a"]])
+    for gi, t in enumerate(outs):
+        eq(t, f"regroup/out{gi}")

@@ -307,3 +307,19 @@ def test_kjt_ops_match_reference_fixture():
     outs = KeyedTensor.regroup(kts, [["b", "e"], ["a", "d", "c"], ["e", "a"]])
     for gi, t in enumerate(outs):
         eq(t, f"regroup/out{gi}")
+
+
+def test_recat_and_split_lengths_match_reference_fixture():
+    """_get_recat (fixed and variable batch sizes, staggered) and _split_lengths equal what the reference's
+    own functions returned (tests/golden/make_golden_recat.py executed them from /root/reference)."""
+    import numpy as np
+    from golden_cases import RECAT_CASES, SPLIT_LENGTHS_CASES
+    from torchrec.distributed.dist_data import _get_recat, _split_lengths
+    z = np.load(os.path.join(HERE, "golden", "recat.npz"))
+    for i, (local_split, num_splits, stagger, batch_sizes) in enumerate(RECAT_CASES):
+        got = _get_recat(local_split, num_splits, stagger, torch.device("cpu"), batch_sizes)
+        exp = z[f"recat{i}"]
+        assert got.numpy().dtype == exp.dtype, (i, got.dtype, exp.dtype)
+        np.testing.assert_array_equal(got.numpy(), exp, err_msg=f"recat case {i}")
+    for i, (splits, keys, offset_per_key) in enumerate(SPLIT_LENGTHS_CASES):
+        assert _split_lengths(splits, keys, offset_per_key) == z[f"split_lengths{i}"].tolist()

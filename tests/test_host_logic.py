@@ -323,3 +323,29 @@ def test_recat_and_split_lengths_match_reference_fixture():
         np.testing.assert_array_equal(got.numpy(), exp, err_msg=f"recat case {i}")
     for i, (splits, keys, offset_per_key) in enumerate(SPLIT_LENGTHS_CASES):
         assert _split_lengths(splits, keys, offset_per_key) == z[f"split_lengths{i}"].tolist()
+
+
+def test_bucketize_kjt_matches_reference_fixture():
+    """Row-wise input dist, step 1: bucketize_kjt_before_all2all (plain / weighted / unbucketize permutation /
+    positions) equals the reference's own function on its own KJT class and CPU kernel
+    (tests/golden/make_golden_bucketize_kjt.py)."""
+    import numpy as np
+    from golden_cases import BUCKETIZE_KJT_CASES, bucketize_kjt_inputs
+    from torchrec.distributed.embedding_sharding import bucketize_kjt_before_all2all
+    from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
+    z = np.load(os.path.join(HERE, "golden", "bucketize_kjt.npz"))
+    for ci, case in enumerate(BUCKETIZE_KJT_CASES):
+        keys, lengths, values, weights, B, block_sizes = bucketize_kjt_inputs(case)
+        k = KeyedJaggedTensor(keys=keys, values=torch.from_numpy(values), lengths=torch.from_numpy(lengths),
+                              weights=None if weights is None else torch.from_numpy(weights), stride=B)
+        got, unbucketize = bucketize_kjt_before_all2all(k, case["W"], torch.from_numpy(block_sizes),
+                                                        output_permute=case["permute"], bucketize_pos=case["pos"])
+        pre = f"case{ci}"
+        assert got.keys() == z[f"{pre}/keys"].tolist() and got.stride() == int(z[f"{pre}/stride"])
+        for name, t in (("values", got.values()), ("lengths", got.lengths()), ("weights", got.weights_or_none()),
+                        ("unbucketize", unbucketize)):
+            key = f"{pre}/{name}"
+            assert (t is not None) == (key in z.files), key
+            if t is not None:
+                assert t.numpy().dtype == z[key].dtype, (key, t.dtype, z[key].dtype)
+                np.testing.assert_array_equal(t.numpy(), z[key], err_msg=key)

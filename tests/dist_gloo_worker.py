@@ -303,6 +303,7 @@ def check_sharded_tensor_state(rank: int, world: int) -> None:
         assert list(sd["state"]) == ["t.weight"] and isinstance(sd["state"]["t.weight"]["t.momentum1"], ShardedTensor)
         new_m = sharded_tensor_from_local(torch.full((sizes[rank],), 7.0), metas[rank], metas, [rows, D],
                                           dist.group.WORLD, rowwise=True)
+        opt.save_param_groups(True)  # reference default: param_groups are neither saved nor loaded
         opt.load_state_dict({"state": {"t.weight": {"t.momentum1": new_m}},
                              "param_groups": [{"params": ["t.weight"], "lr": 0.5}]})
         assert torch.equal(mom, torch.full((sizes[rank],), 7.0)) and opt.param_groups[0]["lr"] == 0.5

@@ -349,3 +349,46 @@ def test_bucketize_kjt_matches_reference_fixture():
             if t is not None:
                 assert t.numpy().dtype == z[key].dtype, (key, t.dtype, z[key].dtype)
                 np.testing.assert_array_equal(t.numpy(), z[key], err_msg=key)
+
+
+def test_combined_optimizer_checkpoint_is_flat_and_strict():
+    """Two fused optimizers combined under empty keys (one per kernel group / sharding type, as
+    ShardedEmbeddingBagCollection builds them) must BOTH survive state_dict()/load_state_dict(); layout and
+    strictness follow the reference's KeyedOptimizer (torchrec/optim/keyed.py:66-196): flat
+    {"state": {<param key>: {<state key>: tensor}}}, no param_groups by default, errors on a missing
+    parameter / state key / count mismatch."""
+    from torchrec.optim.keyed import CombinedOptimizer, KeyedOptimizer
+
+    def fused(name, rows):
+        w, m = torch.zeros(rows, 4), torch.arange(rows, dtype=torch.float32)
+        return KeyedOptimizer({f"embedding_bags.{name}.weight": w}, {w: {f"{name}.momentum1": m}},
+                              [{"params": [w], "lr": 0.1}]), m
+
+    o0, m0 = fused("t0", 3)
+    o1, m1 = fused("t1", 5)
+    comb = CombinedOptimizer([("", o0), ("", o1)])
+    sd = comb.state_dict()
+    assert set(sd) == {"state"}
+    assert set(sd["state"]) == {"embedding_bags.t0.weight", "embedding_bags.t1.weight"}
+    assert sd["state"]["embedding_bags.t0.weight"]["t0.momentum1"] is m0
+    new = {"state": {"embedding_bags.t0.weight": {"t0.momentum1": torch.full((3,), 7.0)},
+                     "embedding_bags.t1.weight": {"t1.momentum1": torch.full((5,), 9.0)}}}
+    comb.load_state_dict(new)
+    assert torch.equal(m0, torch.full((3,), 7.0)) and torch.equal(m1, torch.full((5,), 9.0))
+    with pytest.raises(ValueError, match="Different parameter count"):
+        comb.load_state_dict({"state": {"embedding_bags.t0.weight": new["state"]["embedding_bags.t0.weight"]}})
+    with pytest.raises(ValueError, match="not found"):
+        comb.load_state_dict({"state": {"embedding_bags.t0.weight": new["state"]["embedding_bags.t0.weight"],
+                                        "embedding_bags.tX.weight": {"t1.momentum1": torch.zeros(5)}}})
+    with pytest.raises(ValueError, match="State key"):
+        comb.load_state_dict({"state": {"embedding_bags.t0.weight": {"wrong": torch.zeros(3)},
+                                        "embedding_bags.t1.weight": new["state"]["embedding_bags.t1.weight"]}})
+    with pytest.raises(ValueError, match="Duplicate param key"):
+        CombinedOptimizer([("", o0), ("", fused("t0", 3)[0])])
+    # param_groups travel only when asked for
+    comb.save_param_groups(True)
+    sd = comb.state_dict()
+    assert [g["params"] for g in sd["param_groups"]] == [["embedding_bags.t0.weight"], ["embedding_bags.t1.weight"]]
+    sd["param_groups"][1]["lr"] = 0.5
+    comb.load_state_dict(sd)
+    assert o1.param_groups[0]["lr"] == 0.5 and o0.param_groups[0]["lr"] == 0.1

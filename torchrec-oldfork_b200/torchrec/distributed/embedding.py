@@ -26,6 +26,7 @@ from torchrec.distributed.types import (
     ShardingType)
 from torchrec.modules.embedding_configs import EmbeddingTableConfig, PoolingType
 from torchrec.modules.embedding_modules import EmbeddingCollection
+from torchrec.distributed.embedding_lookup import prefixed_fused_optimizers
 from torchrec.optim.fused import FusedOptimizerModule
 from torchrec.optim.keyed import CombinedOptimizer, KeyedOptimizer
 from torchrec.sparse.jagged_tensor import JaggedTensor, KeyedJaggedTensor
@@ -127,8 +128,7 @@ class ShardedEmbeddingCollection(ShardedModule[SparseFeaturesList, List[torch.Te
         self._feature_splits: List[int] = []
         self._features_order: List[int] = []
         self._has_uninitialized_input_dist = True
-        self._optim = CombinedOptimizer([m.fused_optimizer for m in self._lookups
-                                         if isinstance(m, FusedOptimizerModule)])
+        self._optim = CombinedOptimizer(prefixed_fused_optimizers(self._lookups, "embedding_modules."))
 
     def create_context(self) -> EmbeddingCollectionContext:
         return EmbeddingCollectionContext()

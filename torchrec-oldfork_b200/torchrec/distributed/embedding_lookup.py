@@ -17,6 +17,22 @@ from torchrec.optim.fused import FusedOptimizerModule
 from torchrec.optim.keyed import CombinedOptimizer, KeyedOptimizer
 
 
+def prefixed_fused_optimizers(lookups, prefix: str) -> List[Tuple[str, KeyedOptimizer]]:
+    """The fused optimizers of every table-batched kernel under `lookups`, their parameter keys re-rooted at
+    the unsharded module's attribute (`embedding_bags.` / `embedding_modules.`) so optimizer checkpoints carry
+    the same keys as the reference's (embeddingbag.py:272-283, embedding.py:242-253)."""
+    optims: List[Tuple[str, KeyedOptimizer]] = []
+    for lookup in lookups:
+        for m in lookup.modules():
+            if isinstance(m, (BatchedFusedEmbeddingBag, BatchedFusedEmbedding)):
+                opt = m.fused_optimizer
+                if not getattr(opt, "_b200_prefixed", False):
+                    opt.params = {prefix + k: w for k, w in opt.params.items()}
+                    opt._b200_prefixed = True
+                optims.append(("", opt))
+    return optims
+
+
 class GroupedPooledEmbeddingsLookup(BaseEmbeddingLookup[SparseFeatures, torch.Tensor], FusedOptimizerModule):
     def __init__(self, grouped_configs: List[GroupedEmbeddingConfig],
                  grouped_score_configs: List[GroupedEmbeddingConfig],

@@ -28,6 +28,7 @@ from torchrec.distributed.types import (
     ShardingEnv, ShardingType)
 from torchrec.modules.embedding_configs import EmbeddingTableConfig
 from torchrec.modules.embedding_modules import EmbeddingBagCollection, EmbeddingBagCollectionInterface
+from torchrec.distributed.embedding_lookup import prefixed_fused_optimizers
 from torchrec.optim.fused import FusedOptimizerModule
 from torchrec.optim.keyed import CombinedOptimizer, KeyedOptimizer
 from torchrec.sparse.jagged_tensor import KeyedJaggedTensor, KeyedTensor
@@ -139,9 +140,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         self._env = env
         self._peer = None          # fused lookup + exchange over NVLink peer memory (peer_dist.py)
         self._peer_checked = False
-        optims = [(f"lookups.{i}", m.fused_optimizer) for i, m in enumerate(self._lookups)
-                  if isinstance(m, FusedOptimizerModule)]
-        self._optim = CombinedOptimizer([o for _, o in optims]) if optims else CombinedOptimizer([])
+        self._optim = CombinedOptimizer(prefixed_fused_optimizers(self._lookups, "embedding_bags."))
 
     # ---- lazily built distribution modules
     def _feature_names_of(self, sharding: EmbeddingSharding) -> List[str]:

@@ -3,6 +3,7 @@ KeyedOptimizerWrapper :328): torch.optim.Optimizer subclasses addressed by param
 fused (in-backward) and dense optimizers can be combined and checkpointed together."""
 from __future__ import annotations
 
+import copy
 from typing import Any, Callable, Collection, Dict, List, Mapping, Optional, Tuple, Union
 
 import torch
@@ -43,35 +44,74 @@ class KeyedOptimizer(optim.Optimizer):
         self.state = state
         self.param_groups = param_groups
         self.params = params
-        self.defaults: Dict[str, Any] = {}
-        flat = {id(p) for g in param_groups for p in g["params"]}
-        assert flat == {id(p) for p in params.values()}, "param_groups and params must hold the same tensors"
+        self.defaults: Dict[str, Any] = {"_save_param_groups": False}
+        ids = {id(p) for p in params.values()}
+        stray = [k for k in state if id(k) not in ids]
+        if stray:
+            raise ValueError(f"All state keys must be params. The following keys are not: {stray}.")
 
     def state_dict(self) -> Dict[str, Any]:
+        """Flat `{"state": {<param key>: {...}}}` keyed by parameter name; `param_groups` only after
+        save_param_groups(True) (reference :66-98)."""
         name_of = {id(p): n for n, p in self.params.items()}
-        groups = []
-        for g in self.param_groups:
-            d = {k: v for k, v in g.items() if k != "params"}
-            d["params"] = sorted(name_of[id(p)] for p in g["params"])
-            groups.append(d)
-        state = {name_of[id(p)]: s for p, s in self.state.items() if id(p) in name_of}
-        return {"state": state, "param_groups": groups}
+        ret: Dict[str, Any] = {"state": {name_of[id(p)]: s for p, s in self.state.items()}}
+        if self.defaults.get("_save_param_groups", False):
+            groups = []
+            for g in self.param_groups:
+                d = {"params": sorted(name_of[id(p)] for p in g["params"])}
+                d.update({k: copy.deepcopy(v) for k, v in g.items() if k != "params"})
+                groups.append(d)
+            ret["param_groups"] = groups
+        return ret
+
+    def post_load_state_dict(self) -> None:
+        pass
 
     def load_state_dict(self, state_dict: Mapping[str, Any]) -> None:
+        """Strict in-place load (reference :103-196): the same parameters, the same state keys per
+        parameter; tensors are copied into the live state (ShardedTensors shard by shard)."""
         new_state = state_dict["state"]
-        for name, p in self.params.items():
-            if name not in new_state or p not in self.state:
+        state, params = self.state, self.params
+        if len(state) != len(new_state):
+            raise ValueError(f"Different parameter count: {len(state)} vs {len(new_state)}")
+        for name, p in params.items():
+            if p not in state:
                 continue
-            for k, v in new_state[name].items():
-                cur = self.state[p].get(k)
-                if isinstance(cur, torch.Tensor) and isinstance(v, torch.Tensor):
+            if name not in new_state:
+                raise ValueError(f"Parameter {name} not found")
+            if len(state[p]) != len(new_state[name]):
+                raise ValueError(f"Different state size: {len(state[p])} vs {len(new_state[name])}")
+            for k, cur in state[p].items():
+                if k not in new_state[name]:
+                    raise ValueError(f"State key {k} not found for param {name}")
+                v = new_state[name][k]
+                if isinstance(cur, torch.Tensor):
+                    assert isinstance(v, torch.Tensor), f"{name}/{k}: tensor state loaded from {type(v)}"
                     _copy_state(cur, v)
                 else:
-                    self.state[p][k] = v
-        for g, ng in zip(self.param_groups, state_dict["param_groups"]):
-            for k, v in ng.items():
-                if k != "params":
-                    g[k] = v
+                    state[p][k] = copy.deepcopy(v)
+        if self.defaults.get("_save_param_groups", False):
+            new_groups = state_dict["param_groups"]
+            if len(self.param_groups) != len(new_groups):
+                raise ValueError(f"Different param_groups count: {len(self.param_groups)} vs {len(new_groups)}")
+            name_of = {id(p): n for n, p in params.items()}
+            mine = {"/".join(sorted(name_of[id(p)] for p in g["params"])): g for g in self.param_groups}
+            theirs = {"/".join(sorted(g["params"])): g for g in new_groups}
+            for key, g in mine.items():
+                if key not in theirs:
+                    raise ValueError(f"Group {key} not found")
+                ng = theirs[key]
+                if len(g) != len(ng):
+                    raise ValueError(f"Different param_group size: {len(g)} vs {len(ng)}")
+                for k in g:
+                    if k not in ng:
+                        raise ValueError(f"Group key {k} not found for group {key}")
+                    if k != "params":
+                        g[k] = copy.deepcopy(ng[k])
+        self.post_load_state_dict()
+
+    def save_param_groups(self, save: bool) -> None:
+        self.defaults["_save_param_groups"] = save
 
     def add_param_group(self, param_group: Any) -> None:
         raise NotImplementedError()
@@ -92,7 +132,8 @@ class CombinedOptimizer(KeyedOptimizer):
             self._optims.append(o if isinstance(o, tuple) else ("", o))
         self._optimizer_step_pre_hooks = {}
         self._optimizer_step_post_hooks = {}
-        self.defaults = {}
+        self.defaults = {"_save_param_groups": self._optims[0][1].defaults.get("_save_param_groups", False)
+                         if self._optims else False}
         seen = set()
         for key, o in self._optims:
             for n in o.params:
@@ -132,12 +173,14 @@ class CombinedOptimizer(KeyedOptimizer):
         for _, o in self._optims:
             o.step(closure=closure)
 
-    def state_dict(self) -> Dict[str, Any]:
-        return {"optimizers": {k: o.state_dict() for k, o in self._optims}}
+    def post_load_state_dict(self) -> None:
+        for _, o in self._optims:
+            o.post_load_state_dict()
 
-    def load_state_dict(self, state_dict: Mapping[str, Any]) -> None:
-        for k, o in self._optims:
-            o.load_state_dict(state_dict["optimizers"][k])
+    def save_param_groups(self, save: bool) -> None:
+        self.defaults["_save_param_groups"] = save
+        for _, o in self._optims:
+            o.save_param_groups(save)
 
 
 class KeyedOptimizerWrapper(KeyedOptimizer):

@@ -127,3 +127,31 @@ def ref_rowwise_adagrad(w, g, h, indices, eps, lr):
                               _ptr(gg, C.c_float), _ptr(h, C.c_float), _ptr(idx, C.c_int64), C.c_float(eps),
                               C.c_float(lr))
     assert n == len(idx)
+
+
+QUANT_REF_LIB = os.path.join(HERE, "_ref", "libfbgemm_quant_ref.so")
+_quant = None
+
+
+def quant_ref_lib():
+    """The reference's own QuantUtils.cc (oracle/quant_shim.cc), or None when oracle/_ref was not built."""
+    global _quant
+    if _quant is None and os.path.exists(QUANT_REF_LIB):
+        _quant = C.CDLL(QUANT_REF_LIB)
+        for f in (_quant.ref_quantize_sbhalf_ref, _quant.ref_quantize_sbhalf):
+            f.restype = None
+            f.argtypes = [C.c_int, C.POINTER(C.c_float), C.c_size_t, C.c_int, C.POINTER(C.c_uint8)]
+    return _quant
+
+
+def ref_quantize_sbhalf(w, bit_rate=8, dispatch=False):
+    """[rows, cols] fp32 -> [rows, cols + 4] uint8 ([q...][fp16 scale][fp16 bias]) by the reference's
+    FloatOrHalfToFusedNBitRowwiseQuantizedSBHalfRef (dispatch=False) or by the dispatcher its torch op calls
+    (dispatch=True: the AVX2 kernel on an AVX2 host)."""
+    q = quant_ref_lib()
+    x = _c(w, np.float32)
+    rows, cols = x.shape
+    out = np.zeros((rows, cols * bit_rate // 8 + 4), dtype=np.uint8)
+    (q.ref_quantize_sbhalf if dispatch else q.ref_quantize_sbhalf_ref)(
+        bit_rate, _ptr(x, C.c_float), rows, cols, _ptr(out, C.c_uint8))
+    return out

@@ -176,6 +176,16 @@ def test_grad_indice_weights(ops):
     np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
 
 
+def test_quantize_matches_reference_fixture(ops):
+    """b200_quantize_rowwise_8bit_sbhalf vs bytes produced by the reference's own compiled QuantUtils.cc
+    (tests/golden/quantize_sbhalf.npz): bit-exact, including constant / zero / fp16-overflowing rows."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quantize_sbhalf.npz"))
+    for n in sorted({k.split(".")[0] for k in g.files}):
+        got = ops.quantize_rowwise_8bit_sbhalf(dev(g[n + ".w"])).cpu().numpy()
+        np.testing.assert_array_equal(got, g[n + ".q"], err_msg=n)
+
+
 @pytest.mark.parametrize("D", [4, 32, 128, 252, 1024])
 def test_quantize_and_int8_forward(ops, D):
     rng = np.random.default_rng(D)
@@ -221,8 +231,9 @@ def test_int8_forward_large_batch(ops):
 
 
 def test_interaction_golden(ops):
-    # torchrec/models/tests/test_dlrm.py:247-327 — same seed and call order as the reference test
-    D, B, F = 3, 2, 2  # placeholder replaced by tests/golden fixture when present
+    # torchrec/models/tests/test_dlrm.py:247-327 - same seed and call order as the reference test, the whole
+    # 3 x 14 expected tensor at the reference's tolerance, plus the bmm/triu formulation at rtol 1e-5
+    from golden_cases import INTERACTION_GOLDEN
     torch.manual_seed(0)
     dense = torch.rand(3, 4)
     sparse = torch.rand(3, 4, 4)
@@ -232,7 +243,45 @@ def test_interaction_golden(ops):
     iu = torch.triu_indices(5, 5, offset=1)
     exp = torch.cat([dense, Z[:, iu[0], iu[1]]], dim=1)
     torch.testing.assert_close(out, exp, rtol=1e-5, atol=1e-6)
-    assert abs(float(out[0, 0]) - 0.4963) < 1e-4  # first element of the reference's expected tensor
+    torch.testing.assert_close(out, torch.tensor(INTERACTION_GOLDEN), rtol=1e-4, atol=1e-4)
+
+
+def test_interaction_grad_sink_is_private_to_its_source(ops):
+    """A registered gradient sink (the peer exchange's symmetric buffer) receives the gradient of ITS forward
+    output only: another [B, F, D] input of the same size - a second InteractionArch, an unsharded parity model,
+    a leaf - gets a fresh tensor, and two consumers of one tensor sum to g1 + g2, not 2 * g2."""
+    B, F, D = 64, 4, 32
+    g = torch.Generator(device="cuda").manual_seed(3)
+    dense = torch.randn(B, D, device="cuda", generator=g)
+    src = torch.randn(B, F * D, device="cuda", generator=g)       # stands for PeerExchange.out
+    buf = torch.full((B, F * D), float("nan"), device="cuda")     # stands for PeerExchange.grad
+    sink = ops.register_grad_sink(buf, None, None, src)
+    try:
+        other = torch.randn(B, F, D, device="cuda", generator=g)  # same numel, another tensor
+        go = torch.randn(B, D + (F + 1) * F // 2, device="cuda", generator=g)
+        _gd, gs = ops.interaction_backward(dense, other, go)
+        assert gs.data_ptr() != buf.data_ptr() and bool(torch.isnan(buf).all())
+        _gd2, gs2 = ops.interaction_backward(dense, src.view(B, F, D), go)
+        assert gs2.data_ptr() == buf.data_ptr() and not bool(torch.isnan(buf).any())
+        # two InteractionArch consumers of a leaf: autograd must see two distinct gradient tensors
+        from torchrec.models.dlrm import InteractionArch
+        leaf = other.clone().requires_grad_(True)
+        d1 = dense.clone().requires_grad_(True)
+        ia = InteractionArch(F)
+        (ia(d1, leaf).sum() + 2.0 * ia(d1 * 0.5, leaf).sum()).backward()
+        ref = other.clone().requires_grad_(True)
+        d2 = dense.clone().requires_grad_(True)
+
+        def torch_ia(dd, ss):
+            X = torch.cat([dd.unsqueeze(1), ss], dim=1)
+            Z = torch.bmm(X, X.transpose(1, 2))
+            iu = torch.triu_indices(F + 1, F + 1, offset=1, device="cuda")
+            return torch.cat([dd, Z[:, iu[0], iu[1]]], dim=1)
+        (torch_ia(d2, ref).sum() + 2.0 * torch_ia(d2 * 0.5, ref).sum()).backward()
+        torch.testing.assert_close(leaf.grad, ref.grad, rtol=1e-5, atol=1e-4)
+        torch.testing.assert_close(d1.grad, d2.grad, rtol=1e-5, atol=1e-4)
+    finally:
+        ops.unregister_grad_sink(sink)
 
 
 @pytest.mark.parametrize("B,F,D", [(3, 4, 4), (65, 26, 128), (130, 8, 64), (7, 1, 16), (3001, 26, 128), (1250, 31, 64), (200, 15, 192),

@@ -59,15 +59,17 @@ def test_bucketize_block_vectors():
 
 
 def test_interaction_reference_golden():
-    # torchrec/models/tests/test_dlrm.py:247-327: seed 0, B=3, D=4, F=4, first row of the expected tensor
+    # torchrec/models/tests/test_dlrm.py:247-327: seed 0, B=3, D=4, F=4, the reference's whole expected tensor
+    # at the reference's own tolerance (rtol = atol = 1e-4, :312-319)
+    from golden_cases import INTERACTION_GOLDEN
     torch.manual_seed(0)
     dense, sparse = torch.rand((3, 4)), torch.rand((3, 4, 4))
+    exp = np.array(INTERACTION_GOLDEN, dtype=np.float32)
     out = R.interaction_forward(dense.numpy(), sparse.numpy())
-    exp_row0 = [0.4963, 0.7682, 0.0885, 0.1320, 0.2353, 1.0123, 0.5218, 0.5256, 0.4712, 0.5993, 0.4194,
-                0.9446, 1.0521, 1.0559]
     assert out.shape == (3, 14)
-    np.testing.assert_allclose(out[0, :4], exp_row0[:4], atol=1e-4)
-    np.testing.assert_allclose(out[0], c_oracle.interaction_forward(dense.numpy(), sparse.numpy())[0], rtol=1e-5)
+    np.testing.assert_allclose(out, exp, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(c_oracle.interaction_forward(dense.numpy(), sparse.numpy()), exp, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(out, c_oracle.interaction_forward(dense.numpy(), sparse.numpy()), rtol=1e-5)
 
 
 def _tables(rng, rows, dims):
@@ -130,6 +132,29 @@ def test_int8_forward_and_quantize_vs_reference_code():
     deq = q[:, :D].astype(np.float32) * np.frombuffer(q[:, D:D + 2].tobytes(), np.float16).astype(np.float32)[:, None] \
         + np.frombuffer(q[:, D + 2:].tobytes(), np.float16).astype(np.float32)[:, None]
     assert np.abs(deq - wf).max() <= (wf.max(1) - wf.min(1)).max() / 255 * 0.51 + 2e-3
+
+
+def test_quantizer_oracle_matches_reference_fixture():
+    """a17 pinned: the numpy restatement reproduces, bit for bit, what the reference's own compiled
+    QuantUtils.cc produced (tests/golden/quantize_sbhalf.npz, tests/golden/make_golden_quant.py) - constant
+    rows, all-zero rows, fp16-overflowing rows and exact ties included."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quantize_sbhalf.npz"))
+    names = sorted({k.split(".")[0] for k in g.files})
+    assert len(names) == 5
+    for n in names:
+        np.testing.assert_array_equal(R.quantize_rowwise_8bit_sbhalf(g[n + ".w"]), g[n + ".q"], err_msg=n)
+
+
+@pytest.mark.skipif(c_oracle.quant_ref_lib() is None, reason="oracle/_ref not built (no reference checkout)")
+def test_quantizer_oracle_vs_reference_code():
+    """Random shapes against the reference's scalar definition AND the dispatcher its torch op calls."""
+    rng = np.random.default_rng(5)
+    for rows, cols in ((200, 128), (31, 64), (7, 20), (64, 256), (3, 1)):
+        w = (rng.standard_normal((rows, cols)) * rng.uniform(1e-3, 1e3)).astype(np.float32)
+        mine = R.quantize_rowwise_8bit_sbhalf(w)
+        np.testing.assert_array_equal(mine, c_oracle.ref_quantize_sbhalf(w, dispatch=False))
+        np.testing.assert_array_equal(mine, c_oracle.ref_quantize_sbhalf(w, dispatch=True))
 
 
 @pytest.mark.parametrize("opt", ["sgd", "rowwise_adagrad"])

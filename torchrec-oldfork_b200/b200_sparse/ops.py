@@ -527,7 +527,17 @@ def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: boo
 # keeps the pooled-embedding gradient in symmetric memory so that other ranks can read it) registers
 # that buffer here; interaction_backward then writes grad_sparse straight into it instead of a fresh
 # tensor, which saves the consumer a [B, F*D] copy per step.
+# Keyed by (device, data_ptr of the consumer's forward output): only the backward of THAT tensor writes
+# into the sink; any other [B, F*D] input - a second InteractionArch, an unsharded parity model, a leaf in a
+# unit test - gets a fresh gradient tensor.
 _GRAD_SINKS: Dict[Tuple[int, int], "GradSink"] = {}
+
+
+def interaction_supported(F: int, D: int) -> bool:
+    """True when b200_interaction_forward/backward cover the shape (csrc/interaction.cu: D % 4 == 0 and
+    the general kernel's 4-sample shared-memory tile fits); callers route other shapes to plain torch."""
+    n = F + 1
+    return D > 0 and D % 4 == 0 and 16 * ((n * (D + 4) + n * (n + 1) + 3) & ~3) <= 200 * 1024
 
 
 class GradSink:
@@ -542,14 +552,25 @@ class GradSink:
         # scatter only the gradient of THIS tensor (the consumer's forward output, features in the
         # order of feat_base): any other [B, F*D] input of the same size keeps the dense layout
         self.src_ptr = src.data_ptr() if src is not None else None
+        self.numel = src.numel() if src is not None else buf.numel()
         self.scattered = False
+        self.key: Optional[Tuple[int, int]] = None
 
 
 def register_grad_sink(buf: torch.Tensor, feat_base: Optional[torch.Tensor] = None,
                        feat_pitch: Optional[torch.Tensor] = None, src: Optional[torch.Tensor] = None) -> GradSink:
+    """src: the tensor whose gradient the sink receives (the consumer's persistent forward output)."""
+    if src is None:
+        raise ValueError("register_grad_sink needs the forward output whose gradient goes to the sink")
     sink = GradSink(buf, feat_base, feat_pitch, src)
-    _GRAD_SINKS[(buf.device.index, buf.numel())] = sink
+    sink.key = (buf.device.index, src.data_ptr())
+    _GRAD_SINKS[sink.key] = sink
     return sink
+
+
+def unregister_grad_sink(sink: GradSink) -> None:
+    if sink.key is not None and _GRAD_SINKS.get(sink.key) is sink:
+        del _GRAD_SINKS[sink.key]
 
 
 def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
@@ -561,20 +582,22 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     if grad_out.dim() != 2 or grad_out.stride(1) != 1 or grad_out.stride(0) < grad_out.shape[1]:
         grad_out = grad_out.contiguous()  # a row-pitched view is consumed in place
     gd = torch.empty_like(dense)
-    sink = _GRAD_SINKS.get((dev.index, sparse.numel()))
-    if sink is not None and sink.buf.dtype != sparse.dtype:
+    sink = _GRAD_SINKS.get((dev.index, sparse.data_ptr()))
+    if sink is not None and (sink.buf.dtype != sparse.dtype or sink.numel != sparse.numel()):
         sink = None
     gs = sink.buf.view(sparse.shape) if sink is not None else torch.empty_like(sparse)
     with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
         if sink is not None:
             sink.scattered = False
-            if (sink.feat_base is not None and sink.feat_base.numel() == F and F + 1 <= 32 and D % 32 == 0
-                    and sparse.data_ptr() == sink.src_ptr):
-                check(lib.b200_interaction_backward_scatter(
+            if sink.feat_base is not None and sink.feat_base.numel() == F and F + 1 <= 32 and D % 32 == 0:
+                rc = lib.b200_interaction_backward_scatter(
                     _p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D, _p(gd),
-                    _p(sink.feat_base), _p(sink.feat_pitch), _stream(dev)), "b200_interaction_backward_scatter")
-                sink.scattered = True
-                return gd, gs
+                    _p(sink.feat_base), _p(sink.feat_pitch), _stream(dev))
+                if rc == 0:
+                    sink.scattered = True
+                    return gd, gs
+                if rc != -2:  # B200_EUNSUPPORTED: the dense layout below; anything else is an error
+                    check(rc, "b200_interaction_backward_scatter")
         check(lib.b200_interaction_backward(_p(dense), _p(sparse), _p(grad_out), grad_out.stride(0), B, F, D,
                                             _p(gd), _p(gs), _stream(dev)), "b200_interaction_backward")
     return gd, gs

@@ -110,6 +110,18 @@ class PeerExchange:
         # True after a backward pass: its barrier C already proves that every rank is done with the
         # buffers of that step, so the next forward may skip barrier A (see _PeerLookup.forward)
         self.quiesced = False
+        # Aliasing contract: `out` is ONE persistent buffer that the lookup kernels of every rank rewrite
+        # through raw pointers (no autograd version bump).  A training forward therefore hands out a view of
+        # it that stays valid until that step's backward has run; `outstanding` marks the window, and a
+        # second forward inside it is refused instead of silently overwriting saved activations.
+        # Forwards without autograd (evaluation) return a private copy.
+        self.outstanding = False
+
+    def __del__(self) -> None:
+        try:
+            _b200.unregister_grad_sink(self.sink)
+        except Exception:
+            pass
 
     def barrier(self) -> None:
         self._h_out.barrier()
@@ -169,6 +181,8 @@ class PeerLookupDist:
                 raise NotImplementedError("weighted features take the NCCL path")
             if any(getattr(m.emb_module, "_sr_on", False) for m in mods):
                 raise NotImplementedError("stochastic rounding of fp16/bf16 tables takes the NCCL path")
+            if any(m.emb_module.optimizer_args.gradient_clipping for m in mods):
+                raise NotImplementedError("gradient clipping takes the NCCL path")
             parts: List[_Part] = []
             if isinstance(sharding, BaseTwEmbeddingSharding):
                 # every rank's table-wise features, in that rank's module order: the layout of its gin
@@ -249,6 +263,12 @@ class _PeerLookup(torch.autograd.Function):
         from fbgemm_gpu import _tbe_autograd as ta
         need_grad = any(ctx.needs_input_grad[3:])
         ctx.n_placeholders = len(placeholders)
+        if px.outstanding and os.environ.get("B200_PEER_ALLOW_REENTRY", "0") != "1":
+            raise RuntimeError(
+                "peer-memory embedding lookup re-entered before the backward of its previous training forward: "
+                "the pooled output lives in one persistent symmetric buffer that this call would overwrite "
+                "(see PeerExchange.outstanding). Run backward first, call the module under torch.no_grad() for "
+                "evaluation, or set B200_PEER_DIST=0 to use the NCCL path, which returns fresh tensors.")
         main = torch.cuda.current_stream(px.out.device)
         sorts = []
         for p, idx, off in work:
@@ -290,12 +310,16 @@ class _PeerLookup(torch.autograd.Function):
             _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4,
                                     clear_stage=True)
         ctx.px, ctx.work, ctx.sorts = px, work, sorts
+        if not need_grad:
+            return px.out.clone()  # evaluation: the caller may keep it across further forwards
+        px.outstanding = True
         return px.out
 
     @staticmethod
     def backward(ctx, grad_out):
         from fbgemm_gpu import _tbe_autograd as ta
         px = ctx.px
+        px.outstanding = False
         pushed = px.sink.scattered
         px.sink.scattered = False
         if grad_out.data_ptr() != px.grad.data_ptr() or not grad_out.is_contiguous():
@@ -314,8 +338,7 @@ class _PeerLookup(torch.autograd.Function):
                 continue
             m = p.tbe
             a = m.optimizer_args
-            if a.gradient_clipping:
-                raise NotImplementedError("gradient clipping with the peer path")
+            assert not a.gradient_clipping  # refused at build time (PeerLookupDist.__init__)
             if ev is not None:
                 torch.cuda.current_stream(idx.device).wait_event(ev)
             keys, payload, _bag = s

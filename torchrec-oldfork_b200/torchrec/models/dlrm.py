@@ -90,9 +90,10 @@ class InteractionArch(nn.Module):
     def forward(self, dense_features: torch.Tensor, sparse_features: torch.Tensor) -> torch.Tensor:
         if self.F <= 0:
             return dense_features
-        if dense_features.is_cuda and dense_features.shape[1] % 4 == 0:
+        if dense_features.is_cuda and _b200.interaction_supported(self.F, dense_features.shape[1]):
             return mark_zero_padded(_DotInteraction.apply(dense_features, sparse_features))
-        # shapes the kernel does not cover (D % 4 != 0): reference formulation in plain torch
+        # shapes the kernels do not cover (D % 4 != 0, or F * D beyond the shared-memory tile): the reference
+        # formulation in plain torch
         combined = torch.cat((dense_features.unsqueeze(1), sparse_features), dim=1)
         inter = torch.bmm(combined, combined.transpose(1, 2))
         flat = inter[:, self.triu_indices[0], self.triu_indices[1]]

@@ -34,7 +34,8 @@ enum {
 enum {
   B200_OK = 0,
   B200_EINVAL = -1,      /* bad argument combination */
-  B200_EUNSUPPORTED = -2 /* valid in the reference, not built here */
+  B200_EUNSUPPORTED = -2, /* valid in the reference, not built here */
+  B200_ETOOBIG = -3       /* the problem needs more scratch than a fixed-size entry point owns */
 };
 
 enum { B200_POOL_SUM = 0, B200_POOL_MEAN = 1 };
@@ -149,6 +150,29 @@ int b200_tbe_backward(const float* grad_output, int64_t grad_stride, const void*
                       const float* per_sample_weights, int pooling_mode, int optimizer,
                       float* momentum1, const int64_t* momentum1_offsets, float learning_rate,
                       float eps, void* partial_scratch, void* stream);
+
+/* b200_tbe_backward without a scratch argument, for callers that cannot allocate (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch is a file-scope `static __device__` array of
+ * b200_tbe_backward_static_max_scratch_bytes() = 16 MiB inside the library (every GPU that loads the
+ * library holds it until the process exits); its device address is looked up once per device with
+ * cudaGetSymbolAddress, with the CALLER'S CURRENT DEVICE (which must be the device of `stream` and of
+ * every pointer).  The call makes no cudaMalloc / cudaFree / allocating library call.  Problems with
+ * b200_tbe_backward_scratch_bytes(N, max_D) above the limit return B200_ETOOBIG (cfg2 - 1,703,936 ids,
+ * dim 128 - needs 13.8 MiB and fits).  All calls on one GPU share the array: nothing in it has to start
+ * at zero (each call overwrites what it reads), but two calls that overlap on the GPU (different
+ * streams, or graph branches) race - serialise them or give one of them b200_tbe_backward with its
+ * own scratch.  Arguments and results are otherwise those of b200_tbe_backward. */
+size_t b200_tbe_backward_static_max_scratch_bytes(void);
+int b200_tbe_backward_static(const float* grad_output, int64_t grad_stride, const void* sorted_keys,
+                             const int32_t* sorted_payload, const int32_t* bag_of_pos, int64_t N,
+                             int key_bits, void* weights, int weight_dtype,
+                             const int64_t* weights_offsets, const int32_t* D_offsets,
+                             const int64_t* hash_size_cumsum, int32_t T, int32_t B, int32_t max_D,
+                             int32_t all_D_mult8, const void* offsets, int index_dtype,
+                             const float* per_sample_weights, int pooling_mode, int optimizer,
+                             float* momentum1, const int64_t* momentum1_offsets,
+                             float learning_rate, float eps, void* stream);
 
 /* b200_tbe_backward with stochastic rounding of the updated fp16 / bf16 rows (the reference's
  * `stochastic_rounding` optimizer argument, default true: embedding_backward_split_template.cu:367-

@@ -48,6 +48,9 @@ SIGNATURES = {
     "b200_tbe_backward_scratch_bytes": (_sz, [_i64, _i32]),
     "b200_tbe_backward": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _p, _int, _p, _p, _p, _i32, _i32,
                                  _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32, _p, _p]),
+    "b200_tbe_backward_static_max_scratch_bytes": (_sz, []),
+    "b200_tbe_backward_static": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _p, _int, _p, _p, _p, _i32, _i32,
+                                        _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32, _p]),
     "b200_tbe_backward_sr": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _p, _int, _p, _p, _p, _i32, _i32,
                                     _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32, _p,
                                     C.c_uint64, C.c_uint64, _p]),

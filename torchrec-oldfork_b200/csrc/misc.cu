@@ -124,6 +124,9 @@ extern "C" const char* b200_error_string(int code) {
       return "b200: invalid argument";
     case B200_EUNSUPPORTED:
       return "b200: configuration not supported by this build (see DESIGN.md)";
+    case B200_ETOOBIG:
+      return "b200: problem needs more scratch than this fixed-scratch entry point owns (use the variant "
+             "that takes a scratch pointer)";
     default:
       return code > 0 ? cudaGetErrorString((cudaError_t)code) : "b200: unknown error";
   }

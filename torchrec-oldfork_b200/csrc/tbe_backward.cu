@@ -20,6 +20,7 @@
 //  3. runs that straddle warps are stitched through shared memory in fixed order; runs that
 //     straddle CTAs leave one partial row per CTA in scratch and a small second kernel
 //     finishes them, again in fixed order.
+#include <mutex>
 #include <cub/device/device_radix_sort.cuh>
 
 #include <cstdlib>
@@ -1134,6 +1135,65 @@ extern "C" int b200_tbe_backward_sr(const float* grad_output, int64_t grad_strid
                            per_sample_weights, pooling_mode, optimizer, momentum1,
                            momentum1_offsets, learning_rate, eps, partial_scratch, nullptr, 0,
                            nullptr, 1.0f, 1, sr_seed, sr_offset, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// b200_tbe_backward_static: b200_tbe_backward for callers that cannot allocate (CUDA-graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  The per-CTA partial rows + run records that
+// b200_tbe_backward takes as `partial_scratch` live in this file-scope device array instead.  Every
+// GPU that loads the library holds kStaticScratchBytes of it until the process exits.
+namespace b200 {
+constexpr size_t kStaticScratchBytes = (size_t)16 << 20;  // 16 MiB: cfg2 (N = 1,703,936 ids, dim 128) needs 13.8 MiB
+static __device__ __align__(256) unsigned char g_bwd_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+static void* g_bwd_static_ptr[kMaxDevices];  // device address of the array on device i (0 = not looked up yet)
+static std::mutex g_bwd_static_mu;
+
+// In host code `g_bwd_static_scratch` is only a handle: the device address must come from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return B200_EUNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_bwd_static_mu);
+  if (!g_bwd_static_ptr[dev]) {
+    void* p = nullptr;
+    B200_CUDA_TRY(cudaGetSymbolAddress(&p, g_bwd_static_scratch));
+    if (!p) return B200_EINVAL;
+    g_bwd_static_ptr[dev] = p;
+  }
+  *out = g_bwd_static_ptr[dev];
+  return B200_OK;
+}
+}  // namespace b200
+
+extern "C" size_t b200_tbe_backward_static_max_scratch_bytes(void) { return b200::kStaticScratchBytes; }
+
+extern "C" int b200_tbe_backward_static(const float* grad_output, int64_t grad_stride,
+                                        const void* sorted_keys, const int32_t* sorted_payload,
+                                        const int32_t* bag_of_pos, int64_t N, int key_bits,
+                                        void* weights, int weight_dtype,
+                                        const int64_t* weights_offsets, const int32_t* D_offsets,
+                                        const int64_t* hash_size_cumsum, int32_t T, int32_t B,
+                                        int32_t max_D, int32_t all_D_mult8, const void* offsets,
+                                        int index_dtype, const float* per_sample_weights,
+                                        int pooling_mode, int optimizer, float* momentum1,
+                                        const int64_t* momentum1_offsets, float learning_rate,
+                                        float eps, void* stream) {
+  using namespace b200;
+  if (!grad_output || N < 0 || max_D <= 0) return B200_EINVAL;
+  if (b200_tbe_backward_scratch_bytes(N, max_D) > kStaticScratchBytes) return B200_ETOOBIG;
+  void* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != B200_OK) return rc;
+  // Nothing in the scratch has to start at zero: every CTA writes its partial rows and its run record
+  // before the combine kernel (same stream) reads them, so the previous call's contents are dead.
+  return tbe_backward_impl(grad_output, grad_stride, sorted_keys, sorted_payload, bag_of_pos, N,
+                           key_bits, weights, weight_dtype, weights_offsets, D_offsets,
+                           hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
+                           per_sample_weights, pooling_mode, optimizer, momentum1,
+                           momentum1_offsets, learning_rate, eps, scratch, nullptr, 0, nullptr,
+                           1.0f, 0, 0, 0, stream);
 }
 
 extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_src, int32_t B_src,

@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--cpu-batch", type=int, default=8192, help="batch of the bounded CPU sample")
     ap.add_argument("--cpu-row-cap", type=int, default=1000000, help="row cap of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cuda-graph", type=int, default=int(os.environ.get("B200_CUDA_GRAPH", "0")),
+                    help="replay the steady-state step as a CUDA graph (TrainPipelineSparseDist(cuda_graph=True))")
     return ap.parse_args()
 
 
@@ -295,7 +297,7 @@ def run_ours(args) -> None:
     # H2D of batch i+2 | sparse input dist of batch i+1 | forward/backward/optimizer of batch i.
     import itertools
     from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
-    pipe = TrainPipelineSparseDist(dmp, dense_opt, dev)
+    pipe = TrainPipelineSparseDist(dmp, dense_opt, dev, cuda_graph=bool(args.cuda_graph))
 
     def timed(fn, steps):
         dist.barrier()
@@ -313,7 +315,7 @@ def run_ours(args) -> None:
 
     shapes = lookup_shapes(dmp, dev_batches[0])  # runs the input collectives: every rank must call it
     dev_iter = itertools.cycle(dev_batches)
-    for i in range(max(args.warmup, 3)):
+    for i in range(max(args.warmup, 3) + (14 if args.cuda_graph else 0)):  # graph mode: 11 eager steps + capture
         pipe.progress(dev_iter)
     torch.cuda.synchronize()
 

@@ -123,12 +123,14 @@ int b200_tbe_forward(const void* weights, int weight_dtype, const int64_t* weigh
                      const void* offsets, int index_dtype, const float* per_sample_weights,
                      int pooling_mode, void* output, int output_dtype, void* stream);
 
-/* transpose_embedding_input (fbgemm_gpu/src/split_embeddings_utils.cu:63-306): linearise
- * (table,row) keys and sort them stably.  sorted_keys holds uint32 keys when key_bits <= 32,
- * else uint64.  sorted_payload holds b_t = t*B+b, or the original position p when
- * payload_is_position != 0 (weighted lookups); bag_of_pos (int32[N], may be NULL unless
- * payload_is_position) receives b_t per position.  sort_ws/sort_ws_bytes from the query. */
-size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits);
+/* transpose_embedding_input (fbgemm_gpu/src/split_embeddings_utils.cu:63-306: linearize_index_kernel,
+ * radix_sort_pairs :276-306): linearise (table,row) keys and sort them stably - hand-written segmented LSD
+ * radix sort (csrc/tbe_sort.cu), one segment per table, 9-bit digits, passes = ceil(log2(rows_t) / 9) per
+ * table.  sorted_keys holds uint32 keys when key_bits <= 32, else uint64.  sorted_payload holds
+ * b_t = t*B+b, or the original position p when payload_is_position != 0 (weighted lookups); bag_of_pos
+ * (int32[N], may be NULL unless payload_is_position) receives b_t per position.  Equal keys keep position
+ * order (== a stable argsort, bit for bit).  sort_ws: b200_tbe_sort_workspace_bytes(N, key_bits, T) bytes. */
+size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits, int32_t T);
 int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
                           const int64_t* hash_size_cumsum, int32_t T, int32_t B, int64_t N,
                           int key_bits, int payload_is_position, void* sorted_keys,

@@ -51,10 +51,10 @@ def test_host_only_entry_points():
     """The three entry points that touch no device are callable on CPU."""
     from b200_sparse import cabi
     lib = cabi.load()
-    assert lib.b200_abi_version() == 4
+    assert lib.b200_abi_version() == 5
     assert lib.b200_scan_workspace_bytes() > 0
     assert lib.b200_error_string(-1) and lib.b200_error_string(-1) != lib.b200_error_string(0)
-    assert lib.b200_tbe_sort_workspace_bytes(1 << 20, 32) > 0
+    assert lib.b200_tbe_sort_workspace_bytes(1 << 20, 32, 26) > 0
     assert lib.b200_tbe_backward_scratch_bytes(1 << 20, 128) > 0
 
 

@@ -331,9 +331,10 @@ def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cum
     keys = torch.empty(N, dtype=kdt, device=dev)
     payload = torch.empty(N, dtype=torch.int32, device=dev)
     bag_of_pos = torch.empty(N, dtype=torch.int32, device=dev) if weighted else None
-    ws_bytes = lib.b200_tbe_sort_workspace_bytes(N, key_bits)
+    ws_bytes = lib.b200_tbe_sort_workspace_bytes(N, key_bits, T)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev), _timed("tbe_sort", dev, 7):  # linearize + CUB histogram/scan/4 passes
+    n_pass = (key_bits + 8) // 9
+    with torch.cuda.device(dev), _timed("tbe_sort", dev, 2 + 3 * n_pass):  # plan, linearize, 3 kernels per pass
         check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
                                         key_bits, int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
                                         _p(ws), ws_bytes, _stream(dev)), "b200_tbe_sort_indices")

@@ -132,7 +132,7 @@ extern "C" const char* b200_error_string(int code) {
   }
 }
 
-extern "C" int b200_abi_version(void) { return 4; }
+extern "C" int b200_abi_version(void) { return 5; }
 
 extern "C" int b200_tbe_grad_indice_weights(const float* grad_output, int64_t grad_stride,
                                             const void* weights, int weight_dtype,

@@ -1,7 +1,6 @@
 // Fused backward + optimizer of the pooled lookup for sm_100a.
 //
-// Replaces transpose_embedding_input (fbgemm_gpu/src/split_embeddings_utils.cu:63-306) and
-// split_embedding_backward_codegen_<opt>_{un,}weighted_exact_cuda
+// Replaces split_embedding_backward_codegen_<opt>_{un,}weighted_exact_cuda
 // (fbgemm_gpu/codegen/embedding_backward_split_template.cu:81-1138) with the optimizer bodies
 // of embedding_backward_code_generator.py:376-401 (rowwise Adagrad) and :629-632 (SGD).
 //
@@ -10,8 +9,9 @@
 // deterministic (no float atomics; the per-row sum is taken in stable sorted order).
 //
 // Design (not the reference's warp-per-row / CTA-per-row split):
-//  1. linearise keys (table row-offset + id) and radix-sort (key, b_t) pairs once — the sort
-//     only depends on the ids, so the host layer issues it at forward time on a side stream.
+//  1. linearise keys (table row-offset + id) and sort (key, b_t) pairs once (csrc/tbe_sort.cu: a hand-written
+//     segmented LSD radix sort) — the sort only depends on the ids, so the host layer issues it at forward
+//     time on a side stream.
 //  2. ONE balanced pass over the sorted positions: each warp owns 32 consecutive sorted
 //     positions, keeps 4 gradient rows and the weight rows of the runs that end inside the
 //     batch in flight, sums runs in registers and applies the update as soon as a run ends.
@@ -21,7 +21,6 @@
 //     straddle CTAs leave one partial row per CTA in scratch and a small second kernel
 //     finishes them, again in fixed order.
 #include <mutex>
-#include <cub/device/device_radix_sort.cuh>
 
 #include <cstdlib>
 
@@ -29,91 +28,7 @@
 
 namespace b200 {
 
-// ------------------------------------------------------------------ linearise
-template <typename K>
-__global__ void __launch_bounds__(128)
-tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ offsets, bool idx64,
-                     const int64_t* __restrict__ hash_size_cumsum, int32_t T, int32_t B,
-                     int32_t tiles_per_table, bool payload_is_position, K* __restrict__ keys,
-                     int32_t* __restrict__ payload, int32_t* __restrict__ bag_of_pos) {
-  const int lane = threadIdx.x & 31;
-  const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (tile >= (int64_t)T * tiles_per_table) return;
-  const int t = (int)(tile / tiles_per_table);
-  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
-  const int nb = min(32, B - b0);
-  const int64_t obase = (int64_t)t * B + b0;
-  const int64_t my_start = load_index(offsets, obase + min(lane, nb), idx64);
-  const int64_t S0 = __shfl_sync(kFull, my_start, 0);
-  const int32_t rel_start = (int32_t)(my_start - S0);
-  int32_t rel_end = __shfl_down_sync(kFull, rel_start, 1);
-  if (lane == 31) rel_end = (int32_t)(load_index(offsets, obase + nb, idx64) - S0);
-  const int32_t len = __shfl_sync(kFull, rel_end, 31);
-  const int64_t hash_base = hash_size_cumsum[t];
-  const int32_t iters = (len + 31) / 32;
-  for (int32_t it = 0; it < iters; ++it) {
-    const int32_t p = it * 32 + lane;
-    // bag of position p = number of bags whose end is <= p (ends are sorted)
-    int j = 0;
-#pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      const int probe = j + step - 1;
-      const int32_t e = __shfl_sync(kFull, rel_end, probe);
-      if (e <= p) j += step;
-    }
-    if (p < len) {
-      const int64_t idx = load_index(indices, S0 + p, idx64);
-      const int32_t bt = (int32_t)(obase + j);
-      keys[S0 + p] = (K)(hash_base + idx);
-      payload[S0 + p] = payload_is_position ? (int32_t)(S0 + p) : bt;
-      if (bag_of_pos) bag_of_pos[S0 + p] = bt;
-    }
-  }
-}
-
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
-
-template <typename K>
-static size_t cub_sort_temp_bytes(int64_t N, int key_bits) {
-  size_t bytes = 0;
-  cub::DoubleBuffer<K> dk(nullptr, nullptr);
-  cub::DoubleBuffer<int32_t> dv(nullptr, nullptr);
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)N, 0, key_bits);
-  return bytes;
-}
-
-template <typename K>
-static int sort_impl(const void* indices, const void* offsets, bool idx64,
-                     const int64_t* hash_size_cumsum, int32_t T, int32_t B, int64_t N,
-                     int key_bits, bool payload_is_position, void* sorted_keys,
-                     int32_t* sorted_payload, int32_t* bag_of_pos, void* ws, size_t ws_bytes,
-                     cudaStream_t s) {
-  // ws = [alt keys | alt payload | cub temp]
-  char* p = (char*)ws;
-  K* keys_alt = (K*)p;
-  p += align256(sizeof(K) * (size_t)N);
-  int32_t* pay_alt = (int32_t*)p;
-  p += align256(sizeof(int32_t) * (size_t)N);
-  size_t temp_bytes = ws_bytes - (size_t)(p - (char*)ws);
-  const int tiles_per_table = (B + 31) / 32;
-  const int64_t tiles = (int64_t)T * tiles_per_table;
-  // linearise straight into the caller's output buffers, sort with a double buffer, and
-  // copy back only if CUB finished in the alternate one.
-  tbe_linearize_kernel<K><<<(unsigned)ceil_div(tiles, 4), 128, 0, s>>>(
-      indices, offsets, idx64, hash_size_cumsum, T, B, tiles_per_table, payload_is_position,
-      (K*)sorted_keys, sorted_payload, bag_of_pos);
-  B200_LAUNCH_CHECK();
-  cub::DoubleBuffer<K> dk((K*)sorted_keys, keys_alt);
-  cub::DoubleBuffer<int32_t> dv(sorted_payload, pay_alt);
-  B200_CUDA_TRY(cub::DeviceRadixSort::SortPairs(p, temp_bytes, dk, dv, (int)N, 0, key_bits, s));
-  if (dk.Current() != (K*)sorted_keys)
-    B200_CUDA_TRY(cudaMemcpyAsync(sorted_keys, dk.Current(), sizeof(K) * (size_t)N,
-                                  cudaMemcpyDeviceToDevice, s));
-  if (dv.Current() != sorted_payload)
-    B200_CUDA_TRY(cudaMemcpyAsync(sorted_payload, dv.Current(), sizeof(int32_t) * (size_t)N,
-                                  cudaMemcpyDeviceToDevice, s));
-  return B200_OK;
-}
 
 // ------------------------------------------------------------------ update
 constexpr int kBwdWarps = 8;
@@ -988,38 +903,6 @@ static inline size_t bwd_row_floats(int max_D) {
 }
 
 }  // namespace b200
-
-extern "C" size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits) {
-  using namespace b200;
-  if (N <= 0) return 256;
-  const bool k64 = key_bits > 32;
-  const size_t ksz = k64 ? 8 : 4;
-  size_t temp = k64 ? cub_sort_temp_bytes<uint64_t>(N, key_bits)
-                    : cub_sort_temp_bytes<uint32_t>(N, key_bits);
-  return align256(ksz * (size_t)N) + align256(4 * (size_t)N) + align256(temp) + 256;
-}
-
-extern "C" int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
-                                     const int64_t* hash_size_cumsum, int32_t T, int32_t B,
-                                     int64_t N, int key_bits, int payload_is_position,
-                                     void* sorted_keys, int32_t* sorted_payload,
-                                     int32_t* bag_of_pos, void* sort_ws, size_t sort_ws_bytes,
-                                     void* stream) {
-  using namespace b200;
-  if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
-  if (N >= 0x7fffffffLL || key_bits < 1 || key_bits > 64) return B200_EINVAL;
-  if (payload_is_position && !bag_of_pos) return B200_EINVAL;
-  if (N == 0 || T == 0 || B == 0) return B200_OK;
-  const bool idx64 = index_dtype == B200_I64;
-  cudaStream_t s = (cudaStream_t)stream;
-  if (key_bits > 32)
-    return sort_impl<uint64_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
-                               payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
-                               sort_ws, sort_ws_bytes, s);
-  return sort_impl<uint32_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
-                             payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
-                             sort_ws, sort_ws_bytes, s);
-}
 
 extern "C" size_t b200_tbe_backward_scratch_bytes(int64_t N, int32_t max_D) {
   using namespace b200;

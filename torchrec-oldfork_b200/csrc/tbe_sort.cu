@@ -1,0 +1,480 @@
+// Index transpose for the fused backward: linearise (table,row) keys and sort them stably.
+// Replaces the reference's transpose_embedding_input
+// (third_party/fbgemm/fbgemm_gpu/src/split_embeddings_utils.cu:63-306: linearize_index_kernel + CUB
+// radix_sort_pairs + RLE + scan) with a hand-written segmented LSD radix sort.
+//
+// What the key distribution gives us (and a general-purpose sort cannot use):
+//  * ids arrive table-major, so the positions of one table are already contiguous and tables are already in
+//    key order: the global sort is a set of INDEPENDENT per-table sorts whose output range equals the input
+//    range.  Features that share a table (equal hash base) form one segment.
+//  * a segment only needs ceil(log2(rows)) key bits: 9-bit digits give 1 pass for tables up to 512 rows,
+//    2 up to 262,144 rows, 3 up to 134 M rows (CUB over the 28-bit global key: 4 passes for every table).
+//    At the Criteo shape 9 of 26 tables finish after the first pass and 18 after the second.
+//  * every pass is the same three small kernels over all segments at once - tile histograms, a per-segment
+//    scan, a stable scatter - with segments that are done skipping the pass; buffers ping-pong so that each
+//    segment's LAST pass lands in the caller's output arrays (no copy-back).
+// If the hash bases are not non-decreasing over the features (a feature_table_map that is not grouped by
+// table) the plan falls back to ONE segment over the global key: still correct, just more passes.
+// Stability: LSD passes with a stable scatter (warp-private counters + match_any ranks), so equal keys keep
+// position order - bit-identical to a stable argsort, no atomics in the ordering.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "b200_sparse.h"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kSortDigitBits = 9;
+constexpr int kSortBins = 1 << kSortDigitBits;  // 512
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kSortChunk = 2048;       // positions ranked per CTA step (8 per thread)
+constexpr int kSortMaxPasses = 8;      // 64-bit keys / 9 bits
+
+static inline size_t sort_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+// positions per tile: a multiple of the chunk, at most ~512 tiles over all segments plus one per segment
+__host__ __device__ inline int64_t sort_tile_size(int64_t N) {
+  int64_t ts = ceil_div(ceil_div(N, 512), kSortChunk) * kSortChunk;
+  return ts < kSortChunk ? kSortChunk : ts;
+}
+
+// Device-resident plan built by sort_plan_kernel (arrays sized T + 1), passed by value to the kernels.
+struct SortPlanView {
+  int32_t* hdr;  // nseg, pass_active[8], total_tiles
+  int32_t* feat_seg;
+  int32_t* seg_feat0;
+  int64_t* seg_base;
+  int32_t* seg_passes;
+  int64_t* seg_p0;
+  int32_t* seg_tile0;
+};
+constexpr int kHdrNseg = 0, kHdrPass = 1, kHdrTiles = 1 + kSortMaxPasses;
+
+// ------------------------------------------------------------------------------------ plan
+// One CTA.  Segments = maximal runs of features with the same hash base.
+__global__ void __launch_bounds__(kSortThreads)
+sort_plan_kernel(const int64_t* __restrict__ hsc, const void* __restrict__ offsets, bool idx64, int32_t T,
+                 int32_t B, int64_t N, int key_bits, int64_t tile_size, SortPlanView pv) {
+  __shared__ int32_t s_scan[kSortThreads];
+  __shared__ int32_t s_carry, s_bad, s_pass[kSortMaxPasses];
+  const int tid = threadIdx.x;
+  if (tid == 0) { s_carry = 0; s_bad = 0; }
+  if (tid < kSortMaxPasses) s_pass[tid] = 0;
+  __syncthreads();
+  // 1. segment heads + monotonicity
+  for (int32_t t0 = 0; t0 < T; t0 += kSortThreads) {
+    const int32_t t = t0 + tid;
+    int32_t head = 0;
+    if (t < T) {
+      const int64_t h = hsc[t];
+      const int64_t prev = t > 0 ? hsc[t - 1] : -1;
+      head = (t == 0 || h != prev) ? 1 : 0;
+      if (t > 0 && h < prev) s_bad = 1;
+      if (hsc[t + 1] < h) s_bad = 1;
+    }
+    s_scan[tid] = head;
+    __syncthreads();
+    for (int d = 1; d < kSortThreads; d <<= 1) {  // inclusive Hillis-Steele
+      const int32_t v = tid >= d ? s_scan[tid - d] : 0;
+      __syncthreads();
+      s_scan[tid] += v;
+      __syncthreads();
+    }
+    const int32_t seg = s_carry + s_scan[tid] - 1;
+    if (t < T) {
+      pv.feat_seg[t] = seg;
+      if (head) { pv.seg_feat0[seg] = t; pv.seg_base[seg] = hsc[t]; }
+    }
+    __syncthreads();
+    if (tid == kSortThreads - 1) s_carry += s_scan[tid];
+    __syncthreads();
+  }
+  int32_t nseg = s_carry;
+  if (s_bad) {  // hash bases not grouped by table: one global segment
+    nseg = 1;
+    for (int32_t t = tid; t < T; t += kSortThreads) pv.feat_seg[t] = 0;
+    if (tid == 0) { pv.seg_feat0[0] = 0; pv.seg_base[0] = 0; }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    pv.seg_feat0[nseg] = T;
+    pv.seg_base[nseg] = hsc[T];
+    pv.seg_p0[nseg] = N;
+    s_carry = 0;
+  }
+  __syncthreads();
+  // 2. per segment: bits -> passes, position range, tiles
+  for (int32_t s0 = 0; s0 < nseg; s0 += kSortThreads) {
+    const int32_t s = s0 + tid;
+    int32_t ntiles = 0;
+    if (s < nseg) {
+      const int64_t rows = s_bad ? 0 : pv.seg_base[s + 1] - pv.seg_base[s];
+      int bits = s_bad ? key_bits : (rows <= 1 ? 0 : 64 - __clzll((unsigned long long)(rows - 1)));
+      if (bits > key_bits) bits = key_bits;
+      const int passes = (bits + kSortDigitBits - 1) / kSortDigitBits;
+      pv.seg_passes[s] = passes;
+      for (int k = 0; k < passes; ++k) s_pass[k] = 1;
+      const int64_t p0 = load_index(offsets, (int64_t)pv.seg_feat0[s] * B, idx64);
+      const int64_t p1 = s + 1 < nseg ? load_index(offsets, (int64_t)pv.seg_feat0[s + 1] * B, idx64) : N;
+      pv.seg_p0[s] = p0;
+      ntiles = (int32_t)ceil_div(p1 - p0, tile_size);
+    }
+    s_scan[tid] = ntiles;
+    __syncthreads();
+    for (int d = 1; d < kSortThreads; d <<= 1) {
+      const int32_t v = tid >= d ? s_scan[tid - d] : 0;
+      __syncthreads();
+      s_scan[tid] += v;
+      __syncthreads();
+    }
+    if (s < nseg) pv.seg_tile0[s] = s_carry + s_scan[tid] - ntiles;
+    __syncthreads();
+    if (tid == kSortThreads - 1) s_carry += s_scan[tid];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    pv.seg_tile0[nseg] = s_carry;
+    pv.hdr[kHdrNseg] = nseg;
+    pv.hdr[kHdrTiles] = s_carry;
+  }
+  if (tid < kSortMaxPasses) pv.hdr[kHdrPass + tid] = s_pass[tid];
+}
+
+// ------------------------------------------------------------------------------------ linearise
+// One warp per 32 consecutive bags of one feature: key = hash base + id, payload = bag (t*B+b) or position.
+// A segment with an odd number of passes starts in the alternate buffers, an even one in the caller's, so
+// that its last pass ends in the caller's.
+template <typename K>
+__global__ void __launch_bounds__(128)
+tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ offsets, bool idx64,
+                     const int64_t* __restrict__ hash_size_cumsum, int32_t T, int32_t B,
+                     int32_t tiles_per_table, bool payload_is_position, K* __restrict__ keys_a,
+                     int32_t* __restrict__ payload_a, K* __restrict__ keys_b,
+                     int32_t* __restrict__ payload_b, int32_t* __restrict__ bag_of_pos, SortPlanView pv) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= (int64_t)T * tiles_per_table) return;
+  const int t = (int)(tile / tiles_per_table);
+  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
+  const int nb = min(32, B - b0);
+  const int64_t obase = (int64_t)t * B + b0;
+  const int64_t my_start = load_index(offsets, obase + min(lane, nb), idx64);
+  const int64_t S0 = __shfl_sync(kFull, my_start, 0);
+  const int32_t rel_start = (int32_t)(my_start - S0);
+  int32_t rel_end = __shfl_down_sync(kFull, rel_start, 1);
+  if (lane == 31) rel_end = (int32_t)(load_index(offsets, obase + nb, idx64) - S0);
+  const int32_t len = __shfl_sync(kFull, rel_end, 31);
+  const int64_t hash_base = hash_size_cumsum[t];
+  const bool to_b = (pv.seg_passes[pv.feat_seg[t]] & 1) != 0;
+  K* __restrict__ keys = to_b ? keys_b : keys_a;
+  int32_t* __restrict__ payload = to_b ? payload_b : payload_a;
+  const int32_t iters = (len + 31) / 32;
+  for (int32_t it = 0; it < iters; ++it) {
+    const int32_t p = it * 32 + lane;
+    // bag of position p = number of bags whose end is <= p (ends are sorted)
+    int j = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const int probe = j + step - 1;
+      const int32_t e = __shfl_sync(kFull, rel_end, probe);
+      if (e <= p) j += step;
+    }
+    if (p < len) {
+      const int64_t idx = load_index(indices, S0 + p, idx64);
+      const int32_t bt = (int32_t)(obase + j);
+      keys[S0 + p] = (K)(hash_base + idx);
+      payload[S0 + p] = payload_is_position ? (int32_t)(S0 + p) : bt;
+      if (bag_of_pos) bag_of_pos[S0 + p] = bt;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ per-pass kernels
+struct TileInfo {
+  int32_t seg;
+  int32_t passes;
+  int64_t begin, end;  // positions
+  int64_t base;        // key base of the segment
+  int64_t seg_p0;
+};
+
+// tile -> (segment, position range); false when the tile is past the last one or its segment is done
+__device__ __forceinline__ bool sort_tile_info(const SortPlanView& pv, int32_t tile, int pass,
+                                               int64_t tile_size, TileInfo& ti) {
+  const int32_t nseg = pv.hdr[kHdrNseg];
+  if (tile >= pv.hdr[kHdrTiles]) return false;
+  int32_t lo = 0, hi = nseg;  // largest s with seg_tile0[s] <= tile
+  while (hi - lo > 1) {
+    const int32_t mid = (lo + hi) >> 1;
+    if (pv.seg_tile0[mid] <= tile) lo = mid; else hi = mid;
+  }
+  ti.seg = lo;
+  ti.passes = pv.seg_passes[lo];
+  if (pass >= ti.passes) return false;
+  ti.seg_p0 = pv.seg_p0[lo];
+  ti.begin = ti.seg_p0 + (int64_t)(tile - pv.seg_tile0[lo]) * tile_size;
+  const int64_t seg_end = pv.seg_p0[lo + 1];
+  ti.end = ti.begin + tile_size < seg_end ? ti.begin + tile_size : seg_end;
+  ti.base = pv.seg_base[lo];
+  return true;
+}
+
+template <typename K>
+__device__ __forceinline__ int sort_digit(K key, int64_t base, int shift) {
+  return (int)(((unsigned long long)((int64_t)key - base) >> shift) & (kSortBins - 1));
+}
+
+// counts[tile][bin]
+template <typename K>
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_kernel(const K* __restrict__ keys_a, const K* __restrict__ keys_b, int pass, int64_t tile_size,
+                 uint32_t* __restrict__ counts, SortPlanView pv) {
+  if (!pv.hdr[kHdrPass + pass]) return;
+  __shared__ uint32_t hist[kSortBins];
+  TileInfo ti;
+  if (!sort_tile_info(pv, blockIdx.x, pass, tile_size, ti)) return;
+  const K* __restrict__ src = ((ti.passes - pass) & 1) ? keys_b : keys_a;
+  for (int i = threadIdx.x; i < kSortBins; i += kSortThreads) hist[i] = 0;
+  __syncthreads();
+  const int shift = pass * kSortDigitBits;
+  for (int64_t p0 = ti.begin; p0 < ti.end; p0 += kSortThreads) {
+    const int64_t p = p0 + threadIdx.x;
+    const bool valid = p < ti.end;
+    const int d = valid ? sort_digit<K>(src[p], ti.base, shift) : kSortBins + (threadIdx.x & 31);
+    const unsigned m = __match_any_sync(kFull, d);  // one shared-memory atomic per distinct digit per warp
+    if (valid && (int)(__ffs(m) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&hist[d], __popc(m));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kSortBins; i += kSortThreads)
+    counts[(size_t)blockIdx.x * kSortBins + i] = hist[i];
+}
+
+// One CTA per segment: counts[tile][bin] -> offset (relative to the segment start) of the first element of
+// bin `bin` of tile `tile` in the stably partitioned output.  1024 threads = 2 tile halves x 512 bins.
+__global__ void __launch_bounds__(1024)
+sort_scan_kernel(int pass, uint32_t* __restrict__ counts, SortPlanView pv) {
+  if (!pv.hdr[kHdrPass + pass]) return;
+  const int32_t seg = blockIdx.x;
+  if (seg >= pv.hdr[kHdrNseg] || pass >= pv.seg_passes[seg]) return;
+  __shared__ uint32_t half_sum[2][kSortBins];
+  __shared__ uint32_t bin_base[kSortBins];
+  __shared__ uint32_t warp_tot[kSortBins / 32];
+  const int bin = threadIdx.x & (kSortBins - 1);
+  const int half = threadIdx.x >> kSortDigitBits;
+  const int32_t t0 = pv.seg_tile0[seg], t1 = pv.seg_tile0[seg + 1];
+  const int32_t mid = t0 + (t1 - t0 + 1) / 2;
+  const int32_t a = half ? mid : t0, b = half ? t1 : mid;
+  uint32_t sum = 0;
+#pragma unroll 8
+  for (int32_t t = a; t < b; ++t) sum += counts[(size_t)t * kSortBins + bin];
+  half_sum[half][bin] = sum;
+  __syncthreads();
+  if (half == 0) {  // exclusive scan of the bin totals over the 512 bins
+    const uint32_t tot = half_sum[0][bin] + half_sum[1][bin];
+    uint32_t inc = tot;
+    const int lane = bin & 31;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(kFull, inc, d);
+      if (lane >= d) inc += v;
+    }
+    if (lane == 31) warp_tot[bin >> 5] = inc;
+    bin_base[bin] = inc - tot;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int w = 0; w < kSortBins / 32; ++w) { const uint32_t v = warp_tot[w]; warp_tot[w] = run; run += v; }
+  }
+  __syncthreads();
+  uint32_t run = bin_base[bin] + warp_tot[bin >> 5] + (half ? half_sum[0][bin] : 0);
+  for (int32_t t = a; t < b; ++t) {
+    const size_t i = (size_t)t * kSortBins + bin;
+    const uint32_t c = counts[i];
+    counts[i] = run;
+    run += c;
+  }
+}
+
+// Stable scatter of one tile.  Each warp ranks a contiguous 256-position slice with warp-private counters
+// (match_any gives the rank among the 32 lanes, the counter the rank among earlier rounds), the slices are
+// then chained in warp order: the relative order of equal digits is exactly the position order.
+template <typename K>
+__global__ void __launch_bounds__(kSortThreads)
+sort_scatter_kernel(K* __restrict__ keys_a, int32_t* __restrict__ pay_a, K* __restrict__ keys_b,
+                    int32_t* __restrict__ pay_b, int pass, int64_t tile_size,
+                    const uint32_t* __restrict__ counts, SortPlanView pv) {
+  if (!pv.hdr[kHdrPass + pass]) return;
+  __shared__ uint32_t off[kSortBins];                 // next output offset per bin (segment-relative)
+  __shared__ uint32_t wcnt[kSortWarps][kSortBins];    // per-warp counters, then per-warp bases
+  TileInfo ti;
+  if (!sort_tile_info(pv, blockIdx.x, pass, tile_size, ti)) return;
+  const bool from_b = ((ti.passes - pass) & 1) != 0;
+  const K* __restrict__ src_k = from_b ? keys_b : keys_a;
+  const int32_t* __restrict__ src_p = from_b ? pay_b : pay_a;
+  K* __restrict__ dst_k = from_b ? keys_a : keys_b;
+  int32_t* __restrict__ dst_p = from_b ? pay_a : pay_b;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  const int shift = pass * kSortDigitBits;
+  for (int i = threadIdx.x; i < kSortBins; i += kSortThreads)
+    off[i] = counts[(size_t)blockIdx.x * kSortBins + i];
+  for (int64_t c0 = ti.begin; c0 < ti.end; c0 += kSortChunk) {
+    for (int i = threadIdx.x; i < kSortWarps * kSortBins; i += kSortThreads) (&wcnt[0][0])[i] = 0;
+    __syncthreads();
+    K key[8];
+    int32_t pay[8];
+    int32_t dg[8];
+    uint32_t rank[8];
+    const int64_t w0 = c0 + warp * 256;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int64_t p = w0 + r * 32 + lane;
+      const bool valid = p < ti.end;
+      key[r] = valid ? src_k[p] : (K)0;
+      pay[r] = valid ? src_p[p] : 0;
+      dg[r] = valid ? sort_digit<K>(key[r], ti.base, shift) : -1;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int d = dg[r] >= 0 ? dg[r] : kSortBins + lane;
+      const unsigned m = __match_any_sync(kFull, d);
+      if (dg[r] >= 0) {
+        rank[r] = wcnt[warp][d] + __popc(m & lt);
+      }
+      __syncwarp();
+      if (dg[r] >= 0 && (int)(__ffs(m) - 1) == lane) wcnt[warp][d] += __popc(m);
+      __syncwarp();
+    }
+    __syncthreads();
+    for (int bin = threadIdx.x; bin < kSortBins; bin += kSortThreads) {
+      uint32_t run = off[bin];
+#pragma unroll
+      for (int w = 0; w < kSortWarps; ++w) {
+        const uint32_t c = wcnt[w][bin];
+        wcnt[w][bin] = run;
+        run += c;
+      }
+      off[bin] = run;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      if (dg[r] >= 0) {
+        const int64_t q = ti.seg_p0 + wcnt[warp][dg[r]] + rank[r];
+        dst_k[q] = key[r];
+        dst_p[q] = pay[r];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+namespace {
+
+struct SortWs {
+  void* keys_b;
+  int32_t* pay_b;
+  uint32_t* counts;
+  SortPlanView pv;
+  int64_t tile_size;
+  int64_t max_tiles;
+  size_t bytes;
+};
+
+// ws = [alt keys | alt payload | counts[max_tiles][512] | plan]
+SortWs sort_ws_layout(void* ws, int64_t N, int key_bits, int32_t T) {
+  SortWs w;
+  const size_t ksz = key_bits > 32 ? 8 : 4;
+  w.tile_size = sort_tile_size(N);
+  w.max_tiles = ceil_div(N, w.tile_size) + T;
+  char* p = (char*)ws;
+  w.keys_b = p;
+  p += sort_align256(ksz * (size_t)N);
+  w.pay_b = (int32_t*)p;
+  p += sort_align256(4 * (size_t)N);
+  w.counts = (uint32_t*)p;
+  p += sort_align256((size_t)w.max_tiles * kSortBins * sizeof(uint32_t));
+  const size_t n1 = (size_t)T + 1;
+  w.pv.seg_base = (int64_t*)p;
+  p += sort_align256(8 * n1);
+  w.pv.seg_p0 = (int64_t*)p;
+  p += sort_align256(8 * n1);
+  w.pv.hdr = (int32_t*)p;
+  p += 256;
+  w.pv.feat_seg = (int32_t*)p;
+  p += sort_align256(4 * n1);
+  w.pv.seg_feat0 = (int32_t*)p;
+  p += sort_align256(4 * n1);
+  w.pv.seg_passes = (int32_t*)p;
+  p += sort_align256(4 * n1);
+  w.pv.seg_tile0 = (int32_t*)p;
+  p += sort_align256(4 * n1);
+  w.bytes = (size_t)(p - (char*)ws) + 256;
+  return w;
+}
+
+template <typename K>
+int sort_impl(const void* indices, const void* offsets, bool idx64, const int64_t* hash_size_cumsum,
+              int32_t T, int32_t B, int64_t N, int key_bits, bool payload_is_position, void* sorted_keys,
+              int32_t* sorted_payload, int32_t* bag_of_pos, void* ws, size_t ws_bytes, cudaStream_t s) {
+  const SortWs w = sort_ws_layout(ws, N, key_bits, T);
+  if (ws_bytes < w.bytes) return B200_EINVAL;
+  K* keys_a = (K*)sorted_keys;
+  K* keys_b = (K*)w.keys_b;
+  sort_plan_kernel<<<1, kSortThreads, 0, s>>>(hash_size_cumsum, offsets, idx64, T, B, N, key_bits,
+                                              w.tile_size, w.pv);
+  B200_LAUNCH_CHECK();
+  const int tiles_per_table = (B + 31) / 32;
+  const int64_t ltiles = (int64_t)T * tiles_per_table;
+  tbe_linearize_kernel<K><<<(unsigned)ceil_div(ltiles, 4), 128, 0, s>>>(
+      indices, offsets, idx64, hash_size_cumsum, T, B, tiles_per_table, payload_is_position, keys_a,
+      sorted_payload, keys_b, w.pay_b, bag_of_pos, w.pv);
+  B200_LAUNCH_CHECK();
+  const int passes = (key_bits + kSortDigitBits - 1) / kSortDigitBits;
+  for (int pass = 0; pass < passes; ++pass) {  // passes no segment needs return at once (plan header)
+    sort_hist_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(keys_a, keys_b, pass, w.tile_size,
+                                                                     w.counts, w.pv);
+    B200_LAUNCH_CHECK();
+    sort_scan_kernel<<<(unsigned)T, 1024, 0, s>>>(pass, w.counts, w.pv);
+    B200_LAUNCH_CHECK();
+    sort_scatter_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(
+        keys_a, sorted_payload, keys_b, w.pay_b, pass, w.tile_size, w.counts, w.pv);
+    B200_LAUNCH_CHECK();
+  }
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits, int32_t T) {
+  if (N <= 0 || T <= 0) return 256;
+  return sort_ws_layout(nullptr, N, key_bits, T).bytes;
+}
+
+extern "C" int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
+                                     const int64_t* hash_size_cumsum, int32_t T, int32_t B,
+                                     int64_t N, int key_bits, int payload_is_position,
+                                     void* sorted_keys, int32_t* sorted_payload,
+                                     int32_t* bag_of_pos, void* sort_ws, size_t sort_ws_bytes,
+                                     void* stream) {
+  if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
+  if (N >= 0x7fffffffLL || key_bits < 1 || key_bits > 64) return B200_EINVAL;
+  if (payload_is_position && !bag_of_pos) return B200_EINVAL;
+  if (N == 0 || T == 0 || B == 0) return B200_OK;
+  const bool idx64 = index_dtype == B200_I64;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (key_bits > 32)
+    return sort_impl<uint64_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
+                               payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                               sort_ws, sort_ws_bytes, s);
+  return sort_impl<uint32_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
+                             payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                             sort_ws, sort_ws_bytes, s);
+}

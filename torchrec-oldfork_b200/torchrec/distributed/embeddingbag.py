@@ -110,6 +110,22 @@ class EmbeddingBagCollectionAwaitable(LazyAwaitable[KeyedTensor]):
                            key_dim=1)
 
 
+class _JoinStream(LazyAwaitable[KeyedTensor]):
+    """Finishes `inner` on the stream it was issued on and makes the consumer's stream wait for it."""
+
+    def __init__(self, inner: Awaitable[KeyedTensor], side: "torch.cuda.Stream") -> None:
+        super().__init__()
+        self._inner, self._side = inner, side
+
+    def _wait_impl(self) -> KeyedTensor:
+        with torch.cuda.stream(self._side):
+            kt = self._inner.wait()
+        cur = torch.cuda.current_stream(self._side.device)
+        cur.wait_stream(self._side)
+        kt.values().record_stream(cur)
+        return kt
+
+
 class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch.Tensor], KeyedTensor],
                                     FusedOptimizerModule):
     def __init__(self, module: EmbeddingBagCollectionInterface,
@@ -139,6 +155,8 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         self._has_features_permute = True
         self._env = env
         self._peer = None          # fused lookup + exchange over NVLink peer memory (peer_dist.py)
+        self._lookup_stream_obj = None
+        self._lookup_stream_checked = False
         self._peer_checked = False
         self._optim = CombinedOptimizer(prefixed_fused_optimizers(self._lookups, "embedding_bags."))
 
@@ -212,10 +230,23 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
                 self._peer = peer_dist.try_build(self, self._env.process_group, self._device)
         return self._peer
 
-    def compute_and_output_dist(self, ctx: ShardedModuleContext, input: SparseFeaturesList
-                                ) -> LazyAwaitable[KeyedTensor]:
-        if self._has_uninitialized_output_dist:
-            self._create_output_dist()
+    def _lookup_stream(self) -> Optional["torch.cuda.Stream"]:
+        """The stream the lookups and their output distribution run on.  The pooled lookup depends only on the
+        distributed ids and on the previous step's table update, not on the dense arch, so it gets a stream of
+        its own: forward overlaps the dense-arch forward, and - autograd runs a node's backward on the stream
+        of its forward - the fused optimizer backward (HBM / NVLink bound) overlaps the dense-arch backward
+        GEMMs.  B200_LOOKUP_STREAM=0 keeps everything on the caller's stream."""
+        if self._lookup_stream_checked:
+            return self._lookup_stream_obj
+        self._lookup_stream_checked = True
+        import os
+        if (self._device is not None and self._device.type == "cuda"
+                and os.environ.get("B200_LOOKUP_STREAM", "1") != "0"):
+            self._lookup_stream_obj = torch.cuda.Stream(device=self._device)
+        return self._lookup_stream_obj
+
+    def _compute_and_output_dist(self, ctx: ShardedModuleContext, input: SparseFeaturesList
+                                 ) -> LazyAwaitable[KeyedTensor]:
         if self._variable_batch_size:
             return self.output_dist(ctx, self.compute(ctx, input))
         peer = self._peer_dist()
@@ -226,6 +257,23 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         return EmbeddingBagCollectionAwaitable(
             [d(lookup(f)) for lookup, d, f in zip(self._lookups, self._output_dists, input)],
             self._embedding_dims, self._embedding_names)
+
+    def compute_and_output_dist(self, ctx: ShardedModuleContext, input: SparseFeaturesList
+                                ) -> LazyAwaitable[KeyedTensor]:
+        if self._has_uninitialized_output_dist:
+            self._create_output_dist()
+        side = self._lookup_stream()
+        if side is None:
+            return self._compute_and_output_dist(ctx, input)
+        main = torch.cuda.current_stream(self._device)
+        ready = getattr(ctx, "inputs_ready_event", None)
+        if ready is not None:
+            side.wait_event(ready)  # pipelined: the ids were distributed on another stream a step ago
+        else:
+            side.wait_stream(main)
+        with torch.cuda.stream(side):
+            inner = self._compute_and_output_dist(ctx, input)
+        return _JoinStream(inner, side)
 
     # ---- state / optimizer
     def state_dict(self, destination=None, prefix: str = "", keep_vars: bool = False) -> Dict[str, Any]:

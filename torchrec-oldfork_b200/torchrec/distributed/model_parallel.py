@@ -53,6 +53,13 @@ class DefaultDataParallelWrapper(DataParallelWrapper):
         if not any(p.requires_grad for n, p in dmp._dmp_wrapped_module.named_parameters() if n not in ignored):
             return  # sparse-only model (e.g. a bare EmbeddingCollection): nothing is data-parallel
         DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(dmp._dmp_wrapped_module, ignore)
+        import os
+        if (device.type == "cuda" and dist.get_backend(pg) == "nccl" and env.world_size == dist.get_world_size()
+                and os.environ.get("B200_DDP_OWN_PG", "1") != "0"):
+            # The dense gradient all-reduce gets a communicator of its own: on a shared one it queues in front
+            # of the next batch's KJT all-to-alls (one NCCL stream per communicator), and a captured all-reduce
+            # replayed from a CUDA graph must never interleave with eager collectives of the same communicator.
+            pg = dist.new_group(ranks=list(range(env.world_size)), backend="nccl")
         dmp._dmp_wrapped_module = DistributedDataParallel(
             module=dmp._dmp_wrapped_module.to(device),
             device_ids=None if device.type == "cpu" else [device], process_group=pg,

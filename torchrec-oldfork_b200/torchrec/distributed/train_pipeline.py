@@ -28,6 +28,91 @@ In = TypeVar("In")
 Out = TypeVar("Out")
 
 
+# ---------------------------------------------------------------------------------------------
+# CUDA-graph replay of the steady-state step (SURVEY §8 f1 "then CUDA-graph the steady-state step").
+#
+# What is captured: forward, backward (with the fused table update and DDP's gradient all-reduce) and the
+# dense optimizer step of ONE batch whose sparse input distribution has already run.  What stays eager, on
+# its own streams: the host->device copy of batch i+2 and the input distribution of batch i+1 (its
+# all-to-alls need the host to read the receive sizes).  Every step the distributed ids of batch i are
+# copied into the graph's fixed input buffers and the graph is replayed: ~300 launches, the cross-rank
+# barriers and the autograd bookkeeping of a step cost the host one cudaGraphLaunch.
+#
+# A graph is only valid for the exact shapes it was captured with - including the per-key id counts, which
+# become pointer offsets inside it - and for the learning rates, which are kernel arguments.  The signature
+# below covers all of them; a step whose signature has no graph runs eagerly (and is captured if the
+# signature repeats), so ragged inputs keep working.
+def _sig(obj):
+    from torchrec.distributed.embedding_types import SparseFeatures, SparseFeaturesList
+    if obj is None:
+        return None
+    if isinstance(obj, torch.Tensor):
+        return (tuple(obj.shape), obj.dtype)
+    if isinstance(obj, KeyedJaggedTensor):
+        return ("kjt", tuple(obj.keys()), obj.stride(), tuple(obj.length_per_key()),
+                tuple(_sig(t) for t in (obj._values, obj._weights, obj._lengths, obj._offsets)))
+    if isinstance(obj, SparseFeatures):
+        return ("sf", _sig(obj.id_list_features), _sig(obj.id_score_list_features))
+    if isinstance(obj, SparseFeaturesList):
+        return ("sfl",) + tuple(_sig(f) for f in obj.features)
+    if isinstance(obj, (list, tuple)):
+        return tuple(_sig(o) for o in obj)
+    if hasattr(obj, "dense_features") and hasattr(obj, "sparse_features") and hasattr(obj, "labels"):
+        return ("batch", _sig(obj.dense_features), _sig(obj.sparse_features), _sig(obj.labels))
+    raise TypeError(f"CUDA-graph mode does not know how to hold a {type(obj).__name__} at a fixed address")
+
+
+def _static_copy(obj):
+    """Same structure, every tensor cloned (these clones are the graph's input buffers)."""
+    from torchrec.distributed.embedding_types import SparseFeatures, SparseFeaturesList
+    if obj is None:
+        return None
+    if isinstance(obj, torch.Tensor):
+        return obj.clone()
+    if isinstance(obj, KeyedJaggedTensor):
+        c = lambda t: None if t is None else t.clone()  # noqa: E731
+        return KeyedJaggedTensor(keys=list(obj.keys()), values=c(obj._values), weights=c(obj._weights),
+                                 lengths=c(obj._lengths), offsets=c(obj._offsets), stride=obj.stride(),
+                                 length_per_key=list(obj.length_per_key()))
+    if isinstance(obj, SparseFeatures):
+        return SparseFeatures(id_list_features=_static_copy(obj.id_list_features),
+                              id_score_list_features=_static_copy(obj.id_score_list_features))
+    if isinstance(obj, SparseFeaturesList):
+        return SparseFeaturesList([_static_copy(f) for f in obj.features])
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_static_copy(o) for o in obj)
+    return type(obj)(dense_features=_static_copy(obj.dense_features),
+                     sparse_features=_static_copy(obj.sparse_features), labels=_static_copy(obj.labels))
+
+
+def _tensors(obj, out: list) -> list:
+    from torchrec.distributed.embedding_types import SparseFeatures, SparseFeaturesList
+    if obj is None:
+        return out
+    if isinstance(obj, torch.Tensor):
+        out.append(obj)
+    elif isinstance(obj, KeyedJaggedTensor):
+        out.extend(t for t in (obj._values, obj._weights, obj._lengths, obj._offsets) if t is not None)
+    elif isinstance(obj, SparseFeatures):
+        _tensors(obj.id_list_features, out)
+        _tensors(obj.id_score_list_features, out)
+    elif isinstance(obj, SparseFeaturesList):
+        for f in obj.features:
+            _tensors(f, out)
+    elif isinstance(obj, (list, tuple)):
+        for o in obj:
+            _tensors(o, out)
+    else:
+        _tensors(obj.dense_features, out)
+        _tensors(obj.sparse_features, out)
+        _tensors(obj.labels, out)
+    return out
+
+
+class _StepGraph:
+    __slots__ = ("graph", "static", "slots", "output", "launches")
+
+
 def _rank() -> int:
     import torch.distributed as dist
     return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
@@ -75,9 +160,17 @@ class TrainPipelineBase(Generic[In, Out]):
 class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
     def __init__(self, model: nn.Module, optimizer: torch.optim.Optimizer, device: torch.device,
                  sparse_features_fn: Optional[Callable[[In], KeyedJaggedTensor]] = None,
-                 loss_log_path: Optional[str] = None) -> None:
+                 loss_log_path: Optional[str] = None, cuda_graph: bool = False, graph_warmup: int = 11) -> None:
         super().__init__(model, optimizer, device)
         self._loss_log_path = loss_log_path
+        # cuda_graph: replay the step as one CUDA graph once `graph_warmup` eager steps have run (DDP needs
+        # 11 eager iterations before its backward may be captured) and the step's signature repeats
+        self._cuda_graph = bool(cuda_graph) and loss_log_path is None
+        self._graph_warmup = graph_warmup
+        self._eager_steps = 0
+        self._graphs: dict = {}
+        self._last_sig = None
+        self.graph_replays = 0
         if device.type != "cuda":
             raise RuntimeError("TrainPipelineSparseDist overlaps CUDA streams; use TrainPipelineBase on CPU")
         # high priority: the small bucketize / permute / reduction kernels whose results the host waits for
@@ -109,6 +202,7 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         leaves the distributed features in each module's pipelined queue."""
         main = torch.cuda.current_stream(self._device)
         with torch.cuda.stream(self._data_dist_stream):
+            done = list(self._issued)
             for m, ctx, awaitable in self._issued:
                 dist_input = awaitable.wait()
                 record = getattr(dist_input, "record_stream", None)
@@ -119,6 +213,8 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
             ev = torch.cuda.Event()
             ev.record(self._data_dist_stream)
             self._dist_done.append(ev)
+            for _m, ctx, _a in done:
+                ctx.inputs_ready_event = ev  # lookups on their own stream wait for this, not for `main`
 
     def _start_sparse_data_dist(self, batch) -> None:
         self._issue_sparse_data_dist(batch)
@@ -133,6 +229,73 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         self._issued = []
         self._batch_i = self._batch_ip1 = self._batch_ip2 = None
         self._connected = False
+
+    # ---- CUDA-graph replay
+    def _lr_signature(self):
+        lrs = [g.get("lr") for g in self._optimizer.param_groups]
+        for m in self._model.modules():
+            args = getattr(m, "optimizer_args", None)
+            if args is not None and hasattr(args, "learning_rate"):
+                lrs.append(float(args.learning_rate))
+        return tuple(lrs)
+
+    def _graphed_step(self):
+        """Replays (capturing first if needed) the step of batch i; None = run this step eagerly."""
+        if self._eager_steps < self._graph_warmup:
+            return None
+        if any(len(m._pipelined_inputs) == 0 for m in self._sharded):
+            return None
+        step_in = (self._batch_i, [m._pipelined_inputs[0][1] for m in self._sharded])
+        try:
+            sig = (_sig(step_in), self._lr_signature())
+        except TypeError:
+            self._cuda_graph = False
+            return None
+        sg = self._graphs.get(sig)
+        if sg is None:
+            if sig != self._last_sig:  # capture only shapes that repeat
+                self._last_sig = sig
+                return None
+            sg = self._capture(step_in)
+            self._graphs[sig] = sg
+        for dst, src in zip(sg.slots, _tensors(step_in, [])):
+            dst.copy_(src, non_blocking=True)
+        sg.graph.replay()
+        for m in self._sharded:
+            m._pipelined_inputs.popleft()
+        self.graph_replays += 1
+        from b200_sparse.ops import KernelProfile
+        KernelProfile.launches += sg.launches
+        return sg.output
+
+    def _capture(self, step_in) -> "_StepGraph":
+        """Captures the step on buffers of its own; capture records without running, so the caller then
+        copies the real inputs in and replays."""
+        from b200_sparse.ops import KernelProfile
+        sg = _StepGraph()
+        sg.static = _static_copy(step_in)
+        sg.slots = _tensors(sg.static, [])  # before the capture fills the KJTs' lazy caches
+        batch, dist_inputs = sg.static
+        ctxs = [m._pipelined_inputs[0][0] for m in self._sharded]
+        was_profiling, KernelProfile.enabled = KernelProfile.enabled, False  # timing events cannot be captured
+        n0 = KernelProfile.launches
+        self._optimizer.zero_grad(set_to_none=True)
+        torch.cuda.synchronize(self._device)
+        sg.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(sg.graph):
+            start = torch.cuda.Event()
+            start.record(torch.cuda.current_stream(self._device))
+            for m, ctx, d in zip(self._sharded, ctxs, dist_inputs):
+                ctx.inputs_ready_event = start  # an event of THIS capture: lookups fork from the graph's root
+                m._pipelined_inputs.appendleft((ctx, d))
+            losses, sg.output = self._model(batch)
+            torch.sum(losses, dim=0).backward()
+            self._optimizer.step()
+        sg.launches = KernelProfile.launches - n0
+        KernelProfile.launches = n0
+        KernelProfile.enabled = was_profiling
+        # the capture consumed the static entries it pushed; the real entries of batch i are still queued
+        return sg
 
     def _copy(self, it: Iterator[In]):
         try:
@@ -172,13 +335,16 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         # all-reduces ...
         if self._batch_ip1 is not None:
             self._issue_sparse_data_dist(self._batch_ip1)
-        losses, output = self._model(self._batch_i)
-        if self._model.training:
-            if self._loss_log_path is not None and _rank() == 0:
-                with open(self._loss_log_path, "a") as f:  # same line format as the fork's log
-                    f.write(str(losses.detach().cpu().numpy().tolist()) + "\n")
-            torch.sum(losses, dim=0).backward()
-            self._optimizer.step()
+        output = self._graphed_step() if self._cuda_graph and self._model.training else None
+        if output is None:
+            losses, output = self._model(self._batch_i)
+            if self._model.training:
+                if self._loss_log_path is not None and _rank() == 0:
+                    with open(self._loss_log_path, "a") as f:  # same line format as the fork's log
+                        f.write(str(losses.detach().cpu().numpy().tolist()) + "\n")
+                torch.sum(losses, dim=0).backward()
+                self._optimizer.step()
+            self._eager_steps += 1
         # ... phase 2: the host read of the receive sizes happens once the whole step of batch i is
         # queued, when that exchange has long finished, so neither the host nor the GPU waits.  (The
         # reference does both phases between forward and backward, :529: the GPU idles during the sync.)

@@ -280,7 +280,7 @@ def run_ours(args) -> None:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29571")
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev,
-                            timeout=datetime.timedelta(seconds=180))
+                            timeout=datetime.timedelta(seconds=int(os.environ.get("B200_PG_TIMEOUT", "180"))))
     pg = dist.group.WORLD
     torch.backends.cuda.matmul.allow_tf32 = True  # reference-era PyTorch default for the MLP GEMMs
     torch.backends.cudnn.allow_tf32 = True
@@ -399,6 +399,7 @@ def run_ours(args) -> None:
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": batch_bytes(host_batches[0]) * world, "d2h_bytes_per_step": 4 * world},
         "gpu_launches": launches, "clocks": clocks, "roofline": roof, "kernels": kernels,
+        "cuda_graph": {"enabled": bool(args.cuda_graph), "replays": int(getattr(pipe, "graph_replays", 0))},
     }
     if world == 1 and not args.no_cpu_baseline:
         try:

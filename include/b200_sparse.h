@@ -129,11 +129,13 @@ int b200_tbe_forward(const void* weights, int weight_dtype, const int64_t* weigh
  * table.  sorted_keys holds uint32 keys when key_bits <= 32, else uint64.  sorted_payload holds
  * b_t = t*B+b, or the original position p when payload_is_position != 0 (weighted lookups); bag_of_pos
  * (int32[N], may be NULL unless payload_is_position) receives b_t per position.  Equal keys keep position
- * order (== a stable argsort, bit for bit).  sort_ws: b200_tbe_sort_workspace_bytes(N, key_bits, T) bytes. */
+ * order (== a stable argsort, bit for bit).  max_table_bits: ceil(log2(rows)) of the largest table when the
+ * caller knows it (saves launching passes that no table needs), 0 when unknown; it must be 0 unless
+ * hash_size_cumsum is non-decreasing (features grouped by table).  sort_ws: b200_tbe_sort_workspace_bytes(N, key_bits, T) bytes. */
 size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits, int32_t T);
 int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
                           const int64_t* hash_size_cumsum, int32_t T, int32_t B, int64_t N,
-                          int key_bits, int payload_is_position, void* sorted_keys,
+                          int key_bits, int max_table_bits, int payload_is_position, void* sorted_keys,
                           int32_t* sorted_payload, int32_t* bag_of_pos, void* sort_ws,
                           size_t sort_ws_bytes, void* stream);
 

@@ -321,7 +321,8 @@ class SortedIndices:
 
 
 def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cumsum: torch.Tensor,
-                     total_hash_size_bits: int, B: int, weighted: bool) -> SortedIndices:
+                     total_hash_size_bits: int, B: int, weighted: bool, max_table_bits: int = 0) -> SortedIndices:
+    """max_table_bits: ceil(log2(rows)) of the largest table (0 = unknown); only for features grouped by table."""
     dev = _need_cuda(indices, offsets, hash_size_cumsum)
     idt = _idx_dt(indices, "indices")
     T = hash_size_cumsum.numel() - 1
@@ -333,10 +334,11 @@ def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cum
     bag_of_pos = torch.empty(N, dtype=torch.int32, device=dev) if weighted else None
     ws_bytes = lib.b200_tbe_sort_workspace_bytes(N, key_bits, T)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    n_pass = (key_bits + 8) // 9
+    host_bits = max_table_bits if 0 < max_table_bits < key_bits else key_bits
+    n_pass = (host_bits + 8) // 9
     with torch.cuda.device(dev), _timed("tbe_sort", dev, 2 + 3 * n_pass):  # plan, linearize, 3 kernels per pass
         check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
-                                        key_bits, int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
+                                        key_bits, int(max_table_bits), int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
                                         _p(ws), ws_bytes, _stream(dev)), "b200_tbe_sort_indices")
     return SortedIndices(keys, payload, bag_of_pos, N, key_bits, ws)
 

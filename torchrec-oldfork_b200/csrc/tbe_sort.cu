@@ -34,9 +34,10 @@ constexpr int kSortChunk = 2048;       // positions ranked per CTA step (8 per t
 constexpr int kSortMaxPasses = 8;      // 64-bit keys / 9 bits
 
 static inline size_t sort_align256(size_t x) { return (x + 255) & ~(size_t)255; }
-// positions per tile: a multiple of the chunk, at most ~512 tiles over all segments plus one per segment
+// positions per tile: one chunk while that keeps the tile count near 2048 (latency is hidden by many small
+// CTAs in flight), else a multiple of the chunk so that the count matrix and the per-segment scan stay bounded
 __host__ __device__ inline int64_t sort_tile_size(int64_t N) {
-  int64_t ts = ceil_div(ceil_div(N, 512), kSortChunk) * kSortChunk;
+  int64_t ts = ceil_div(ceil_div(N, 2048), kSortChunk) * kSortChunk;
   return ts < kSortChunk ? kSortChunk : ts;
 }
 
@@ -143,9 +144,13 @@ sort_plan_kernel(const int64_t* __restrict__ hsc, const void* __restrict__ offse
 }
 
 // ------------------------------------------------------------------------------------ linearise
-// One warp per 32 consecutive bags of one feature: key = hash base + id, payload = bag (t*B+b) or position.
-// A segment with an odd number of passes starts in the alternate buffers, an even one in the caller's, so
-// that its last pass ends in the caller's.
+// One warp per kLinTiles groups of 32 consecutive bags of one feature: key = hash base + id, payload = bag
+// (t*B+b) or position.  The offsets of all groups, then the first 32 ids of every group, are loaded before
+// anything is stored, so a warp has up to 2 x kLinTiles independent loads in flight (with one id per bag the
+// kernel is pure latency otherwise).  A segment with an odd number of passes starts in the alternate
+// buffers, an even one in the caller's, so that its last pass ends in the caller's.
+constexpr int kLinTiles = 4;
+
 template <typename K>
 __global__ void __launch_bounds__(128)
 tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ offsets, bool idx64,
@@ -154,39 +159,60 @@ tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ 
                      int32_t* __restrict__ payload_a, K* __restrict__ keys_b,
                      int32_t* __restrict__ payload_b, int32_t* __restrict__ bag_of_pos, SortPlanView pv) {
   const int lane = threadIdx.x & 31;
-  const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (tile >= (int64_t)T * tiles_per_table) return;
-  const int t = (int)(tile / tiles_per_table);
-  const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
-  const int nb = min(32, B - b0);
-  const int64_t obase = (int64_t)t * B + b0;
-  const int64_t my_start = load_index(offsets, obase + min(lane, nb), idx64);
-  const int64_t S0 = __shfl_sync(kFull, my_start, 0);
-  const int32_t rel_start = (int32_t)(my_start - S0);
-  int32_t rel_end = __shfl_down_sync(kFull, rel_start, 1);
-  if (lane == 31) rel_end = (int32_t)(load_index(offsets, obase + nb, idx64) - S0);
-  const int32_t len = __shfl_sync(kFull, rel_end, 31);
-  const int64_t hash_base = hash_size_cumsum[t];
-  const bool to_b = (pv.seg_passes[pv.feat_seg[t]] & 1) != 0;
-  K* __restrict__ keys = to_b ? keys_b : keys_a;
-  int32_t* __restrict__ payload = to_b ? payload_b : payload_a;
-  const int32_t iters = (len + 31) / 32;
-  for (int32_t it = 0; it < iters; ++it) {
-    const int32_t p = it * 32 + lane;
-    // bag of position p = number of bags whose end is <= p (ends are sorted)
-    int j = 0;
+  const int64_t group0 = ((int64_t)blockIdx.x * 4 + (threadIdx.x >> 5)) * kLinTiles;
+  const int64_t ngroups = (int64_t)T * tiles_per_table;
+  if (group0 >= ngroups) return;
+  int64_t S0[kLinTiles], obase[kLinTiles], first_idx[kLinTiles];
+  int32_t rel_end[kLinTiles], len[kLinTiles];
+  int tt[kLinTiles];
 #pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      const int probe = j + step - 1;
-      const int32_t e = __shfl_sync(kFull, rel_end, probe);
-      if (e <= p) j += step;
-    }
-    if (p < len) {
-      const int64_t idx = load_index(indices, S0 + p, idx64);
-      const int32_t bt = (int32_t)(obase + j);
-      keys[S0 + p] = (K)(hash_base + idx);
-      payload[S0 + p] = payload_is_position ? (int32_t)(S0 + p) : bt;
-      if (bag_of_pos) bag_of_pos[S0 + p] = bt;
+  for (int g = 0; g < kLinTiles; ++g) {
+    const int64_t tile = group0 + g;
+    len[g] = -1;
+    if (tile >= ngroups) continue;
+    const int t = (int)(tile / tiles_per_table);
+    const int b0 = (int)(tile - (int64_t)t * tiles_per_table) * 32;
+    const int nb = min(32, B - b0);
+    tt[g] = t;
+    obase[g] = (int64_t)t * B + b0;
+    const int64_t my_start = load_index(offsets, obase[g] + min(lane, nb), idx64);
+    const int64_t end_all = load_index(offsets, obase[g] + nb, idx64);
+    S0[g] = __shfl_sync(kFull, my_start, 0);
+    const int32_t rel_start = (int32_t)(my_start - S0[g]);
+    int32_t re = __shfl_down_sync(kFull, rel_start, 1);
+    if (lane == 31) re = (int32_t)(end_all - S0[g]);
+    rel_end[g] = re;
+    len[g] = (int32_t)(end_all - S0[g]);
+  }
+#pragma unroll
+  for (int g = 0; g < kLinTiles; ++g)
+    first_idx[g] = (len[g] > lane) ? load_index(indices, S0[g] + lane, idx64) : 0;
+#pragma unroll
+  for (int g = 0; g < kLinTiles; ++g) {
+    if (len[g] <= 0) continue;
+    const int t = tt[g];
+    const int64_t hash_base = hash_size_cumsum[t];
+    const bool to_b = (pv.seg_passes[pv.feat_seg[t]] & 1) != 0;
+    K* __restrict__ keys = to_b ? keys_b : keys_a;
+    int32_t* __restrict__ payload = to_b ? payload_b : payload_a;
+    const int32_t iters = (len[g] + 31) / 32;
+    for (int32_t it = 0; it < iters; ++it) {
+      const int32_t p = it * 32 + lane;
+      // bag of position p = number of bags whose end is <= p (ends are sorted)
+      int j = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const int probe = j + step - 1;
+        const int32_t e = __shfl_sync(kFull, rel_end[g], probe);
+        if (e <= p) j += step;
+      }
+      if (p < len[g]) {
+        const int64_t idx = it == 0 ? first_idx[g] : load_index(indices, S0[g] + p, idx64);
+        const int32_t bt = (int32_t)(obase[g] + j);
+        keys[S0[g] + p] = (K)(hash_base + idx);
+        payload[S0[g] + p] = payload_is_position ? (int32_t)(S0[g] + p) : bt;
+        if (bag_of_pos) bag_of_pos[S0[g] + p] = bt;
+      }
     }
   }
 }
@@ -239,12 +265,18 @@ sort_hist_kernel(const K* __restrict__ keys_a, const K* __restrict__ keys_b, int
   for (int i = threadIdx.x; i < kSortBins; i += kSortThreads) hist[i] = 0;
   __syncthreads();
   const int shift = pass * kSortDigitBits;
-  for (int64_t p0 = ti.begin; p0 < ti.end; p0 += kSortThreads) {
-    const int64_t p = p0 + threadIdx.x;
-    const bool valid = p < ti.end;
-    const int d = valid ? sort_digit<K>(src[p], ti.base, shift) : kSortBins + (threadIdx.x & 31);
-    const unsigned m = __match_any_sync(kFull, d);  // one shared-memory atomic per distinct digit per warp
-    if (valid && (int)(__ffs(m) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&hist[d], __popc(m));
+  for (int64_t c0 = ti.begin; c0 < ti.end; c0 += kSortChunk) {
+    K key[8];  // all loads of the chunk in flight before the first atomic
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int64_t p = c0 + r * kSortThreads + threadIdx.x;
+      key[r] = p < ti.end ? src[p] : (K)0;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int64_t p = c0 + r * kSortThreads + threadIdx.x;
+      if (p < ti.end) atomicAdd(&hist[sort_digit<K>(key[r], ti.base, shift)], 1u);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kSortBins; i += kSortThreads)
@@ -252,23 +284,35 @@ sort_hist_kernel(const K* __restrict__ keys_a, const K* __restrict__ keys_b, int
 }
 
 // One CTA per segment: counts[tile][bin] -> offset (relative to the segment start) of the first element of
-// bin `bin` of tile `tile` in the stably partitioned output.  1024 threads = 2 tile halves x 512 bins.
+// bin `bin` of tile `tile` in the stably partitioned output.  The segment's whole [tiles x 512] count matrix is
+// pulled into shared memory with one round of independent coalesced loads (up to smem_tiles tiles), scanned
+// there column by column, and written back; larger segments walk global memory (2 halves x 512 bins).
 __global__ void __launch_bounds__(1024)
-sort_scan_kernel(int pass, uint32_t* __restrict__ counts, SortPlanView pv) {
+sort_scan_kernel(int pass, uint32_t* __restrict__ counts, int smem_tiles, SortPlanView pv) {
   if (!pv.hdr[kHdrPass + pass]) return;
   const int32_t seg = blockIdx.x;
   if (seg >= pv.hdr[kHdrNseg] || pass >= pv.seg_passes[seg]) return;
+  extern __shared__ uint32_t s_mat[];  // [smem_tiles][kSortBins]
   __shared__ uint32_t half_sum[2][kSortBins];
   __shared__ uint32_t bin_base[kSortBins];
   __shared__ uint32_t warp_tot[kSortBins / 32];
   const int bin = threadIdx.x & (kSortBins - 1);
   const int half = threadIdx.x >> kSortDigitBits;
   const int32_t t0 = pv.seg_tile0[seg], t1 = pv.seg_tile0[seg + 1];
-  const int32_t mid = t0 + (t1 - t0 + 1) / 2;
+  const int32_t nt = t1 - t0;
+  const bool in_smem = nt <= smem_tiles;
+  const int32_t mid = t0 + (nt + 1) / 2;
   const int32_t a = half ? mid : t0, b = half ? t1 : mid;
   uint32_t sum = 0;
+  if (in_smem) {
+    uint32_t* g = counts + (size_t)t0 * kSortBins;
+    for (int i = threadIdx.x; i < nt * kSortBins; i += 1024) s_mat[i] = g[i];
+    __syncthreads();
+    for (int32_t t = a - t0; t < b - t0; ++t) sum += s_mat[t * kSortBins + bin];
+  } else {
 #pragma unroll 8
-  for (int32_t t = a; t < b; ++t) sum += counts[(size_t)t * kSortBins + bin];
+    for (int32_t t = a; t < b; ++t) sum += counts[(size_t)t * kSortBins + bin];
+  }
   half_sum[half][bin] = sum;
   __syncthreads();
   if (half == 0) {  // exclusive scan of the bin totals over the 512 bins
@@ -290,11 +334,22 @@ sort_scan_kernel(int pass, uint32_t* __restrict__ counts, SortPlanView pv) {
   }
   __syncthreads();
   uint32_t run = bin_base[bin] + warp_tot[bin >> 5] + (half ? half_sum[0][bin] : 0);
-  for (int32_t t = a; t < b; ++t) {
-    const size_t i = (size_t)t * kSortBins + bin;
-    const uint32_t c = counts[i];
-    counts[i] = run;
-    run += c;
+  if (in_smem) {
+    for (int32_t t = a - t0; t < b - t0; ++t) {
+      const uint32_t c = s_mat[t * kSortBins + bin];
+      s_mat[t * kSortBins + bin] = run;
+      run += c;
+    }
+    __syncthreads();
+    uint32_t* g = counts + (size_t)t0 * kSortBins;
+    for (int i = threadIdx.x; i < nt * kSortBins; i += 1024) g[i] = s_mat[i];
+  } else {
+    for (int32_t t = a; t < b; ++t) {
+      const size_t i = (size_t)t * kSortBins + bin;
+      const uint32_t c = counts[i];
+      counts[i] = run;
+      run += c;
+    }
   }
 }
 
@@ -422,8 +477,9 @@ SortWs sort_ws_layout(void* ws, int64_t N, int key_bits, int32_t T) {
 
 template <typename K>
 int sort_impl(const void* indices, const void* offsets, bool idx64, const int64_t* hash_size_cumsum,
-              int32_t T, int32_t B, int64_t N, int key_bits, bool payload_is_position, void* sorted_keys,
-              int32_t* sorted_payload, int32_t* bag_of_pos, void* ws, size_t ws_bytes, cudaStream_t s) {
+              int32_t T, int32_t B, int64_t N, int key_bits, int max_table_bits, bool payload_is_position,
+              void* sorted_keys, int32_t* sorted_payload, int32_t* bag_of_pos, void* ws, size_t ws_bytes,
+              cudaStream_t s) {
   const SortWs w = sort_ws_layout(ws, N, key_bits, T);
   if (ws_bytes < w.bytes) return B200_EINVAL;
   K* keys_a = (K*)sorted_keys;
@@ -433,16 +489,25 @@ int sort_impl(const void* indices, const void* offsets, bool idx64, const int64_
   B200_LAUNCH_CHECK();
   const int tiles_per_table = (B + 31) / 32;
   const int64_t ltiles = (int64_t)T * tiles_per_table;
-  tbe_linearize_kernel<K><<<(unsigned)ceil_div(ltiles, 4), 128, 0, s>>>(
+  tbe_linearize_kernel<K><<<(unsigned)ceil_div(ltiles, 4 * kLinTiles), 128, 0, s>>>(
       indices, offsets, idx64, hash_size_cumsum, T, B, tiles_per_table, payload_is_position, keys_a,
       sorted_payload, keys_b, w.pay_b, bag_of_pos, w.pv);
   B200_LAUNCH_CHECK();
-  const int passes = (key_bits + kSortDigitBits - 1) / kSortDigitBits;
-  for (int pass = 0; pass < passes; ++pass) {  // passes no segment needs return at once (plan header)
+  // the host only knows an upper bound of the per-table key width: max_table_bits when the caller has it
+  // (0 = unknown), else key_bits; passes no segment needs return at once (plan header)
+  // the scan holds a segment's count matrix in shared memory when it fits (one segment cannot have more tiles
+  // than the whole problem)
+  int64_t smem_tiles = ceil_div(N, w.tile_size) + 1;
+  if (smem_tiles > 80) smem_tiles = 80;  // 160 KB
+  const size_t scan_smem = (size_t)smem_tiles * kSortBins * sizeof(uint32_t);
+  B200_CUDA_TRY(cudaFuncSetAttribute(sort_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scan_smem));
+  const int host_bits = max_table_bits > 0 && max_table_bits < key_bits ? max_table_bits : key_bits;
+  const int passes = (host_bits + kSortDigitBits - 1) / kSortDigitBits;
+  for (int pass = 0; pass < passes; ++pass) {
     sort_hist_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(keys_a, keys_b, pass, w.tile_size,
                                                                      w.counts, w.pv);
     B200_LAUNCH_CHECK();
-    sort_scan_kernel<<<(unsigned)T, 1024, 0, s>>>(pass, w.counts, w.pv);
+    sort_scan_kernel<<<(unsigned)T, 1024, scan_smem, s>>>(pass, w.counts, (int)smem_tiles, w.pv);
     B200_LAUNCH_CHECK();
     sort_scatter_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(
         keys_a, sorted_payload, keys_b, w.pay_b, pass, w.tile_size, w.counts, w.pv);
@@ -460,21 +525,22 @@ extern "C" size_t b200_tbe_sort_workspace_bytes(int64_t N, int key_bits, int32_t
 
 extern "C" int b200_tbe_sort_indices(const void* indices, const void* offsets, int index_dtype,
                                      const int64_t* hash_size_cumsum, int32_t T, int32_t B,
-                                     int64_t N, int key_bits, int payload_is_position,
-                                     void* sorted_keys, int32_t* sorted_payload,
+                                     int64_t N, int key_bits, int max_table_bits,
+                                     int payload_is_position, void* sorted_keys, int32_t* sorted_payload,
                                      int32_t* bag_of_pos, void* sort_ws, size_t sort_ws_bytes,
                                      void* stream) {
   if (index_dtype != B200_I32 && index_dtype != B200_I64) return B200_EINVAL;
   if (N >= 0x7fffffffLL || key_bits < 1 || key_bits > 64) return B200_EINVAL;
   if (payload_is_position && !bag_of_pos) return B200_EINVAL;
+  if (max_table_bits < 0 || max_table_bits > 64) return B200_EINVAL;
   if (N == 0 || T == 0 || B == 0) return B200_OK;
   const bool idx64 = index_dtype == B200_I64;
   cudaStream_t s = (cudaStream_t)stream;
   if (key_bits > 32)
     return sort_impl<uint64_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
-                               payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                               max_table_bits, payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
                                sort_ws, sort_ws_bytes, s);
   return sort_impl<uint32_t>(indices, offsets, idx64, hash_size_cumsum, T, B, N, key_bits,
-                             payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
+                             max_table_bits, payload_is_position != 0, sorted_keys, sorted_payload, bag_of_pos,
                              sort_ws, sort_ws_bytes, s);
 }

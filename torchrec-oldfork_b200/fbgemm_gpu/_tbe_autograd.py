@@ -29,7 +29,7 @@ _lib.define(
     "int output_dtype) -> Tensor")
 _lib.define(
     "b200_tbe_sort_indices(Tensor indices, Tensor offsets, Tensor hash_size_cumsum, int total_hash_size_bits, "
-    "int B, bool weighted) -> (Tensor, Tensor, Tensor)")
+    "int B, bool weighted, int max_table_bits=0) -> (Tensor, Tensor, Tensor)")
 _lib.define(
     "b200_tbe_backward(Tensor grad_output, Tensor sorted_keys, Tensor sorted_payload, Tensor bag_of_pos, "
     "int total_hash_size_bits, Tensor(a!) dev_weights, Tensor weights_offsets, Tensor D_offsets, "
@@ -51,8 +51,9 @@ def _fwd_cuda(dev_weights, weights_offsets, D_offsets, total_D, max_D, all_D_mul
                            offsets, indice_weights, pooling_mode, _OUT_DT[output_dtype])
 
 
-def _sort_cuda(indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted):
-    s = ops.tbe_sort_indices(indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted)
+def _sort_cuda(indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted, max_table_bits=0):
+    s = ops.tbe_sort_indices(indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted,
+                             max_table_bits)
     bag = s.bag_of_pos if s.bag_of_pos is not None else s.payload.new_empty(0)
     return s.keys, s.payload, bag
 
@@ -109,7 +110,8 @@ class _Lookup(torch.autograd.Function):
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
                     sort_out = torch.ops.fbgemm.b200_tbe_sort_indices(
-                        indices, offsets, m.hash_size_cumsum, m.total_hash_size_bits, B, weighted)
+                        indices, offsets, m.hash_size_cumsum, m.total_hash_size_bits, B, weighted,
+                        getattr(m, "max_table_bits", 0))
                     ev = torch.cuda.Event()
                     ev.record(side)
                 for t in (indices, offsets):
@@ -118,7 +120,8 @@ class _Lookup(torch.autograd.Function):
                     t.record_stream(main)
             else:
                 sort_out = torch.ops.fbgemm.b200_tbe_sort_indices(
-                    indices, offsets, m.hash_size_cumsum, m.total_hash_size_bits, B, weighted)
+                    indices, offsets, m.hash_size_cumsum, m.total_hash_size_bits, B, weighted,
+                        getattr(m, "max_table_bits", 0))
         out = torch.ops.fbgemm.b200_tbe_forward(
             m.weights_dev, m.weights_offsets, m.D_offsets, m.total_D, m.max_D, m._all_D_mult8, indices, offsets,
             int(m.pooling_mode), indice_weights, m.output_dtype)

@@ -170,6 +170,10 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
         self.total_hash_size_bits: int = (
             0 if table_hash_cumsum[-1] == 0 else int(log2(float(table_hash_cumsum[-1])) + 1)
         )
+        # key width of the largest table: a hint for the index transpose (how many radix passes to launch); only
+        # valid when features are grouped by table, i.e. the per-feature hash bases never go back
+        grouped = self.feature_table_map == sorted(self.feature_table_map)
+        self.max_table_bits: int = max((max(r, 1) - 1).bit_length() for r in rows) if grouped and rows else 0
         table_weight_offsets = [0] + list(accumulate(r * d for r, d in zip(rows, dims)))
         i64 = dict(device=dev, dtype=torch.int64)
         self.register_buffer("D_offsets", torch.tensor(D_offsets, device=dev, dtype=torch.int32))
@@ -308,6 +312,8 @@ class _SequenceView:
             return o.seq_D_offsets
         if name == "hash_size_cumsum":
             return o.seq_hash_size_cumsum
+        if name == "max_table_bits":
+            return 0  # one "table" spanning every row: the key width is total_hash_size_bits
         return getattr(o, name)
 
 

@@ -53,17 +53,30 @@ class DefaultDataParallelWrapper(DataParallelWrapper):
         if not any(p.requires_grad for n, p in dmp._dmp_wrapped_module.named_parameters() if n not in ignored):
             return  # sparse-only model (e.g. a bare EmbeddingCollection): nothing is data-parallel
         DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(dmp._dmp_wrapped_module, ignore)
-        import os
-        if (device.type == "cuda" and dist.get_backend(pg) == "nccl" and env.world_size == dist.get_world_size()
-                and os.environ.get("B200_DDP_OWN_PG", "1") != "0"):
-            # The dense gradient all-reduce gets a communicator of its own: on a shared one it queues in front
-            # of the next batch's KJT all-to-alls (one NCCL stream per communicator), and a captured all-reduce
-            # replayed from a CUDA graph must never interleave with eager collectives of the same communicator.
-            pg = dist.new_group(ranks=list(range(env.world_size)), backend="nccl")
-        dmp._dmp_wrapped_module = DistributedDataParallel(
-            module=dmp._dmp_wrapped_module.to(device),
-            device_ids=None if device.type == "cpu" else [device], process_group=pg,
-            gradient_as_bucket_view=True, broadcast_buffers=False, bucket_cap_mb=self._bucket_cap_mb)
+        def build() -> DistributedDataParallel:
+            return DistributedDataParallel(
+                module=dmp._dmp_wrapped_module.to(device),
+                device_ids=None if device.type == "cpu" else [device], process_group=pg,
+                gradient_as_bucket_view=True, broadcast_buffers=False, bucket_cap_mb=self._bucket_cap_mb)
+
+        if device.type == "cuda":
+            # DDP keeps every parameter's AccumulateGrad node alive, and a node runs on the stream that was
+            # current when it was created.  Built on the default (legacy) stream those nodes could never take part
+            # in a CUDA-graph capture of the step (TrainPipelineSparseDist(cuda_graph=True)), so DDP is built on a
+            # side stream, as PyTorch's CUDA-graph notes prescribe.
+            cur = torch.cuda.current_stream(device)
+            side = torch.cuda.Stream(device=device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                dmp._dmp_wrapped_module = build()
+            cur.wait_stream(side)
+            dmp._ddp_stream = side
+            try:  # the stream mismatch between those nodes and their producers is intended
+                torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+            except AttributeError:
+                pass
+        else:
+            dmp._dmp_wrapped_module = build()
 
 
 class DistributedModelParallel(nn.Module, FusedOptimizerModule):

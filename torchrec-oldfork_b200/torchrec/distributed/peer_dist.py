@@ -280,7 +280,8 @@ class _PeerLookup(torch.autograd.Function):
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
                     s = torch.ops.fbgemm.b200_tbe_sort_indices(idx, off, m.hash_size_cumsum,
-                                                               m.total_hash_size_bits, B, False)
+                                                               m.total_hash_size_bits, B, False,
+                                                               getattr(m, "max_table_bits", 0))
                     ev = torch.cuda.Event()
                     ev.record(side)
                 for t in (idx, off):

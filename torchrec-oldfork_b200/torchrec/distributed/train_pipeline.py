@@ -31,9 +31,10 @@ Out = TypeVar("Out")
 # ---------------------------------------------------------------------------------------------
 # CUDA-graph replay of the steady-state step (SURVEY §8 f1 "then CUDA-graph the steady-state step").
 #
-# What is captured: forward, backward (with the fused table update and DDP's gradient all-reduce) and the
-# dense optimizer step of ONE batch whose sparse input distribution has already run.  What stays eager, on
-# its own streams: the host->device copy of batch i+2 and the input distribution of batch i+1 (its
+# What is captured: forward and backward (with the fused table update and the peer-memory exchange) of ONE
+# batch whose sparse input distribution has already run, ending in one flat buffer of dense gradients.  What
+# stays eager: the all-reduce of that buffer and the dense optimizer step (a handful of launches), and, on
+# their own streams, the host->device copy of batch i+2 and the input distribution of batch i+1 (its
 # all-to-alls need the host to read the receive sizes).  Every step the distributed ids of batch i are
 # copied into the graph's fixed input buffers and the graph is replayed: ~300 launches, the cross-rank
 # barriers and the autograd bookkeeping of a step cost the host one cudaGraphLaunch.
@@ -110,7 +111,7 @@ def _tensors(obj, out: list) -> list:
 
 
 class _StepGraph:
-    __slots__ = ("graph", "static", "slots", "output", "launches")
+    __slots__ = ("graph", "static", "slots", "output", "launches", "flat", "group", "grads")
 
 
 def _rank() -> int:
@@ -248,7 +249,9 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         step_in = (self._batch_i, [m._pipelined_inputs[0][1] for m in self._sharded])
         try:
             sig = (_sig(step_in), self._lr_signature())
-        except TypeError:
+        except TypeError as e:
+            import warnings
+            warnings.warn(f"TrainPipelineSparseDist: CUDA-graph mode switched off ({e})")
             self._cuda_graph = False
             return None
         sg = self._graphs.get(sig)
@@ -263,26 +266,50 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
         sg.graph.replay()
         for m in self._sharded:
             m._pipelined_inputs.popleft()
+        # Eager tail: the data-parallel gradient reduction and the dense optimizer.  The all-reduce stays
+        # OUT of the graph on purpose: a captured NCCL kernel replayed from the graph's own stream would run
+        # unordered against the eager all-to-alls of the next batch's input distribution on the same
+        # communicator (and a second communicator deadlocked against the peer barriers when tried).
+        if sg.flat is not None:
+            import torch.distributed as dist
+            dist.all_reduce(sg.flat, group=sg.group)
+            sg.flat.mul_(1.0 / dist.get_world_size(sg.group))
+        for p, g in sg.grads:
+            p.grad = g
+        self._optimizer.step()
         self.graph_replays += 1
         from b200_sparse.ops import KernelProfile
         KernelProfile.launches += sg.launches
         return sg.output
 
     def _capture(self, step_in) -> "_StepGraph":
-        """Captures the step on buffers of its own; capture records without running, so the caller then
-        copies the real inputs in and replays."""
+        """Captures forward + backward (fused table update included) of one step on buffers of its own; capture
+        records without running, so the caller then copies the real inputs in and replays.  The dense
+        gradients are packed into one flat buffer at the end of the graph; under DistributedDataParallel the
+        capture runs in no_sync() mode (its reducer hooks are no-ops) and the caller reduces the flat buffer."""
+        import contextlib
+        import torch.distributed as dist
+        from torch.nn.parallel import DistributedDataParallel
         from b200_sparse.ops import KernelProfile
         sg = _StepGraph()
         sg.static = _static_copy(step_in)
         sg.slots = _tensors(sg.static, [])  # before the capture fills the KJTs' lazy caches
         batch, dist_inputs = sg.static
         ctxs = [m._pipelined_inputs[0][0] for m in self._sharded]
+        ddp = next((m for m in self._model.modules() if isinstance(m, DistributedDataParallel)), None)
+        params = [p for g in self._optimizer.param_groups for p in g["params"]]
         was_profiling, KernelProfile.enabled = KernelProfile.enabled, False  # timing events cannot be captured
         n0 = KernelProfile.launches
         self._optimizer.zero_grad(set_to_none=True)
         torch.cuda.synchronize(self._device)
         sg.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(sg.graph):
+        sg.flat, sg.group = None, None
+        # thread_local: other threads of the process (NCCL watchdog, data loading) keep making CUDA calls that a
+        # "global" capture would treat as errors; everything this step launches goes to capturing streams
+        import os
+        mode = os.environ.get("B200_GRAPH_CAPTURE_MODE", "thread_local")
+        with torch.cuda.graph(sg.graph, capture_error_mode=mode), \
+                (ddp.no_sync() if ddp is not None else contextlib.nullcontext()):
             start = torch.cuda.Event()
             start.record(torch.cuda.current_stream(self._device))
             for m, ctx, d in zip(self._sharded, ctxs, dist_inputs):
@@ -290,7 +317,18 @@ class TrainPipelineSparseDist(TrainPipelineBase[In, Out]):
                 m._pipelined_inputs.appendleft((ctx, d))
             losses, sg.output = self._model(batch)
             torch.sum(losses, dim=0).backward()
-            self._optimizer.step()
+            with_grad = [p for p in params if p.grad is not None]
+            if ddp is not None and with_grad:
+                sg.flat = torch.cat([p.grad.reshape(-1) for p in with_grad])
+        if sg.flat is not None:
+            sg.group = ddp.process_group
+            views, pos = [], 0
+            for p in with_grad:
+                views.append(sg.flat[pos: pos + p.numel()].view_as(p))
+                pos += p.numel()
+            sg.grads = list(zip(with_grad, views))
+        else:
+            sg.grads = [(p, p.grad) for p in with_grad]
         sg.launches = KernelProfile.launches - n0
         KernelProfile.launches = n0
         KernelProfile.enabled = was_profiling

@@ -291,8 +291,9 @@ int b200_relu_bias_grad(const float* grad_out, int64_t grad_out_stride, const fl
 
 /* b200_tbe_forward whose pooled row of global sample b is written to
  * dst_bases[b / B_dst] + (b % B_dst) * dst_pitch + dst_col[t]  (elements of the output dtype).
- * skip_empty != 0: empty bags store nothing (the destination is pre-zeroed; used for the partial sums
- * of row-wise sharding, where a bag is empty on every rank that owns none of its rows). */
+ * skip_empty != 0: empty bags store nothing (used for the partial sums of row-wise sharding, where a bag is
+ * empty on every rank that owns none of its rows).  flag_bases != NULL: every non-empty bag also sets the
+ * byte flag_bases[b / B_dst][(b % B_dst) * flag_pitch + flag_col[t]] for b200_peer_stage_reduce_flagged. */
 int b200_tbe_forward_peer(const void* weights, int weight_dtype, const int64_t* weights_offsets,
                           const int32_t* D_offsets, int32_t T, int32_t B, int32_t total_D,
                           int32_t max_D, int32_t all_D_mult8, const void* indices,
@@ -300,7 +301,8 @@ int b200_tbe_forward_peer(const void* weights, int weight_dtype, const int64_t* 
                           int pooling_mode, void* const* dst_bases /*device [n_dst]*/,
                           int32_t n_dst, int32_t B_dst, int64_t dst_pitch,
                           const int32_t* dst_col /*device [T]*/, int output_dtype,
-                          int32_t skip_empty, void* stream);
+                          int32_t skip_empty, uint8_t* const* flag_bases /*device [n_dst], may be NULL*/,
+                          int64_t flag_pitch, const int32_t* flag_col /*device [T]*/, void* stream);
 
 /* b200_tbe_backward whose gradient row of global sample b is read from
  * grad_bases[b / B_src] + (b % B_src) * grad_stride + src_col[t], scaled by grad_scale
@@ -324,6 +326,15 @@ int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, in
 int b200_peer_stage_reduce(float* stage, int32_t W, int32_t B_local, int32_t Dw, float* out,
                            int64_t out_pitch, const int32_t* out_col4, int32_t clear_stage,
                            void* stream);
+
+/* The same reduction driven by presence flags: flags is [B_local][F][W] bytes (set by the peers'
+ * b200_tbe_forward_peer with flag_pitch = F*W, flag_col[t] = f*W + rank); feature f owns the staged float4
+ * columns [feat_col4[f], feat_col4[f+1]).  Only flagged slots are read (rank order, deterministic), consumed
+ * flags are cleared, the staging data is left as is.  Replaces the dense pass of
+ * reduce_scatter_pooled (comm_ops.py:382) when most (sample, feature, rank) slots are empty.  W <= 32. */
+int b200_peer_stage_reduce_flagged(const float* stage, uint8_t* flags, int32_t W, int32_t B_local,
+                                   int32_t Dw, int32_t F, const int32_t* feat_col4, float* out,
+                                   int64_t out_pitch, const int32_t* out_col4, void* stream);
 
 #ifdef __cplusplus
 }

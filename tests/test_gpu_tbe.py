@@ -474,6 +474,65 @@ def test_peer_stage_reduce(ops):
     assert torch.equal(out2, out) and not st.any()
 
 
+@pytest.mark.parametrize("W,L", [(4, 1), (8, 3), (3, 0)])
+def test_row_wise_exchange_with_presence_flags(ops, W, L):
+    """Row-wise output dist on ONE GPU standing for W ranks (reference reduce_scatter_pooled, comm_ops.py:382):
+    every "rank" r looks up its row block for all W * B_local samples and stores its NON-EMPTY partial bags into
+    slot r of the owning rank's staging buffer, setting flags[b][f][r]; b200_peer_stage_reduce_flagged then sums
+    only flagged slots.  The staging buffers start as garbage (NaN): nothing unflagged may be read.  Result ==
+    the unsharded pooled forward (bit-exact for L <= 1: one contributing rank per bag), flags end up cleared,
+    and a second round over the same buffers (stale data from round one) still matches."""
+    rng = np.random.default_rng(W * 10 + L)
+    rows, dims, B_local = [1000, 37, 5000], [16, 8, 32], 50
+    T, B = len(rows), W * B_local
+    Do = np.concatenate([[0], np.cumsum(dims)]).astype(np.int32)
+    Dw = int(Do[-1])
+    feat_col4 = dev((Do // 4).astype(np.int32))
+    out_col4 = dev(np.arange(0, Dw, 4, dtype=np.int32))
+    stages = [torch.full((W, B_local, Dw), float("nan"), device="cuda") for _ in range(W)]
+    flags = [torch.zeros((B_local, T, W), dtype=torch.uint8, device="cuda") for _ in range(W)]
+    blk = [-(-r // W) for r in rows]
+    tabs = [rng.standard_normal((r, d)).astype(np.float32) for r, d in zip(rows, dims)]
+    for rnd in range(2):
+        if L == 0:
+            lengths = np.zeros(T * B, dtype=np.int64)
+        else:
+            lengths = rng.integers(0, L + 1, size=T * B) if L > 1 else (rng.random(T * B) < 0.8).astype(np.int64)
+        offsets = np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64)
+        idx = np.concatenate([rng.integers(0, rows[t], size=int(lengths[t * B:(t + 1) * B].sum()))
+                              for t in range(T)]).astype(np.int64) if lengths.sum() else np.zeros(0, np.int64)
+        w_full = np.concatenate([x.reshape(-1) for x in tabs])
+        wo_full = np.concatenate([[0], np.cumsum([r * d for r, d in zip(rows, dims)])[:-1]]).astype(np.int64)
+        exp = R.tbe_forward(w_full, wo_full, Do, idx, offsets)
+        bag = np.repeat(np.arange(T * B), lengths)
+        for r in range(W):  # rank r: ids of its row block, rebased (block_bucketize semantics)
+            lo = np.array([blk[t] * r for t in range(T)])
+            keep = (idx // np.array(blk)[bag // B]) == r
+            l_r = np.bincount(bag[keep], minlength=T * B)
+            off_r = np.concatenate([[0], np.cumsum(l_r)]).astype(np.int64)
+            idx_r = (idx[keep] - lo[bag[keep] // B]).astype(np.int64)
+            local = [tabs[t][blk[t] * r: blk[t] * (r + 1)] for t in range(T)]
+            w_r = np.concatenate([x.reshape(-1) for x in local] + [np.zeros(1, np.float32)])
+            wo_r = np.concatenate([[0], np.cumsum([x.size for x in local])[:-1]]).astype(np.int64)
+            stage_bases = torch.tensor([s_.data_ptr() + 4 * r * B_local * Dw for s_ in stages], dtype=torch.int64,
+                                       device="cuda")
+            flag_bases = torch.tensor([f.data_ptr() for f in flags], dtype=torch.int64, device="cuda")
+            flag_col = dev(np.array([t * W + r for t in range(T)], dtype=np.int32))
+            ops.tbe_forward_peer(dev(w_r), dev(wo_r), dev(Do), Dw, max(dims), all(d % 8 == 0 for d in dims),
+                                 dev(idx_r), dev(off_r), None, 0, stage_bases, B_local, Dw, dev(Do[:-1].copy()),
+                                 skip_empty=True, flag_bases=flag_bases, flag_pitch=T * W, flag_col=flag_col)
+        for d_ in range(W):
+            out = torch.full((B_local, Dw), 9.0, device="cuda")
+            ops.peer_stage_reduce_flagged(stages[d_], flags[d_], W, B_local, Dw, feat_col4, out, out_col4)
+            got = out.cpu().numpy()
+            want = exp[d_ * B_local:(d_ + 1) * B_local]
+            if L <= 1:
+                np.testing.assert_array_equal(got, want)
+            else:
+                np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5)
+            assert not bool(flags[d_].any()), "consumed flags must be cleared"
+
+
 # ------------------------------------------------------------------ stochastic rounding (fp16 / bf16 tables)
 @pytest.mark.parametrize("wdt,D,pattern", [
     ("fp16", 32, "unique"),     # packed narrow-row tile (4 lanes per row)

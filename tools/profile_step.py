@@ -85,16 +85,19 @@ def main():
             tp = os.path.join(td, "t.json")
             prof.export_chrome_trace(tp)
             ev = json.load(open(tp))["traceEvents"]
-        rows = [(e["ts"], e.get("dur", 0), e.get("args", {}).get("stream", -1), e.get("cat"), e["name"][:120])
+        launch = {e["args"]["correlation"]: e["ts"] for e in ev
+                  if e.get("cat") == "cuda_runtime" and "correlation" in e.get("args", {})}
+        rows = [(e["ts"], e.get("dur", 0), e.get("args", {}).get("stream", -1), e.get("cat"), e["name"][:120],
+                 e["ts"] - launch.get(e.get("args", {}).get("correlation"), e["ts"]))
                 for e in ev if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
         rows.sort()
         t0 = rows[0][0] if rows else 0
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
         with gzip.open(os.path.join(ROOT, "gpurun_out", f"timeline_n{world}_r{rank}.csv.gz"), "wt", newline="") as f:
             w = csv.writer(f)
-            w.writerow(["start_us", "dur_us", "stream", "cat", "name"])
-            for ts, dur, st, cat, name in rows:
-                w.writerow([round(ts - t0, 1), round(dur, 1), st, cat, name])
+            w.writerow(["start_us", "dur_us", "stream", "cat", "name", "queued_us"])
+            for ts, dur, st, cat, name, q in rows:
+                w.writerow([round(ts - t0, 1), round(dur, 1), st, cat, name, round(q, 1)])
     if rank == 0:
         print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=32, max_name_column_width=60))
         print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=60))

@@ -37,11 +37,12 @@ SIGNATURES = {
     "b200_tbe_forward": (_int, [_p, _int, _p, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _int, _p,
                                 _int, _p, _int, _p]),
     "b200_tbe_forward_peer": (_int, [_p, _int, _p, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _int, _p,
-                                     _int, _p, _i32, _i32, _i64, _p, _int, _i32, _p]),
+                                     _int, _p, _i32, _i32, _i64, _p, _int, _i32, _p, _i64, _p, _p]),
     "b200_tbe_backward_peer": (_int, [_p, _i32, _i32, _i64, _p, _f32, _p, _p, _p, _i64, _int, _p, _int, _p, _p,
                                       _p, _i32, _i32, _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32,
                                       _p, _p]),
     "b200_peer_stage_reduce": (_int, [_p, _i32, _i32, _i32, _p, _i64, _p, _i32, _p]),
+    "b200_peer_stage_reduce_flagged": (_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _i64, _p, _p]),
     "b200_tbe_sort_workspace_bytes": (_sz, [_i64, _int, _i32]),
     "b200_tbe_sort_indices": (_int, [_p, _p, _int, _p, _i32, _i32, _i64, _int, _int, _int, _p, _p, _p, _p,
                                      _sz, _p]),

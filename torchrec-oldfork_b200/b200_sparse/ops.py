@@ -445,10 +445,13 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
 def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets: torch.Tensor,
                      total_D: int, max_D: int, all_D_mult8: bool, indices: torch.Tensor, offsets: torch.Tensor,
                      per_sample_weights: Optional[torch.Tensor], pooling_mode: int, dst_bases: torch.Tensor,
-                     B_dst: int, dst_pitch: int, dst_col: torch.Tensor, skip_empty: bool = False) -> None:
+                     B_dst: int, dst_pitch: int, dst_col: torch.Tensor, skip_empty: bool = False,
+                     flag_bases: Optional[torch.Tensor] = None, flag_pitch: int = 0,
+                     flag_col: Optional[torch.Tensor] = None) -> None:
     """Pooled lookup whose rows go to dst_bases[b // B_dst] (int64 device array of fp32 buffer
     addresses, usually NVLink peer mappings) at row b % B_dst, column dst_col[t].  skip_empty: empty
-    bags store nothing (pre-zeroed destination)."""
+    bags store nothing.  flag_bases (int64 addresses of uint8 buffers) / flag_pitch / flag_col (int32 [T]):
+    non-empty bags also set a presence byte for peer_stage_reduce_flagged."""
     dev = _need_cuda(weights, weights_offsets, D_offsets, indices, offsets, per_sample_weights, dst_bases, dst_col)
     if indices.dtype != offsets.dtype:
         raise TypeError("indices and offsets must share a dtype")
@@ -464,7 +467,8 @@ def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
                                         total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
                                         _p(offsets.contiguous()), idt, _p(per_sample_weights), int(pooling_mode),
                                         _p(dst_bases), dst_bases.numel(), int(B_dst), int(dst_pitch), _p(dst_col),
-                                        _DT[torch.float32], int(bool(skip_empty)), _stream(dev)),
+                                        _DT[torch.float32], int(bool(skip_empty)), _p(flag_bases),
+                                        int(flag_pitch), _p(flag_col), _stream(dev)),
               "b200_tbe_forward_peer")
 
 
@@ -506,6 +510,23 @@ def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: t
         check(lib.b200_peer_stage_reduce(_p(stage), int(W), int(B_local), int(Dw), _p(out), out.stride(0),
                                          _p(out_col4), int(bool(clear_stage)), _stream(dev)),
               "b200_peer_stage_reduce")
+
+
+def peer_stage_reduce_flagged(stage: torch.Tensor, flags: torch.Tensor, W: int, B_local: int, Dw: int,
+                              feat_col4: torch.Tensor, out: torch.Tensor, out_col4: torch.Tensor) -> None:
+    """Sum of the FLAGGED rank slots of stage ([W, B_local, Dw] fp32); flags is uint8 [B_local, F, W] and is
+    cleared where consumed; feat_col4 (int32 [F + 1]) gives every feature's staged float4 columns."""
+    dev = _need_cuda(stage, flags, feat_col4, out, out_col4)
+    F = feat_col4.numel() - 1
+    if flags.dtype != torch.uint8 or flags.numel() != B_local * F * W:
+        raise TypeError("flags must be uint8 [B_local, F, W]")
+    if out_col4.dtype != torch.int32 or out_col4.numel() != Dw // 4 or feat_col4.dtype != torch.int32:
+        raise TypeError("out_col4 / feat_col4 must be int32 with Dw // 4 / F + 1 entries")
+    with torch.cuda.device(dev):
+        KernelProfile.launches += 1
+        check(lib.b200_peer_stage_reduce_flagged(_p(stage), _p(flags), int(W), int(B_local), int(Dw), int(F),
+                                                 _p(feat_col4), _p(out), out.stride(0), _p(out_col4),
+                                                 _stream(dev)), "b200_peer_stage_reduce_flagged")
 
 
 # ------------------------------------------------------------------------ dot interaction

@@ -215,6 +215,60 @@ peer_stage_reduce_kernel(float* __restrict__ stage, int32_t W, int64_t rows, int
 }
 }  // namespace b200
 
+// Flag-driven variant: flags[b][f][r] != 0 says that rank r stored a partial sum for feature f of sample b.
+// One warp per (sample, feature): it reads the W flag bytes, adds only the flagged slots in rank order
+// (deterministic), clears the flags it consumed and writes the pooled row.  The staging data itself is never
+// cleared - unflagged slots are simply not read - so the pass moves ~1/W of the staging buffer when bags
+// have one id.
+namespace b200 {
+__global__ void __launch_bounds__(256)
+peer_stage_reduce_flagged_kernel(const float* __restrict__ stage, uint8_t* __restrict__ flags, int32_t W,
+                                 int64_t rows, int32_t F, int32_t Dw4,
+                                 const int32_t* __restrict__ feat_col4, float* __restrict__ out,
+                                 int64_t pitch, const int32_t* __restrict__ out_col4) {
+  const int lane = threadIdx.x & 31;
+  const int64_t pair = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (pair >= rows * F) return;
+  const int64_t b = pair / F;
+  const int f = (int)(pair - b * F);
+  uint8_t* fl = flags + pair * W;
+  unsigned mask = 0;
+  if (lane < W) mask = fl[lane] ? 1u : 0u;
+  mask = __ballot_sync(kFull, mask != 0);
+  if (lane < W && ((mask >> lane) & 1u)) fl[lane] = 0;
+  const int c0 = feat_col4[f], c1 = feat_col4[f + 1];
+  const int64_t slot = rows * Dw4;  // float4s per rank slot
+  for (int c = c0 + lane; c < c1; c += 32) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (unsigned m = mask; m; m &= m - 1) {
+      const int r = __ffs(m) - 1;
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(stage) + (int64_t)r * slot + b * Dw4 + c);
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
+    }
+    *reinterpret_cast<float4*>(out + b * pitch + out_col4[c]) = acc;
+  }
+}
+}  // namespace b200
+
+extern "C" int b200_peer_stage_reduce_flagged(const float* stage, uint8_t* flags, int32_t W,
+                                              int32_t B_local, int32_t Dw, int32_t F,
+                                              const int32_t* feat_col4, float* out, int64_t out_pitch,
+                                              const int32_t* out_col4, void* stream) {
+  using namespace b200;
+  if (W <= 0 || W > 32 || B_local < 0 || Dw < 0 || (Dw & 3) || (out_pitch & 3) || F <= 0 || !out_col4 ||
+      !feat_col4 || !flags)
+    return B200_EINVAL;
+  if (B_local == 0 || Dw == 0) return B200_OK;
+  const int64_t warps = (int64_t)B_local * F;
+  peer_stage_reduce_flagged_kernel<<<(unsigned)ceil_div(warps, 8), 256, 0, (cudaStream_t)stream>>>(
+      stage, flags, W, B_local, F, Dw >> 2, feat_col4, out, out_pitch, out_col4);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 extern "C" int b200_peer_stage_reduce(float* stage, int32_t W, int32_t B_local, int32_t Dw,
                                       float* out, int64_t out_pitch, const int32_t* out_col4,
                                       int32_t clear_stage, void* stream) {

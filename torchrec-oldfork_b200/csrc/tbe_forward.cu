@@ -78,7 +78,13 @@ struct FwdPeerDst {
   const int32_t* col;
   int64_t pitch;
   int32_t B_dst;
-  int32_t skip_empty;  // destination is pre-zeroed: empty bags store nothing (row-wise partial sums)
+  int32_t skip_empty;  // empty bags store nothing (row-wise partial sums)
+  // Optional presence flags (row-wise sharding): every NON-EMPTY bag also sets the byte
+  // flag_bases[b / B_dst][(b % B_dst) * flag_pitch + flag_col[t]], so that the reduction on the destination reads
+  // only the slots that were written (with one id per bag that is 1/W of the staging buffer).
+  uint8_t* const* flag_bases;
+  const int32_t* flag_col;
+  int64_t flag_pitch;
 };
 
 template <typename W, typename O, int EPV, int NV, bool PEER>
@@ -115,6 +121,13 @@ tbe_forward_kernel(const W* __restrict__ weights, const int64_t* __restrict__ we
   unsigned remaining = __ballot_sync(kFull, in_tile && rel_end > rel_start);
   const unsigned empty = __ballot_sync(kFull, in_tile && rel_end <= rel_start);
 
+  if constexpr (PEER) {
+    if (peer.flag_bases != nullptr && in_tile && rel_end > rel_start) {
+      const int b = b0 + lane;
+      const int r = b / peer.B_dst;
+      peer.flag_bases[r][(int64_t)(b - r * peer.B_dst) * peer.flag_pitch + peer.flag_col[t]] = 1;
+    }
+  }
   O* __restrict__ out_tile = PEER ? nullptr : out + (int64_t)b0 * total_D + D_begin + EPV * lane;
   const int peer_col = PEER ? peer.col[t] + EPV * lane : 0;
   auto row_ptr = [&](int bag) -> O* {
@@ -392,11 +405,15 @@ extern "C" int b200_tbe_forward_peer(const void* weights, int weight_dtype,
                                      int index_dtype, const float* per_sample_weights,
                                      int pooling_mode, void* const* dst_bases, int32_t n_dst,
                                      int32_t B_dst, int64_t dst_pitch, const int32_t* dst_col,
-                                     int output_dtype, int32_t skip_empty, void* stream) {
+                                     int output_dtype, int32_t skip_empty,
+                                     uint8_t* const* flag_bases, int64_t flag_pitch,
+                                     const int32_t* flag_col, void* stream) {
   if (!dst_bases || !dst_col || n_dst <= 0 || B_dst <= 0 || (int64_t)n_dst * B_dst < B ||
       (dst_pitch & 3))
     return B200_EINVAL;
-  b200::FwdPeerDst peer{dst_bases, dst_col, dst_pitch, B_dst, skip_empty ? 1 : 0};
+  if (flag_bases && (!flag_col || flag_pitch <= 0)) return B200_EINVAL;
+  b200::FwdPeerDst peer{dst_bases, dst_col, dst_pitch, B_dst, skip_empty ? 1 : 0,
+                        flag_bases, flag_col, flag_pitch};
   return tbe_forward_impl(weights, weight_dtype, weights_offsets, D_offsets, T, B, total_D, max_D,
                           all_D_mult8, indices, offsets, index_dtype, per_sample_weights,
                           pooling_mode, nullptr, output_dtype, &peer, stream);

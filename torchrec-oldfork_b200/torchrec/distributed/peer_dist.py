@@ -53,7 +53,8 @@ class PeerExchange:
 
     def __init__(self, pg: dist.ProcessGroup, device: torch.device, B_local: int, total_D: int, rw_dim: int,
                  feat_cols: Optional[List[Tuple[int, int]]] = None,
-                 tw_map: Optional[List[Optional[Tuple[int, int]]]] = None, tw_pitch: int = 0) -> None:
+                 tw_map: Optional[List[Optional[Tuple[int, int]]]] = None, tw_pitch: int = 0,
+                 rw_features: int = 0) -> None:
         import torch.distributed._symmetric_memory as symm_mem
         self.W, self.rank = dist.get_world_size(pg), dist.get_rank(pg)
         self.B_local, self.total_D, self.rw_dim = B_local, total_D, rw_dim
@@ -63,8 +64,8 @@ class PeerExchange:
         except Exception:  # newer torch: rendezvous does it
             pass
 
-        def make(shape) -> Tuple[torch.Tensor, object, torch.Tensor]:
-            t = symm_mem.empty(shape, dtype=torch.float32, device=device)
+        def make(shape, dtype=torch.float32) -> Tuple[torch.Tensor, object, torch.Tensor]:
+            t = symm_mem.empty(shape, dtype=dtype, device=device)
             h = symm_mem.rendezvous(t, gname)
             ptrs = [int(p) for p in h.buffer_ptrs]
             return t, h, ptrs
@@ -106,6 +107,14 @@ class PeerExchange:
             self.stage.zero_()
             slot = self.rank * B_local * rw_dim * 4  # my slot in every destination's staging buffer
             self.stage_bases = torch.tensor([p + slot for p in st_ptrs], dtype=torch.int64, device=device)
+        # presence flags [B_local, F_rw, W]: peers set flags[b][f][their rank] next to a stored partial row and
+        # the reduction reads only flagged slots (B200_PEER_FLAGS=0: the dense reduce over all W slots)
+        self.flags = self.flag_bases = None
+        self.rw_features = rw_features
+        if rw_dim > 0 and rw_features > 0 and self.W <= 32 and os.environ.get("B200_PEER_FLAGS", "1") != "0":
+            self.flags, self._h_flags, fl_ptrs = make((B_local, rw_features, self.W), torch.uint8)
+            self.flags.zero_()
+            self.flag_bases = torch.tensor(fl_ptrs, dtype=torch.int64, device=device)
 
         # True after a backward pass: its barrier C already proves that every rank is done with the
         # buffers of that step, so the next forward may skip barrier A (see _PeerLookup.forward)
@@ -130,12 +139,13 @@ class PeerExchange:
 class _Part:
     """One table-batched lookup module with its column maps."""
 
-    __slots__ = ("tbe", "row_wise", "dst_col", "src_col", "n_features", "gin_col")
+    __slots__ = ("tbe", "row_wise", "dst_col", "src_col", "n_features", "gin_col", "flag_col")
 
     def __init__(self, tbe, row_wise: bool, dst_col: torch.Tensor, src_col: torch.Tensor, n_features: int,
                  gin_col: Optional[torch.Tensor] = None) -> None:
         self.tbe, self.row_wise, self.dst_col, self.src_col, self.n_features = tbe, row_wise, dst_col, src_col, n_features
         self.gin_col = gin_col  # table-wise: this module's feature columns inside my gin buffer
+        self.flag_col: Optional[torch.Tensor] = None  # row-wise: f * W + my rank for each of its features
 
 
 class PeerLookupDist:
@@ -171,6 +181,8 @@ class PeerLookupDist:
         self._tw_pitch = 0
         self._rw_dim = 0
         self._rw_col4: Optional[torch.Tensor] = None
+        self._rw_feat_col4: Optional[torch.Tensor] = None
+        self._rw_features = 0
 
         def cols(names: List[str]) -> torch.Tensor:
             return torch.tensor([col_of[n] for n in names], dtype=torch.int32, device=device)
@@ -206,15 +218,25 @@ class PeerLookupDist:
                     raise NotImplementedError("one row-wise sharding per module")
                 local0 = 0
                 chunk_cols: List[int] = []
+                feat_col4: List[int] = [0]
+                # the feature numbering of the presence flags must be the same on every rank: the row-wise
+                # features of ALL ranks' modules are the same list (every rank holds a row block of each table)
                 for m in mods:
                     stage_cols = (m.emb_module.D_offsets[:-1] + local0).to(torch.int32)
                     names = m.config.embedding_names()
-                    parts.append(_Part(m.emb_module, True, stage_cols, cols(names), m.config.num_features()))
+                    part = _Part(m.emb_module, True, stage_cols, cols(names), m.config.num_features())
+                    f0 = len(feat_col4) - 1
+                    part.flag_col = torch.tensor([(f0 + k) * self._W + self._rank for k in range(len(names))],
+                                                 dtype=torch.int32, device=device)
+                    parts.append(part)
                     for n, d in zip(names, m.config.embedding_dims()):
                         chunk_cols.extend(col_of[n] + 4 * k for k in range(d // 4))
+                        feat_col4.append(feat_col4[-1] + d // 4)
                     local0 += m.emb_module.total_D
                 self._rw_dim = local0
                 self._rw_col4 = torch.tensor(chunk_cols, dtype=torch.int32, device=device)
+                self._rw_feat_col4 = torch.tensor(feat_col4, dtype=torch.int32, device=device)
+                self._rw_features = len(feat_col4) - 1
             else:
                 raise NotImplementedError(type(sharding).__name__)
             self._parts.append(parts)
@@ -236,7 +258,7 @@ class PeerLookupDist:
                 c0 += d
             tw_map = [self._tw_of.get(n) for n in self.embedding_names]
             px = PeerExchange(self._pg, self._device, B_local, self._total_D, self._rw_dim, feat_cols, tw_map,
-                              self._tw_pitch)
+                              self._tw_pitch, self._rw_features)
             self._exchanges[B_local] = px
         return px
 
@@ -305,11 +327,17 @@ class _PeerLookup(torch.autograd.Function):
             pitch = px.rw_dim if p.row_wise else px.total_D
             _b200.tbe_forward_peer(m.weights_dev, m.weights_offsets, m.D_offsets, m.total_D, m.max_D,
                                    m._all_D_mult8, idx, off, None, int(m.pooling_mode), bases, px.B_local, pitch,
-                                   p.dst_col, skip_empty=p.row_wise)
+                                   p.dst_col, skip_empty=p.row_wise,
+                                   flag_bases=px.flag_bases if p.row_wise else None,
+                                   flag_pitch=px.rw_features * px.W, flag_col=p.flag_col if p.row_wise else None)
         px.barrier()  # B: all peer stores have landed
         if px.stage is not None:
-            _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4,
-                                    clear_stage=True)
+            if px.flags is not None:
+                _b200.peer_stage_reduce_flagged(px.stage, px.flags, px.W, px.B_local, px.rw_dim,
+                                                owner._rw_feat_col4, px.out, owner._rw_col4)
+            else:
+                _b200.peer_stage_reduce(px.stage, px.W, px.B_local, px.rw_dim, px.out, owner._rw_col4,
+                                        clear_stage=True)
         ctx.px, ctx.work, ctx.sorts = px, work, sorts
         if not need_grad:
             return px.out.clone()  # evaluation: the caller may keep it across further forwards

@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=65536, help="local batch per GPU")
     ap.add_argument("--row-cap", type=int, default=40000000)
-    ap.add_argument("--cpu-batch", type=int, default=8192, help="batch of the bounded CPU sample")
+    ap.add_argument("--cpu-batch", type=int, default=65536, help="batch of the bounded CPU sample")
     ap.add_argument("--cpu-row-cap", type=int, default=1000000, help="row cap of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cuda-graph", type=int, default=int(os.environ.get("B200_CUDA_GRAPH", "0")),
@@ -118,29 +118,43 @@ def table_configs(rows):
 
 
 # ------------------------------------------------------------------------------------------
-# CPU arm: the reference algorithm on the host cores (oracle port; bounded sample)
-class CpuDLRM:
-    """DLRM train step on the CPU: torch MLPs + the oracle's C restatement of the reference's CPU
-    pooled lookup / fused rowwise-Adagrad backward (oracle/tbe_ref.c) + the reference's bmm/triu
-    interaction formulation (torchrec/models/dlrm.py:193-219)."""
+# CPU arm: the reference's own CPU embedding kernels on the host cores.  Nothing of the product is imported
+# here (no torchrec-oldfork_b200 module, no libb200sparse.so): torch.nn for the dense layers, oracle/ for the
+# sparse path.
+def _cpu_mlp(sizes):
+    layers = []
+    for i, o in zip(sizes[:-1], sizes[1:]):
+        layers += [torch.nn.Linear(i, o), torch.nn.ReLU()]
+    return torch.nn.Sequential(*layers)
 
-    def __init__(self, rows, batch: int, seed: int = 0) -> None:
+
+class CpuDLRM:
+    """DLRM train step on the CPU: torch.nn MLPs + the reference's CPU pooled lookup / fused rowwise-Adagrad
+    backward - FBGEMM's JIT EmbeddingSpMDM and sparse-Adagrad kernels driven as
+    embedding_forward_split_cpu.cpp:71-116 and embedding_backward_split_cpu_template.cpp:125-182 drive them
+    (oracle/_ref/libfbgemm_tbe_ref.so; kind "reference") - or, when that library is absent, the oracle's C
+    restatement (kind "port") + the reference's bmm/triu interaction (torchrec/models/dlrm.py:193-219)."""
+
+    def __init__(self, rows, batch: int, dim: int = EMB_DIM, dense_arch=None, over_arch=None, seed: int = 0) -> None:
         from oracle import c_oracle
         self.c = c_oracle
-        self.c.lib()
+        self.kind = "reference" if c_oracle.tbe_ref_lib() is not None else "port"
+        if self.kind == "port":
+            self.c.lib()
         torch.manual_seed(seed)
-        self.rows, self.B, self.T, self.D = rows, batch, len(rows), EMB_DIM
+        dense_arch = dense_arch or DENSE_ARCH
+        over_arch = over_arch or OVER_ARCH
+        self.rows, self.B, self.T, self.D = list(rows), batch, len(rows), dim
         rng = np.random.default_rng(seed)
         self.hsc = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
         self.wo = (self.hsc[:-1] * self.D).astype(np.int64)
         self.Do = np.arange(0, (self.T + 1) * self.D, self.D, dtype=np.int32)
         self.weights = (rng.random(int(self.hsc[-1]) * self.D, dtype=np.float32) - 0.5) * 0.02
         self.mom = np.zeros(int(self.hsc[-1]), dtype=np.float32)
-        from torchrec.modules.mlp import MLP
         n = self.T + 1
-        self.dense = MLP(DENSE_IN, DENSE_ARCH)
-        self.over = torch.nn.Sequential(MLP(self.D + n * (n - 1) // 2, OVER_ARCH[:-1]),
-                                        torch.nn.Linear(OVER_ARCH[-2], OVER_ARCH[-1]))
+        self.dense = _cpu_mlp([DENSE_IN] + list(dense_arch))
+        self.over = torch.nn.Sequential(_cpu_mlp([self.D + n * (n - 1) // 2] + list(over_arch[:-1])),
+                                        torch.nn.Linear(over_arch[-2], over_arch[-1]))
         self.opt = torch.optim.SGD(list(self.dense.parameters()) + list(self.over.parameters()), lr=0.1)
         self.triu = torch.triu_indices(n, n, offset=1)
         self.loss_fn = torch.nn.BCEWithLogitsLoss()
@@ -153,7 +167,10 @@ class CpuDLRM:
 
     def step(self, i: int) -> float:
         idx, off, dense_in, labels = self.batches[i % len(self.batches)]
-        pooled = self.c.tbe_forward(self.weights, self.wo, self.Do, idx, off)
+        if self.kind == "reference":
+            pooled = self.c.ref_tbe_forward(self.weights, self.wo, self.Do, self.rows, idx, off)
+        else:
+            pooled = self.c.tbe_forward(self.weights, self.wo, self.Do, idx, off)
         sparse = torch.from_numpy(pooled).view(self.B, self.T, self.D).requires_grad_(True)
         self.opt.zero_grad(set_to_none=True)
         d = self.dense(dense_in)
@@ -163,45 +180,76 @@ class CpuDLRM:
         loss = self.loss_fn(self.over(inter).squeeze(), labels)
         loss.backward()
         self.opt.step()
-        self.c.tbe_backward(sparse.grad.view(self.B, self.T * self.D).numpy(), self.weights, self.wo, self.Do,
-                            self.hsc, idx, off, "rowwise_adagrad", LR, EPS, self.mom, self.hsc[:-1])
+        grad = sparse.grad.view(self.B, self.T * self.D).numpy()
+        if self.kind == "reference":
+            self.c.ref_tbe_backward_rowwise_adagrad(grad, self.weights, self.wo, self.Do, self.rows, idx, off, LR, EPS,
+                                                    self.mom, self.hsc[:-1])
+        else:
+            self.c.tbe_backward(grad, self.weights, self.wo, self.Do, self.hsc, idx, off, "rowwise_adagrad", LR, EPS,
+                                self.mom, self.hsc[:-1])
         return float(loss.detach())
+
+
+def _time_cpu_model(model: "CpuDLRM", steps: int, warmup: int) -> float:
+    for i in range(warmup):  # the first calls JIT the FBGEMM kernels and first-touch the tables
+        model.step(i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        model.step(i)
+    return (time.perf_counter() - t0) / steps
 
 
 def time_cpu_arm(args, steps: int, warmup: int) -> dict:
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
     rows = [min(r, args.cpu_row_cap) for r in CRITEO_ROWS]
     model = CpuDLRM(rows, args.cpu_batch)
-    for i in range(warmup):
-        model.step(i)
-    t0 = time.perf_counter()
-    for i in range(steps):
-        model.step(i)
-    dt = time.perf_counter() - t0
-    return {"value": args.cpu_batch * steps / dt, "unit": "samples/s", "cores": cores, "kind": "port",
-            "ms_per_step": dt / steps * 1e3,
-            "sample": f"same DLRM step, batch {args.cpu_batch}, tables row-capped at {args.cpu_row_cap}, "
-                      f"{steps} steps after {warmup} warm-up, oracle/tbe_ref.c (OpenMP) + torch CPU MLPs"}
+    dt = _time_cpu_model(model, steps, warmup)
+    what = ("the reference's FBGEMM JIT CPU kernels (EmbeddingSpMDM + rowwise sparse Adagrad, oracle/_ref)"
+            if model.kind == "reference" else "oracle/tbe_ref.c (OpenMP restatement)")
+    return {"value": args.cpu_batch / dt, "unit": "samples/s", "cores": cores, "kind": model.kind,
+            "ms_per_step": dt * 1e3,
+            "sample": f"same DLRM step (dense 512-256-128, over 1024-1024-512-256-1, fp32), batch {args.cpu_batch}, "
+                      f"26 tables row-capped at {args.cpu_row_cap} (host memory), {steps} steps after {warmup} "
+                      f"warm-up; sparse path: {what}; dense layers: torch.nn on {cores} threads"}
+
+
+def time_cpu_cfg1(steps: int = 6, warmup: int = 2) -> dict:
+    """BASELINE.json configs[0]: the reference's CPU-runnable example - 26 Criteo-Kaggle-shaped tables capped at
+    100 k rows, dim 64, batch 2048, dense 512-256-64, over 512-512-256-1 (examples/dlrm/dlrm_main.py:107-124)."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    kaggle = [1460, 583, 10131227, 2202608, 305, 24, 12517, 633, 3, 93145, 5683, 8351593, 3194, 27, 14992, 5461306,
+              10, 5652, 2173, 4, 7046547, 18, 15, 286181, 105, 142572]
+    rows = [min(r, 100_000) for r in kaggle]
+    model = CpuDLRM(rows, 2048, dim=64, dense_arch=[512, 256, 64], over_arch=[512, 512, 256, 1])
+    dt = _time_cpu_model(model, steps, warmup)
+    return {"value": 2048 / dt, "unit": "samples/s", "ms_per_step": dt * 1e3, "cores": cores, "kind": model.kind,
+            "sample": "configs[0]: 26 tables capped at 100k rows, dim 64, batch 2048, whole DLRM train step on CPU"}
 
 
 def run_reference(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = min(args.steps, 10)
-    r = time_cpu_arm(args, steps, max(2, min(args.warmup, 3)))
+    warmup = max(args.warmup, 1)
+    r = time_cpu_arm(args, args.steps, warmup)
     line = {
         "impl": "reference", "metric": "dlrm_train_samples_per_sec", "value": r["value"], "unit": "samples/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": max(2, min(args.warmup, 3)), "ms_per_step": r["ms_per_step"],
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": warmup, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "DLRM Criteo-1TB (MLPerf) shape, 26 tables dim 128 fp32, fused rowwise Adagrad; "
-                               "reference CPU algorithm on host cores over a bounded sample", "sample": r["sample"]},
+        "config": {"workload": "DLRM Criteo-1TB (MLPerf) shape, 26 tables dim 128 fp32, fused rowwise Adagrad, "
+                               "batch %d; the reference's CPU implementation of the path on the host cores over a "
+                               "bounded sample (tables row-capped to fit host memory)" % args.cpu_batch,
+                   "sample": r["sample"]},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    try:
+        line["cpu_baseline_cfg1"] = time_cpu_cfg1()
+    except Exception as e:  # a reported extra, never a reason to lose the line
+        line["cpu_baseline_cfg1"] = {"value": None, "sample": f"failed: {e}"}
     print(json.dumps(line))
 
 
@@ -358,31 +406,69 @@ def run_ours(args) -> None:
     peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
     alg = [algorithmic_bytes(n, b, t, EMB_DIM, u) for (n, b, t, u) in shapes]
     calls_per_step = max(1, len(shapes))
-    roof = {}
-    kernels = {}
-    for name, key in (("tbe_backward", "bwd"), ("tbe_forward", "fwd")):
-        if name in kern and alg:
-            cnt, mean_ms = kern[name]
-            per_step_bytes = sum(a[key] for a in alg)
-            per_step_ms = mean_ms * calls_per_step
-            kernels[name] = {"launch_groups_per_step": calls_per_step, "mean_ms_per_call": mean_ms,
-                             "algorithmic_bytes_per_step": per_step_bytes,
-                             "achieved_gbs": per_step_bytes / per_step_ms / 1e6}
-    for name in ("tbe_sort", "interaction_forward", "interaction_backward"):
-        if name in kern:
-            kernels[name] = {"mean_ms_per_call": kern[name][1]}
-    traffic = None
-    try:  # DRAM bytes per launch from the committed ncu capture (only valid for the cfg2 shape at N=1)
+    # DRAM bytes per launch from this round's `ncu --set full` capture of the same command (profiles/r2_traffic.json,
+    # produced by tools/summarize_ncu.py); only valid for the cfg2 shape at N = 1, else null
+    traffic_of = {}
+    try:
         if world == 1 and args.batch == 65536 and args.row_cap == 40_000_000:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["tbe_backward_tile_kernel"]
+            traffic_of = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
     except Exception:
-        traffic = None
-    if "tbe_backward" in kernels:
-        k = kernels["tbe_backward"]
-        roof = {"kernel": "tbe_backward_tile_kernel (+combine) — fused segment-reduce + rowwise Adagrad",
-                "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                "frac": k["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_step"] // calls_per_step}
+        traffic_of = {}
+    F = len(CRITEO_ROWS)
+    ix_fwd_bytes = args.batch * (F + 1) * EMB_DIM * 4 + args.batch * (EMB_DIM + F * (F + 1) // 2) * 4
+    ix_bwd_bytes = args.batch * ((EMB_DIM + F * (F + 1) // 2 + 1) * 4 + 2 * (F + 1) * EMB_DIM * 4)
+    per_step_bytes = {
+        "tbe_forward": sum(a["fwd"] for a in alg) if alg else None,
+        "tbe_backward": sum(a["bwd"] for a in alg) if alg else None,
+        "tbe_sort": 0,  # the index transpose moves no algorithmic bytes: it is charged as time only
+        "interaction_forward": ix_fwd_bytes,
+        "interaction_backward": ix_bwd_bytes,
+    }
+    ncu_name = {"tbe_forward": "tbe_forward_kernel", "tbe_backward": "tbe_backward_tile_kernel",
+                "tbe_sort": "sort_scatter_kernel", "interaction_forward": "interaction_forward_mma_kernel",
+                "interaction_backward": "interaction_backward_mma_kernel"}
+    kernels = {}
+    for name, nbytes in per_step_bytes.items():
+        if name not in kern:
+            continue
+        cnt, mean_ms = kern[name]
+        calls = calls_per_step if name.startswith("tbe_") else 1
+        per_step_ms = mean_ms * calls
+        k = {"calls_per_step": calls, "mean_ms_per_call": mean_ms, "ms_per_step": per_step_ms,
+             "algorithmic_bytes_per_step": nbytes}
+        if nbytes:
+            k["achieved_gbs"] = nbytes / per_step_ms / 1e6
+            k["frac_of_peak"] = k["achieved_gbs"] / peak
+        k["traffic"] = traffic_of.get(ncu_name[name])
+        kernels[name] = k
+
+    def roofline_of(name, label):
+        k = kernels[name]
+        return {"kernel": label, "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                "frac": k["frac_of_peak"], "traffic": k["traffic"], "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": k["algorithmic_bytes_per_step"] // k["calls_per_step"],
+                "ms_per_launch": k["mean_ms_per_call"]}
+
+    labels = {"tbe_forward": "tbe_forward_kernel - pooled lookup",
+              "tbe_backward": "tbe_backward_tile_kernel (+combine) - fused segment-reduce + rowwise Adagrad",
+              "interaction_forward": "interaction_forward_mma_kernel - dot interaction",
+              "interaction_backward": "interaction_backward_mma_kernel - dot interaction backward"}
+    rooflines = {n: roofline_of(n, lab) for n, lab in labels.items() if n in kernels}
+    # the BASELINE metric's second half: pooled-lookup forward + index transpose + fused backward as ONE figure,
+    # the transpose's time included (it moves no algorithmic bytes)
+    if all(n in kernels for n in ("tbe_forward", "tbe_backward", "tbe_sort")):
+        ms = sum(kernels[n]["ms_per_step"] for n in ("tbe_forward", "tbe_sort", "tbe_backward"))
+        nb = kernels["tbe_forward"]["algorithmic_bytes_per_step"] + kernels["tbe_backward"]["algorithmic_bytes_per_step"]
+        rooflines["tbe_fwd+transpose+bwd"] = {
+            "kernel": "lookup forward + index transpose + fused backward (sum of the three)", "bound": "hbm",
+            "achieved": nb / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": nb / ms / 1e6 / peak, "traffic": None,
+            "peak_source": peak_src, "ms_per_step": ms, "frac_of_nominal_8TBs": nb / ms / 1e6 / 8000.0,
+            "note": "the transpose runs on a side stream beside the forward; its in-step duration is charged in full"}
+    # top-level `roofline`: the repo kernel with the longest in-step duration
+    roof = {}
+    if rooflines:
+        dominant = max((n for n in labels if n in kernels), key=lambda n: kernels[n]["ms_per_step"])
+        roof = dict(rooflines[dominant])
     line = {
         "metric": "dlrm_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
@@ -398,13 +484,14 @@ def run_ours(args) -> None:
         },
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": batch_bytes(host_batches[0]) * world, "d2h_bytes_per_step": 4 * world},
-        "gpu_launches": launches, "clocks": clocks, "roofline": roof, "kernels": kernels,
+        "gpu_launches": launches, "clocks": clocks, "roofline": roof, "rooflines": rooflines, "kernels": kernels,
         "cuda_graph": {"enabled": bool(args.cuda_graph), "replays": int(getattr(pipe, "graph_replays", 0))},
     }
     if world == 1 and not args.no_cpu_baseline:
         try:
             r = time_cpu_arm(args, 4, 2)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline_cfg1"] = time_cpu_cfg1()
         except Exception as e:  # the baseline is a reported number, never a reason to lose the bench line
             line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"failed: {e}"}

@@ -155,3 +155,48 @@ def ref_quantize_sbhalf(w, bit_rate=8, dispatch=False):
     (q.ref_quantize_sbhalf if dispatch else q.ref_quantize_sbhalf_ref)(
         bit_rate, _ptr(x, C.c_float), rows, cols, _ptr(out, C.c_uint8))
     return out
+
+
+TBE_REF_LIB = os.path.join(HERE, "_ref", "libfbgemm_tbe_ref.so")
+_tbe_ref = None
+
+
+def tbe_ref_lib():
+    """The reference's own JIT CPU embedding kernels behind oracle/ref_tbe_harness.cc, or None when not built."""
+    global _tbe_ref
+    if _tbe_ref is None and os.path.exists(TBE_REF_LIB):
+        _tbe_ref = C.CDLL(TBE_REF_LIB)
+    return _tbe_ref
+
+
+def ref_tbe_forward(weights, weights_offsets, D_offsets, rows, indices, offsets, psw=None, mean=False):
+    """embedding_forward_split_cpu.cpp:71-116 through FBGEMM's GenerateEmbeddingSpMDMWithStrides kernels."""
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    w, wo, Do = _c(weights, np.float32), _c(weights_offsets, np.int64), _c(D_offsets, np.int32)
+    idx, off, pw, rr = _c(indices, np.int64), _c(offsets, np.int64), _c(psw, np.float32), _c(rows, np.int64)
+    out = np.zeros((B, int(Do[-1])), dtype=np.float32)
+    ok = tbe_ref_lib().ref_tbe_forward_f32(
+        _ptr(w, C.c_float), _ptr(wo, C.c_int64), _ptr(Do, C.c_int32), _ptr(rr, C.c_int64), C.c_int32(T),
+        C.c_int32(B), _ptr(idx, C.c_int64), _ptr(off, C.c_int64), _ptr(pw, C.c_float), C.c_int(int(mean)),
+        _ptr(out, C.c_float), C.c_int64(out.shape[1]))
+    assert ok == 1, "the reference kernel reported an out-of-range index"
+    return out
+
+
+def ref_tbe_backward_rowwise_adagrad(grad, weights, weights_offsets, D_offsets, rows, indices, offsets, lr, eps,
+                                     momentum1, momentum1_offsets):
+    """embedding_backward_split_cpu_template.cpp:125-182 (rowwise Adagrad) through FBGEMM's SpMDM +
+    GenerateSparseAdaGrad kernels; in place on `weights` and `momentum1`."""
+    assert weights.dtype == np.float32 and weights.flags.c_contiguous
+    assert momentum1.dtype == np.float32 and momentum1.flags.c_contiguous
+    T = len(D_offsets) - 1
+    B = (len(offsets) - 1) // T
+    g = _c(grad, np.float32)
+    wo, Do, rr = _c(weights_offsets, np.int64), _c(D_offsets, np.int32), _c(rows, np.int64)
+    idx, off, mo = _c(indices, np.int64), _c(offsets, np.int64), _c(momentum1_offsets, np.int64)
+    ok = tbe_ref_lib().ref_tbe_backward_rowwise_adagrad_f32(
+        _ptr(g, C.c_float), C.c_int64(g.shape[1]), _ptr(weights, C.c_float), _ptr(wo, C.c_int64),
+        _ptr(Do, C.c_int32), _ptr(rr, C.c_int64), C.c_int32(T), C.c_int32(B), _ptr(idx, C.c_int64),
+        _ptr(off, C.c_int64), _ptr(momentum1, C.c_float), _ptr(mo, C.c_int64), C.c_float(lr), C.c_float(eps))
+    assert ok == 1

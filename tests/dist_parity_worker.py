@@ -1,8 +1,8 @@
 """Multi-rank worker (torchrun): sharded-vs-unsharded one-step parity on real GPUs, the pattern of
 torchrec/distributed/test_utils/test_model_parallel_base.py:144-290.  Every rank builds the same
 unsharded DLRM (nn.EmbeddingBag tables, plain SGD) and a DistributedModelParallel DLRM with a mix of
-table-wise and row-wise tables and the fused EXACT_SGD; after ONE step on per-rank batches the
-sharded predictions must equal the unsharded model's predictions on the same samples, and every
+table-wise and row-wise tables and the fused EXACT_SGD; after SIX steps on fresh per-rank batches (B200_PARITY_STEPS) the
+sharded predictions of every step must equal the unsharded model's predictions on the same samples, and every
 local weight shard must equal the corresponding slice of the unsharded weights."""
 import os
 import sys
@@ -86,30 +86,42 @@ def main() -> None:
             to_load[k] = gsd[k].clone()
     res = dmp.load_state_dict(to_load)
     assert not res.missing_keys and not res.unexpected_keys, res
-    batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
-                                       manual_seed=100 + rank))).to(dev)
-    # global batch = concatenation of the per-rank batches along the batch dim
-    dense_all = [torch.empty_like(batch.dense_features) for _ in range(world)]
-    dist.all_gather(dense_all, batch.dense_features)
-    vals_all = [torch.empty_like(batch.sparse_features.values()) for _ in range(world)]
-    dist.all_gather(vals_all, batch.sparse_features.values())
+    steps = int(os.environ.get("B200_PARITY_STEPS", "6"))
     F = len(keys)
-    per_rank = [v.view(F, B * 2) for v in vals_all]
-    gvalues = torch.cat(per_rank, dim=1).reshape(-1)
-    gkjt = KeyedJaggedTensor(keys=keys, values=gvalues,
-                             lengths=torch.full((F * B * world,), 2, dtype=torch.int32, device=dev), stride=B * world)
-    gdense = torch.cat(dense_all, dim=0)
-
     opt_g = torch.optim.SGD(glob.parameters(), lr=lr)
     opt_l = torch.optim.SGD(list(dmp.parameters()), lr=lr)
-    opt_g.zero_grad()
-    # DDP averages dense grads over ranks and the pooled collectives divide by W (GRADIENT_DIVISION):
-    # the equivalent unsharded objective is the mean over ranks of the per-rank sums.
-    (glob(gdense, gkjt).sum() / world).backward()
-    opt_g.step()
-    opt_l.zero_grad()
-    dmp(batch.dense_features, batch.sparse_features).sum().backward()
-    opt_l.step()
+
+    def global_view(batch):
+        """The global batch = concatenation of the per-rank batches along the batch dim."""
+        dense_all = [torch.empty_like(batch.dense_features) for _ in range(world)]
+        dist.all_gather(dense_all, batch.dense_features)
+        vals_all = [torch.empty_like(batch.sparse_features.values()) for _ in range(world)]
+        dist.all_gather(vals_all, batch.sparse_features.values())
+        gvalues = torch.cat([v.view(F, B * 2) for v in vals_all], dim=1).reshape(-1)
+        gkjt = KeyedJaggedTensor(keys=keys, values=gvalues,
+                                 lengths=torch.full((F * B * world,), 2, dtype=torch.int32, device=dev),
+                                 stride=B * world)
+        return torch.cat(dense_all, dim=0), gkjt
+
+    # SEVERAL steps on fresh batches: the peer exchange skips its first barrier from the second step on
+    # ("quiesced"), persistent symmetric buffers are reused, and errors would compound in the weights
+    for step in range(steps):
+        batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2,
+                                           num_dense=13, manual_seed=100 + rank + 1000 * step))).to(dev)
+        gdense, gkjt = global_view(batch)
+        opt_g.zero_grad()
+        # DDP averages dense grads over ranks and the pooled collectives divide by W (GRADIENT_DIVISION):
+        # the equivalent unsharded objective is the mean over ranks of the per-rank sums.
+        out_g = glob(gdense, gkjt)
+        (out_g.sum() / world).backward()
+        opt_g.step()
+        opt_l.zero_grad()
+        out_l = dmp(batch.dense_features, batch.sparse_features)
+        out_l.sum().backward()
+        opt_l.step()
+        # the training-time predictions of every step (the loss trajectory) agree as well
+        torch.testing.assert_close(out_l.detach(), out_g.detach()[rank * B:(rank + 1) * B], rtol=2e-4, atol=2e-4,
+                                   msg=lambda m: f"rank {rank} step {step}: {m}")
     with torch.no_grad():
         pred_g = glob(gdense, gkjt)[rank * B:(rank + 1) * B]
         pred_l = dmp(batch.dense_features, batch.sparse_features)
@@ -119,10 +131,10 @@ def main() -> None:
         exp = shard_of(k.split(".")[-2], gsd[k]) if "embedding_bags" in k else gsd[k]
         v = local_tensor(v)
         err = float((v - exp).abs().max()) if v.numel() else 0.0
-        if err > 1e-4:
+        if err > 3e-4:  # six steps of fp32 reassociation between nn.EmbeddingBag + SGD and the fused kernels
             bad.append(f"{k}: max abs diff {err:.3e}")
     assert not bad, f"rank {rank}: weights differ from the unsharded model after one step: " + "; ".join(bad)
-    torch.testing.assert_close(pred_l, pred_g, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(pred_l, pred_g, rtol=3e-4, atol=3e-4)
     from torchrec.distributed.embeddingbag import ShardedEmbeddingBagCollection
     sebc = next(m for m in dmp.module.modules() if isinstance(m, ShardedEmbeddingBagCollection))
     mode = "peer" if sebc._peer is not None else "nccl"
@@ -135,7 +147,7 @@ def main() -> None:
         mode = "peer" if want_push else "peer_pull"
     dist.barrier()
     if rank == 0:
-        print(f"DIST PARITY OK world={world} exchange={mode}")
+        print(f"DIST PARITY OK world={world} exchange={mode} steps={steps}")
     dist.destroy_process_group()
 
 

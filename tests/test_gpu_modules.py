@@ -119,6 +119,59 @@ def test_tbe_sequence_mode_vs_embedding(opt, wp, shared):
         torch.testing.assert_close(w.float(), exp, rtol=tol, atol=tol)
 
 
+@pytest.mark.parametrize("opt", ["EXACT_SGD", "EXACT_ROWWISE_ADAGRAD"])
+@pytest.mark.parametrize("weighted", [False, True])
+def test_tbe_pooled_shared_tables_and_feature_requires_grad(opt, weighted):
+    """f2: POOLED lookups where several features share a table (feature_table_map with T > T_,
+    split_table_batched_embeddings_ops.py:580-640): the forward pools each feature from its table, and the fused
+    backward must coalesce the gradients of ALL features of a table into one update per row (one index-transpose
+    segment per table).  With per-sample weights, feature_requires_grad masks the weight gradient of the features
+    that do not need it (embedding_backward_split_indice_weights_template.cu)."""
+    from fbgemm_gpu.split_table_batched_embeddings_ops import PoolingMode
+    torch.manual_seed(11)
+    rows, dims, B, L = [40, 9, 300], [16, 32, 8], 50, 4
+    ftm = [0, 0, 1, 2, 2, 2]  # features 0-1 share table 0, features 3-5 share table 2
+    T = len(ftm)
+    lr, eps = 0.1, 1e-4
+    m = _tbe(rows, dims, opt, learning_rate=lr, eps=eps, pooling_mode=PoolingMode.SUM, feature_table_map=ftm)
+    m.init_embedding_weights_uniform(-1.0, 1.0)
+    bags = [torch.nn.EmbeddingBag(r, d, mode="sum", sparse=False, include_last_offset=True).cuda()
+            for r, d in zip(rows, dims)]
+    for b, w in zip(bags, m.split_embedding_weights()):
+        b.weight.data.copy_(w)
+    lengths = torch.randint(0, L + 1, (T, B))
+    idx = [torch.randint(0, rows[ftm[f]], (int(lengths[f].sum()),)) for f in range(T)]
+    offs = [torch.cat([torch.zeros(1, dtype=torch.long), lengths[f].cumsum(0)]) for f in range(T)]
+    indices = torch.cat(idx).cuda()
+    offsets = torch.cat([torch.zeros(1, dtype=torch.long), lengths.view(-1).cumsum(0)]).cuda()
+    psw = [torch.rand(i.numel()) for i in idx] if weighted else None
+    psw_all = torch.cat(psw).cuda().requires_grad_(True) if weighted else None
+    frg = torch.tensor([1, 0, 1, 0, 0, 1], dtype=torch.int32, device="cuda") if weighted else None
+    out = m(indices, offsets, psw_all, frg)
+    ref_psw = [p.cuda().requires_grad_(True) for p in psw] if weighted else [None] * T
+    ref = torch.cat([bags[ftm[f]](idx[f].cuda(), offs[f].cuda(), per_sample_weights=ref_psw[f]) for f in range(T)], 1)
+    assert out.shape == (B, sum(dims[t] for t in ftm))
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+    go = torch.randn_like(out)
+    out.backward(go)
+    ref.backward(go)
+    for t, (b, w) in enumerate(zip(bags, m.split_embedding_weights())):
+        g = b.weight.grad  # autograd already summed the contributions of every feature of the table
+        if opt == "EXACT_SGD":
+            exp = b.weight.data - lr * g
+        else:
+            state = g.pow(2).mean(dim=1)
+            exp = torch.addcdiv(b.weight.data, g, (state.sqrt() + eps).unsqueeze(1), value=-lr)
+            touched = torch.unique(torch.cat([idx[f] for f in range(T) if ftm[f] == t])).cuda()
+            torch.testing.assert_close(m.split_optimizer_states()[t][0][touched], state[touched],
+                                       rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(w, exp, rtol=1e-4, atol=1e-4)
+    if weighted:
+        exp_g = torch.cat([p.grad if int(frg[f]) else torch.zeros_like(p) for f, p in enumerate(ref_psw)])
+        torch.testing.assert_close(psw_all.grad, exp_g, rtol=1e-4, atol=1e-4)
+        assert float(psw_all.grad[: idx[0].numel()].abs().sum()) > 0  # feature 0 does get its gradient
+
+
 @pytest.mark.parametrize("wp", ["FP16", "BF16"])
 def test_tbe_module_stochastic_rounding_default(wp):
     """16-bit tables round stochastically by default, like the reference's module (:200): many SGD steps of
@@ -245,7 +298,7 @@ def test_quantized_ebc():
     assert sd["embedding_bags.t0.weight"].shape == (100, 144)
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("exchange", ["peer", "peer_pull", "nccl"])
 def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     """TW + RW over `world` GPUs (torchrun): the fused peer-memory exchange and the NCCL collectives both
@@ -260,9 +313,35 @@ def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                         "--master-addr", "127.0.0.1", "--master-port",
                         {"peer": "29611", "peer_pull": "29616", "nccl": "29621"}[exchange],
-                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=600,
+                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=300,
                        env=env)
     assert r.returncode == 0 and f"exchange={exchange}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_reference_torchrec_runs_over_this_fbgemm_gpu(world):
+    """The drop-in claim shown, not asserted: the REFERENCE's torchrec (copied unmodified into the git-ignored
+    baseline/_ref by tools/install_reference_torchrec.py) builds its own DistributedModelParallel +
+    ShardedEmbeddingBagCollection + BatchedFusedEmbeddingBag over this repo's `fbgemm_gpu` (table-wise + row-wise,
+    NCCL collectives at world 2) and two fused-SGD steps match its unsharded EmbeddingBagCollection."""
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    root = os.path.dirname(here)
+    ref = os.path.join(root, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "torchrec")):
+        pytest.skip("baseline/_ref/torchrec not installed (python tools/install_reference_torchrec.py)")
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    pkg = os.path.join(root, "torchrec-oldfork_b200")
+    dropin = os.path.join(pkg, "dropin")
+    # reference torchrec first; this repo contributes fbgemm_gpu + b200_sparse only
+    path = [ref, dropin if os.path.isdir(os.path.join(dropin, "fbgemm_gpu")) else pkg]
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join(path))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29661",
+                        os.path.join(here, "dropin_worker.py")], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and f"DROPIN OK world={world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
 @pytest.mark.parametrize("world", [1, 2])

@@ -375,9 +375,25 @@ def run_ours(args) -> None:
     ms_total = timed(lambda i: pipe.progress(dev_iter), args.steps)
     launches = KernelProfile.launches
     kern = KernelProfile.summary_ms()
+    sort_args = KernelProfile.last_sort_args
     KernelProfile.reset(enabled=False)
     clocks = sampler.stop() if rank == 0 else {}
     pipe.reset()
+    # the index transpose alone (in the step it runs on a side stream beside the forward, so its in-step
+    # duration mostly measures how long it waits for SMs): 20 isolated runs on the same ids
+    sort_isolated_ms = None
+    if sort_args is not None:
+        from b200_sparse import ops as _ops
+        torch.cuda.synchronize()
+        for _ in range(3):
+            _ops.tbe_sort_indices(*sort_args)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            _ops.tbe_sort_indices(*sort_args)
+        e1.record()
+        torch.cuda.synchronize()
+        sort_isolated_ms = e0.elapsed_time(e1) / 20
 
     # ---- e2e: pinned host batch -> H2D every step (memcpy stream), loss read back every step
     host_iter = itertools.cycle(host_batches)
@@ -440,6 +456,8 @@ def run_ours(args) -> None:
             k["achieved_gbs"] = nbytes / per_step_ms / 1e6
             k["frac_of_peak"] = k["achieved_gbs"] / peak
         k["traffic"] = traffic_of.get(ncu_name[name])
+        if name == "tbe_sort" and sort_isolated_ms is not None:
+            k["isolated_ms_per_call"] = sort_isolated_ms
         kernels[name] = k
 
     def roofline_of(name, label):
@@ -464,6 +482,12 @@ def run_ours(args) -> None:
             "achieved": nb / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": nb / ms / 1e6 / peak, "traffic": None,
             "peak_source": peak_src, "ms_per_step": ms, "frac_of_nominal_8TBs": nb / ms / 1e6 / 8000.0,
             "note": "the transpose runs on a side stream beside the forward; its in-step duration is charged in full"}
+        if sort_isolated_ms is not None:  # the same sum with the transpose timed alone
+            ms2 = ms - kernels["tbe_sort"]["ms_per_step"] + sort_isolated_ms * kernels["tbe_sort"]["calls_per_step"]
+            rooflines["tbe_fwd+transpose+bwd"].update(
+                {"ms_per_step_transpose_isolated": ms2, "achieved_transpose_isolated": nb / ms2 / 1e6,
+                 "frac_transpose_isolated": nb / ms2 / 1e6 / peak,
+                 "frac_of_nominal_8TBs_transpose_isolated": nb / ms2 / 1e6 / 8000.0})
     # top-level `roofline`: the repo kernel with the longest in-step duration
     roof = {}
     if rooflines:

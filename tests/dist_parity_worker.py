@@ -113,13 +113,14 @@ def main() -> None:
         # DDP averages dense grads over ranks and the pooled collectives divide by W (GRADIENT_DIVISION):
         # the equivalent unsharded objective is the mean over ranks of the per-rank sums.
         out_g = glob(gdense, gkjt)
-        (out_g.sum() / world).backward()
+        (torch.tanh(out_g).sum() / world).backward()  # a bounded objective: six steps at lr 0.1 must not diverge
         opt_g.step()
         opt_l.zero_grad()
         out_l = dmp(batch.dense_features, batch.sparse_features)
-        out_l.sum().backward()
+        torch.tanh(out_l).sum().backward()
         opt_l.step()
         # the training-time predictions of every step (the loss trajectory) agree as well
+        assert bool(torch.isfinite(out_g).all()), f"step {step}: the unsharded model diverged"
         torch.testing.assert_close(out_l.detach(), out_g.detach()[rank * B:(rank + 1) * B], rtol=2e-4, atol=2e-4,
                                    msg=lambda m: f"rank {rank} step {step}: {m}")
     with torch.no_grad():

@@ -65,7 +65,7 @@ def main() -> None:
     dmp = DistributedModelParallel(local, env=ShardingEnv.from_process_group(pg), device=dev, plan=plan,
                                    sharders=sharders)
     sebc = [m for m in dmp.modules() if isinstance(m, ShardedEmbeddingBagCollection)]
-    fused = [m for m in dmp.modules() if isinstance(m, BatchedFusedEmbeddingBag)]
+    fused = [m for lookup in sebc[0]._lookups for m in lookup.modules() if isinstance(m, BatchedFusedEmbeddingBag)]
     assert len(sebc) == 1 and len(fused) >= 1, (len(sebc), len(fused))
     from fbgemm_gpu.split_table_batched_embeddings_ops import SplitTableBatchedEmbeddingBagsCodegen
     assert all(isinstance(m.emb_module, SplitTableBatchedEmbeddingBagsCodegen) for m in fused)

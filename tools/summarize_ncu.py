@@ -36,5 +36,30 @@ def main(path: str) -> None:
         print()
 
 
+def traffic_json(path: str) -> None:
+    """{kernel base name: mean dram read + write bytes per launch} as JSON (profiles/r*_traffic.json)."""
+    import json
+    import re
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    acc = {}
+    for r in rows[2:]:
+        name = re.sub(r"^void\s+", "", r[idx["Kernel Name"]])
+        name = re.sub(r"^b200::", "", name).split("<")[0].split("(")[0]
+        tot = 0.0
+        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            tot += float(r[idx[m]].replace(",", "")) * scale.get(units[idx[m]], 1)
+        acc.setdefault(name, []).append(tot)
+    out = {"source": f"{path}: ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, mean per launch"}
+    out.update({k: int(sum(v) / len(v)) for k, v in acc.items()})
+    print(json.dumps(out, indent=2))
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--traffic-json":
+        traffic_json(sys.argv[1])
+    else:
+        main(sys.argv[1])

@@ -26,6 +26,7 @@ class KernelProfile:
     launches = 0
     enabled = False
     events: Dict[str, List[Tuple["torch.cuda.Event", "torch.cuda.Event"]]] = {}
+    last_sort_args: Optional[tuple] = None  # arguments of the latest index transpose (bench.py re-times it alone)
 
     @classmethod
     def reset(cls, enabled: bool = False) -> None:
@@ -336,6 +337,9 @@ def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cum
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     host_bits = max_table_bits if 0 < max_table_bits < key_bits else key_bits
     n_pass = (host_bits + 8) // 9
+    if KernelProfile.enabled:
+        KernelProfile.last_sort_args = (indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted,
+                                        max_table_bits)
     with torch.cuda.device(dev), _timed("tbe_sort", dev, 2 + 3 * n_pass):  # plan, linearize, 3 kernels per pass
         check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
                                         key_bits, int(max_table_bits), int(weighted), _p(keys), _p(payload), _p(bag_of_pos),

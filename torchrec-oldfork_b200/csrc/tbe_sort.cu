@@ -50,7 +50,9 @@ struct SortPlanView {
   int32_t* seg_passes;
   int64_t* seg_p0;
   int32_t* seg_tile0;
+  int64_t* tile_rec;  // [max_tiles][5]: (passes << 32 | seg), begin, end, key base, segment start
 };
+constexpr int kTileRecWords = 5;
 constexpr int kHdrNseg = 0, kHdrPass = 1, kHdrTiles = 1 + kSortMaxPasses;
 
 // ------------------------------------------------------------------------------------ plan
@@ -141,6 +143,25 @@ sort_plan_kernel(const int64_t* __restrict__ hsc, const void* __restrict__ offse
     pv.hdr[kHdrTiles] = s_carry;
   }
   if (tid < kSortMaxPasses) pv.hdr[kHdrPass + tid] = s_pass[tid];
+  __syncthreads();
+  // 3. one record per tile, so that the per-pass kernels start with ONE round of loads instead of a binary
+  //    search over the segments (five dependent L2 latencies per CTA)
+  const int32_t total = s_carry;
+  for (int32_t tile = tid; tile < total; tile += kSortThreads) {
+    int32_t lo = 0, hi = nseg;  // largest s with seg_tile0[s] <= tile
+    while (hi - lo > 1) {
+      const int32_t mid = (lo + hi) >> 1;
+      if (pv.seg_tile0[mid] <= tile) lo = mid; else hi = mid;
+    }
+    const int64_t p0 = pv.seg_p0[lo], seg_end = pv.seg_p0[lo + 1];
+    const int64_t begin = p0 + (int64_t)(tile - pv.seg_tile0[lo]) * tile_size;
+    int64_t* rec = pv.tile_rec + (int64_t)tile * kTileRecWords;
+    rec[0] = ((int64_t)pv.seg_passes[lo] << 32) | (uint32_t)lo;
+    rec[1] = begin;
+    rec[2] = begin + tile_size < seg_end ? begin + tile_size : seg_end;
+    rec[3] = pv.seg_base[lo];
+    rec[4] = p0;
+  }
 }
 
 // ------------------------------------------------------------------------------------ linearise
@@ -229,21 +250,18 @@ struct TileInfo {
 // tile -> (segment, position range); false when the tile is past the last one or its segment is done
 __device__ __forceinline__ bool sort_tile_info(const SortPlanView& pv, int32_t tile, int pass,
                                                int64_t tile_size, TileInfo& ti) {
-  const int32_t nseg = pv.hdr[kHdrNseg];
-  if (tile >= pv.hdr[kHdrTiles]) return false;
-  int32_t lo = 0, hi = nseg;  // largest s with seg_tile0[s] <= tile
-  while (hi - lo > 1) {
-    const int32_t mid = (lo + hi) >> 1;
-    if (pv.seg_tile0[mid] <= tile) lo = mid; else hi = mid;
-  }
-  ti.seg = lo;
-  ti.passes = pv.seg_passes[lo];
+  // all six loads are independent: one round trip (records past the last tile are garbage but mapped)
+  const int64_t* rec = pv.tile_rec + (int64_t)tile * kTileRecWords;
+  const int32_t total = pv.hdr[kHdrTiles];
+  const int64_t r0 = rec[0], r1 = rec[1], r2 = rec[2], r3 = rec[3], r4 = rec[4];
+  if (tile >= total) return false;
+  ti.seg = (int32_t)(r0 & 0xffffffff);
+  ti.passes = (int32_t)(r0 >> 32);
   if (pass >= ti.passes) return false;
-  ti.seg_p0 = pv.seg_p0[lo];
-  ti.begin = ti.seg_p0 + (int64_t)(tile - pv.seg_tile0[lo]) * tile_size;
-  const int64_t seg_end = pv.seg_p0[lo + 1];
-  ti.end = ti.begin + tile_size < seg_end ? ti.begin + tile_size : seg_end;
-  ti.base = pv.seg_base[lo];
+  ti.begin = r1;
+  ti.end = r2;
+  ti.base = r3;
+  ti.seg_p0 = r4;
   return true;
 }
 
@@ -257,7 +275,6 @@ template <typename K>
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const K* __restrict__ keys_a, const K* __restrict__ keys_b, int pass, int64_t tile_size,
                  uint32_t* __restrict__ counts, SortPlanView pv) {
-  if (!pv.hdr[kHdrPass + pass]) return;
   __shared__ uint32_t hist[kSortBins];
   TileInfo ti;
   if (!sort_tile_info(pv, blockIdx.x, pass, tile_size, ti)) return;
@@ -355,15 +372,20 @@ sort_scan_kernel(int pass, uint32_t* __restrict__ counts, int smem_tiles, SortPl
 
 // Stable scatter of one tile.  Each warp ranks a contiguous 256-position slice with warp-private counters
 // (match_any gives the rank among the 32 lanes, the counter the rank among earlier rounds), the slices are
-// then chained in warp order: the relative order of equal digits is exactly the position order.
+// then chained in warp order: the relative order of equal digits is exactly the position order.  The chunk is
+// first reordered by digit in shared memory and then copied out slot by slot, so that consecutive threads write
+// consecutive addresses of one bin's run (a direct scatter writes 4 useful bytes per 32-byte sector).
 template <typename K>
 __global__ void __launch_bounds__(kSortThreads)
 sort_scatter_kernel(K* __restrict__ keys_a, int32_t* __restrict__ pay_a, K* __restrict__ keys_b,
                     int32_t* __restrict__ pay_b, int pass, int64_t tile_size,
                     const uint32_t* __restrict__ counts, SortPlanView pv) {
-  if (!pv.hdr[kHdrPass + pass]) return;
   __shared__ uint32_t off[kSortBins];                 // next output offset per bin (segment-relative)
-  __shared__ uint32_t wcnt[kSortWarps][kSortBins];    // per-warp counters, then per-warp bases
+  __shared__ uint32_t lbase[kSortBins];               // first slot of the bin inside the reordered chunk
+  __shared__ uint32_t wcnt[kSortWarps][kSortBins];    // per-warp counters, then per-warp slot bases
+  __shared__ uint32_t warp_sum[kSortWarps];
+  __shared__ K s_key[kSortChunk];
+  __shared__ int32_t s_pay[kSortChunk];
   TileInfo ti;
   if (!sort_tile_info(pv, blockIdx.x, pass, tile_size, ti)) return;
   const bool from_b = ((ti.passes - pass) & 1) != 0;
@@ -396,32 +418,67 @@ sort_scatter_kernel(K* __restrict__ keys_a, int32_t* __restrict__ pay_a, K* __re
     for (int r = 0; r < 8; ++r) {
       const int d = dg[r] >= 0 ? dg[r] : kSortBins + lane;
       const unsigned m = __match_any_sync(kFull, d);
-      if (dg[r] >= 0) {
-        rank[r] = wcnt[warp][d] + __popc(m & lt);
-      }
+      if (dg[r] >= 0) rank[r] = wcnt[warp][d] + __popc(m & lt);
       __syncwarp();
       if (dg[r] >= 0 && (int)(__ffs(m) - 1) == lane) wcnt[warp][d] += __popc(m);
       __syncwarp();
     }
     __syncthreads();
-    for (int bin = threadIdx.x; bin < kSortBins; bin += kSortThreads) {
-      uint32_t run = off[bin];
+    // chunk totals per bin -> exclusive scan over the 512 bins (thread t owns bins 2t, 2t+1) -> slot bases
+    uint32_t tot[2], wb[2][kSortWarps];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int bin = 2 * threadIdx.x + j;
+      uint32_t run = 0;
 #pragma unroll
       for (int w = 0; w < kSortWarps; ++w) {
-        const uint32_t c = wcnt[w][bin];
-        wcnt[w][bin] = run;
-        run += c;
+        wb[j][w] = run;
+        run += wcnt[w][bin];
       }
-      off[bin] = run;
+      tot[j] = run;
+    }
+    uint32_t inc = tot[0] + tot[1];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(kFull, inc, d);
+      if (lane >= d) inc += v;
+    }
+    if (lane == 31) warp_sum[warp] = inc;
+    __syncthreads();
+    uint32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) before += w < warp ? warp_sum[w] : 0u;
+    uint32_t base = before + inc - (tot[0] + tot[1]);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int bin = 2 * threadIdx.x + j;
+      lbase[bin] = base;
+#pragma unroll
+      for (int w = 0; w < kSortWarps; ++w) wcnt[w][bin] = base + wb[j][w];
+      base += tot[j];
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
       if (dg[r] >= 0) {
-        const int64_t q = ti.seg_p0 + wcnt[warp][dg[r]] + rank[r];
-        dst_k[q] = key[r];
-        dst_p[q] = pay[r];
+        const uint32_t slot = wcnt[warp][dg[r]] + rank[r];
+        s_key[slot] = key[r];
+        s_pay[slot] = pay[r];
       }
+    }
+    __syncthreads();
+    const int n = (int)(ti.end - c0 < kSortChunk ? ti.end - c0 : kSortChunk);
+    for (int i = threadIdx.x; i < n; i += kSortThreads) {
+      const K k = s_key[i];
+      const int d = sort_digit<K>(k, ti.base, shift);
+      const int64_t q = ti.seg_p0 + off[d] + (uint32_t)(i - lbase[d]);
+      dst_k[q] = k;
+      dst_p[q] = s_pay[i];
+    }
+    __syncthreads();
+    for (int j = 0; j < 2; ++j) {  // this chunk's elements are placed: advance the bins' output offsets
+      const int bin = 2 * threadIdx.x + j;
+      off[bin] += tot[j];
     }
     __syncthreads();
   }
@@ -471,6 +528,8 @@ SortWs sort_ws_layout(void* ws, int64_t N, int key_bits, int32_t T) {
   p += sort_align256(4 * n1);
   w.pv.seg_tile0 = (int32_t*)p;
   p += sort_align256(4 * n1);
+  w.pv.tile_rec = (int64_t*)p;
+  p += sort_align256(8 * (size_t)kTileRecWords * (size_t)w.max_tiles);
   w.bytes = (size_t)(p - (char*)ws) + 256;
   return w;
 }

@@ -251,15 +251,15 @@ class SplitTableBatchedEmbeddingBagsCodegen(nn.Module):
         return out
 
     def split_optimizer_states(self) -> List[Tuple[Tensor]]:
-        """Per table tuple of optimizer-state views (reference :948-1024): (momentum1[rows],)
-        for rowwise Adagrad, an empty-tensor tuple for SGD."""
+        """Per table tuple of optimizer-state views (reference :948-1024): (momentum1[rows],) for rowwise
+        Adagrad; for SGD, which has no state, the reference's `list(zip(*[]))` - an EMPTY list (its torchrec
+        wrapper walks it with zip_longest, batched_embedding_kernel.py:136-148)."""
+        if self.optimizer != OptimType.EXACT_ROWWISE_ADAGRAD:
+            return []
         out = []
         for t, (r, _, _, _) in enumerate(self.embedding_specs):
-            if self.optimizer == OptimType.EXACT_ROWWISE_ADAGRAD:
-                o = self._table_row_offsets[t]
-                out.append((self.momentum1_dev.detach()[o:o + r],))
-            else:
-                out.append((torch.empty(0, device=self.current_device),))
+            o = self._table_row_offsets[t]
+            out.append((self.momentum1_dev.detach()[o:o + r],))
         return out
 
     def get_optimizer_state(self):

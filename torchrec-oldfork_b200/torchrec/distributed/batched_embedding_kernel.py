@@ -7,6 +7,7 @@ views of them."""
 from __future__ import annotations
 
 import copy
+import itertools
 from typing import Any, Dict, Iterator, List, Optional, Tuple
 
 import torch
@@ -38,7 +39,7 @@ class EmbeddingFusedOptimizer(FusedOptimizer):
         state: Dict[Any, Any] = {}
         weights = emb_module.split_embedding_weights()
         opt_states = emb_module.split_optimizer_states()
-        for table, w, st in zip(config.embedding_tables, weights, opt_states):
+        for table, w, st in itertools.zip_longest(config.embedding_tables, weights, opt_states):  # SGD: no states
             name = f"{table.name}.weight"
             sharded = pg is not None and table.global_metadata is not None and table.local_metadata is not None
             if sharded:

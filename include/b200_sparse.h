@@ -327,6 +327,13 @@ int b200_peer_stage_reduce(float* stage, int32_t W, int32_t B_local, int32_t Dw,
                            int64_t out_pitch, const int32_t* out_col4, int32_t clear_stage,
                            void* stream);
 
+/* Stream-ordered cross-rank barrier over peer memory (what brackets the peer stores / loads above; the
+ * reference's collectives synchronise inside NCCL, comm_ops.py:490,592,866,922).  pads: device array of W
+ * pointers to the ranks' signal pads (uint32[W] each, zero-initialised symmetric memory); epoch_ctr: a
+ * device-local uint32 counter owned by this barrier instance (zero-initialised, bumped by the kernel).
+ * Every rank must call it the same number of times.  One 32-thread kernel; graph-capturable. */
+int b200_peer_barrier(uint32_t* const* pads, int32_t rank, int32_t W, uint32_t* epoch_ctr, void* stream);
+
 /* The same reduction driven by presence flags: flags is [B_local][F][W] bytes (set by the peers'
  * b200_tbe_forward_peer with flag_pitch = F*W, flag_col[t] = f*W + rank); feature f owns the staged float4
  * columns [feat_col4[f], feat_col4[f+1]).  Only flagged slots are read (rank order, deterministic), consumed

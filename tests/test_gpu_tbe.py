@@ -533,6 +533,22 @@ def test_row_wise_exchange_with_presence_flags(ops, W, L):
             assert not bool(flags[d_].any()), "consumed flags must be cleared"
 
 
+def test_peer_barrier_single_rank_epochs(ops):
+    """b200_peer_barrier with W = 1 (the cross-rank case runs in tests/dist_parity_worker.py): the device-resident
+    epoch advances by one per call and the rank's own slot follows it; a barrier behind a kernel on the same
+    stream does not hang."""
+    pad = torch.zeros(32, dtype=torch.int32, device="cuda")
+    ctr = torch.zeros(1, dtype=torch.int32, device="cuda")
+    bases = torch.tensor([pad.data_ptr()], dtype=torch.int64, device="cuda")
+    x = torch.randn(1 << 20, device="cuda")
+    for i in range(1, 4):
+        y = x * 2
+        ops.peer_barrier(bases, 0, 1, ctr)
+        torch.cuda.synchronize()
+        assert int(ctr[0]) == i and int(pad[0]) == i and int(pad[1:].abs().sum()) == 0
+    assert torch.equal(y, x * 2)
+
+
 # ------------------------------------------------------------------ stochastic rounding (fp16 / bf16 tables)
 @pytest.mark.parametrize("wdt,D,pattern", [
     ("fp16", 32, "unique"),     # packed narrow-row tile (4 lanes per row)

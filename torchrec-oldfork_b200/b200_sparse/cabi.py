@@ -42,6 +42,7 @@ SIGNATURES = {
                                       _p, _i32, _i32, _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32,
                                       _p, _p]),
     "b200_peer_stage_reduce": (_int, [_p, _i32, _i32, _i32, _p, _i64, _p, _i32, _p]),
+    "b200_peer_barrier": (_int, [_p, _i32, _i32, _p, _p]),
     "b200_peer_stage_reduce_flagged": (_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _i64, _p, _p]),
     "b200_tbe_sort_workspace_bytes": (_sz, [_i64, _int, _i32]),
     "b200_tbe_sort_indices": (_int, [_p, _p, _int, _p, _i32, _i32, _i64, _int, _int, _int, _p, _p, _p, _p,

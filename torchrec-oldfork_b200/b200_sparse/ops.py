@@ -516,6 +516,16 @@ def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: t
               "b200_peer_stage_reduce")
 
 
+def peer_barrier(pad_bases: torch.Tensor, rank: int, W: int, epoch_ctr: torch.Tensor) -> None:
+    """Cross-rank barrier on the current stream: pad_bases (int64 [W]) are the ranks' uint32[W] signal pads,
+    epoch_ctr a device-local int32/uint32 [1] counter of this barrier instance."""
+    dev = _need_cuda(pad_bases, epoch_ctr)
+    with torch.cuda.device(dev):
+        KernelProfile.launches += 1
+        check(lib.b200_peer_barrier(_p(pad_bases), int(rank), int(W), _p(epoch_ctr), _stream(dev)),
+              "b200_peer_barrier")
+
+
 def peer_stage_reduce_flagged(stage: torch.Tensor, flags: torch.Tensor, W: int, B_local: int, Dw: int,
                               feat_col4: torch.Tensor, out: torch.Tensor, out_col4: torch.Tensor) -> None:
     """Sum of the FLAGGED rank slots of stage ([W, B_local, Dw] fp32); flags is uint8 [B_local, F, W] and is

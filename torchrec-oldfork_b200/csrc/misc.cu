@@ -215,6 +215,43 @@ peer_stage_reduce_kernel(float* __restrict__ stage, int32_t W, int64_t rows, int
 }
 }  // namespace b200
 
+// Cross-rank barrier over NVLink peer memory: one small kernel, no host round trip.  pads[r] is rank r's
+// signal pad (uint32[W], symmetric memory); rank `rank` writes the barrier's epoch into slot `rank` of every
+// peer's pad with a system-scope release store and waits until every slot of its own pad has reached the epoch.
+// The epoch is a DEVICE-resident counter bumped by the kernel itself (every rank runs the same sequence of
+// barriers, so the counters agree), which keeps the launch valid inside a replayed CUDA graph.  Everything the
+// stream did before the barrier is visible to the peers after it, and vice versa.
+namespace b200 {
+__global__ void __launch_bounds__(32)
+peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank, int W, uint32_t* __restrict__ epoch_ctr) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) s_epoch = ++(*epoch_ctr);
+  __syncwarp();
+  const uint32_t epoch = s_epoch;
+  __threadfence_system();
+  for (int t = threadIdx.x; t < W; t += 32) {
+    uint32_t* remote = pads[t] + rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+  }
+  for (int t = threadIdx.x; t < W; t += 32) {
+    const uint32_t* mine = pads[rank] + t;
+    uint32_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+    } while ((int32_t)(v - epoch) < 0);
+  }
+  __threadfence_system();
+}
+}  // namespace b200
+
+extern "C" int b200_peer_barrier(uint32_t* const* pads, int32_t rank, int32_t W, uint32_t* epoch_ctr,
+                                 void* stream) {
+  if (!pads || !epoch_ctr || W <= 0 || rank < 0 || rank >= W) return B200_EINVAL;
+  b200::peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pads, rank, W, epoch_ctr);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 // Flag-driven variant: flags[b][f][r] != 0 says that rank r stored a partial sum for feature f of sample b.
 // One warp per (sample, feature): it reads the W flag bytes, adds only the flagged slots in rank order
 // (deterministic), clears the flags it consumed and writes the pooled row.  The staging data itself is never

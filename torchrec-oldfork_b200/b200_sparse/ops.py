@@ -76,6 +76,32 @@ def _need_cuda(*ts: Optional[torch.Tensor]) -> torch.device:
 
 
 _raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_get_dev = getattr(torch._C, "_cuda_getDevice", None)
+_set_dev = getattr(torch._C, "_cuda_setDevice", None)
+
+
+class _on:
+    """`with _on(dev)`: makes `dev` the current CUDA device for the C-ABI call; when it already is (the usual
+    case: one process per GPU) this is two attribute reads instead of torch.cuda.device's full guard - the
+    training step makes ~30 of these calls and is bound by host time at 8 ranks."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, dev: torch.device) -> None:
+        self.idx = dev.index
+        self.prev = -1
+
+    def __enter__(self):
+        if self.idx is not None and _get_dev is not None:
+            cur = _get_dev()
+            if cur != self.idx:
+                _set_dev(self.idx)
+                self.prev = cur
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            _set_dev(self.prev)
+        return False
 
 
 def _stream(dev: torch.device) -> int:
@@ -119,7 +145,7 @@ def cumsum(t_in: torch.Tensor, mode: int) -> torch.Tensor:
     dt = _idx_dt(x, "cumsum input")
     shape = (n + 1,) if mode == cabi.CUMSUM_COMPLETE else x.shape
     out = torch.empty(shape, dtype=x.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_cumsum(_p(x), _p(out), n, dt, mode, _p(_ws(dev)), _stream(dev)), "b200_cumsum")
     return out
@@ -157,7 +183,7 @@ def permute_sparse_data(
         total = int(permuted_lengths_sum)
         out_values = torch.empty(total, dtype=values_c.dtype, device=dev)
         out_weights = torch.empty(total, dtype=weights_c.dtype, device=dev) if weights_c is not None else None
-        with torch.cuda.device(dev):
+        with _on(dev):
             KernelProfile.launches += 1
             check(lib.b200_permute_2d_fused(_p(permute), _p(lengths_c), ldt, T, Tp, B, _p(out_lengths),
                                             _p(values_c), _p(out_values), values_c.element_size(),
@@ -167,7 +193,7 @@ def permute_sparse_data(
         return out_lengths, out_values, out_weights
     in_off = torch.empty(T * B + 1, dtype=torch.int64, device=dev)
     out_off = torch.empty(Tp * B + 1, dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         st = _stream(dev)
         KernelProfile.launches += 1
         check(lib.b200_permute_lengths(_p(permute), _p(lengths_c), ldt, T, Tp, B, _p(out_lengths),
@@ -204,7 +230,7 @@ def expand_into_jagged_permute(permute: torch.Tensor, input_offsets: torch.Tenso
         raise RuntimeError("offsets must have permute.numel() + 1 entries")
     dt = _idx_dt(input_offsets, "offsets")
     out = torch.empty(int(output_size), dtype=input_offsets.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_expand_into_jagged_permute(_p(permute.contiguous()), _p(input_offsets.contiguous()),
                                                   _p(output_offsets.contiguous()), dt, n, _p(out),
@@ -217,7 +243,7 @@ def offsets_range(offsets: torch.Tensor, range_size: int) -> torch.Tensor:
     dev = _need_cuda(offsets)
     dt = _idx_dt(offsets, "offsets")
     out = torch.empty(int(range_size), dtype=offsets.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_offsets_range(_p(offsets.contiguous()), dt, offsets.numel(), _p(out),
                                      int(range_size), _stream(dev)), "b200_offsets_range")
@@ -253,7 +279,7 @@ def block_bucketize_sparse_features(
         return new_lengths, new_indices, new_weights, new_pos, unbucketize
     off = torch.empty(TB + 1, dtype=torch.int64, device=dev)
     noff = torch.empty(TB * W + 1, dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_block_bucketize(_p(lengths), odt, _p(indices), idt, _p(block_sizes), T, B, W, N,
                                        _p(weights.contiguous() if weights is not None else None),
@@ -275,7 +301,7 @@ def bounds_check_indices(rows_per_table: torch.Tensor, indices: torch.Tensor, of
     if T == 0:
         return
     B = (offsets.numel() - 1) // T
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 2
         check(lib.b200_bounds_check(_p(rows_per_table), _p(indices), _p(offsets), dt, T, B,
                                     indices.numel(), int(mode), _p(warning), _p(_ws(dev)), _stream(dev)),
@@ -302,7 +328,7 @@ def tbe_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_offsets:
             per_sample_weights = per_sample_weights.float()
         per_sample_weights = per_sample_weights.contiguous()
     out = torch.empty((B, total_D), dtype=output_dtype, device=dev)
-    with torch.cuda.device(dev), _timed("tbe_forward", dev, 1):
+    with _on(dev), _timed("tbe_forward", dev, 1):
         check(lib.b200_tbe_forward(_p(weights), _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
                                    T, B, total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
                                    _p(offsets.contiguous()), idt, _p(per_sample_weights),
@@ -340,7 +366,7 @@ def tbe_sort_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_size_cum
     if KernelProfile.enabled:
         KernelProfile.last_sort_args = (indices, offsets, hash_size_cumsum, total_hash_size_bits, B, weighted,
                                         max_table_bits)
-    with torch.cuda.device(dev), _timed("tbe_sort", dev, 2 + 3 * n_pass):  # plan, linearize, 3 kernels per pass
+    with _on(dev), _timed("tbe_sort", dev, 2 + 3 * n_pass):  # plan, linearize, 3 kernels per pass
         check(lib.b200_tbe_sort_indices(_p(indices), _p(offsets), idt, _p(hash_size_cumsum), T, B, N,
                                         key_bits, int(max_table_bits), int(weighted), _p(keys), _p(payload), _p(bag_of_pos),
                                         _p(ws), ws_bytes, _stream(dev)), "b200_tbe_sort_indices")
@@ -369,7 +395,7 @@ def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.T
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
     if stochastic_rounding and weights.dtype != torch.float32:
-        with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):
+        with _on(dev), _timed("tbe_backward", dev, 2):
             check(lib.b200_tbe_backward_sr(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
                                            _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),
                                            _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
@@ -380,7 +406,7 @@ def tbe_backward(grad_output: torch.Tensor, srt: SortedIndices, weights: torch.T
                                            _p(scratch), int(sr_seed) & (2 ** 64 - 1),
                                            int(sr_offset) & (2 ** 64 - 1), _stream(dev)), "b200_tbe_backward_sr")
         return
-    with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):  # tile kernel + cross-CTA combine
+    with _on(dev), _timed("tbe_backward", dev, 2):  # tile kernel + cross-CTA combine
         check(lib.b200_tbe_backward(_p(grad_output), grad_output.stride(0), _p(srt.keys), _p(srt.payload),
                                     _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights),
                                     _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
@@ -399,7 +425,7 @@ def tbe_grad_indice_weights(grad_output: torch.Tensor, weights: torch.Tensor,
     T = D_offsets.numel() - 1
     B = (offsets.numel() - 1) // T
     out = torch.empty(indices.numel(), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_tbe_grad_indice_weights(_p(grad_output), grad_output.stride(0), _p(weights),
                                                _DT[weights.dtype], _p(weights_offsets), _p(D_offsets),
@@ -416,7 +442,7 @@ def quantize_rowwise_8bit_sbhalf(w: torch.Tensor) -> torch.Tensor:
         raise RuntimeError("expected a 2-D weight")
     w = w.float().contiguous()
     out = torch.empty((w.shape[0], w.shape[1] + 4), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_quantize_rowwise_8bit_sbhalf(_p(w), w.shape[0], w.shape[1], _p(out), _stream(dev)),
               "b200_quantize_rowwise_8bit_sbhalf")
@@ -435,7 +461,7 @@ def tbe_int8_forward(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
     out = torch.empty((B, total_D), dtype=output_dtype, device=dev)
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_tbe_int8_forward(_p(weights), _p(weights_offsets), _p(D_offsets), T, B, total_D,
                                         max_D, int(row_alignment), _p(indices.contiguous()),
@@ -466,7 +492,7 @@ def tbe_forward_peer(weights: torch.Tensor, weights_offsets: torch.Tensor, D_off
     B = (offsets.numel() - 1) // T
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
-    with torch.cuda.device(dev), _timed("tbe_forward", dev, 1):
+    with _on(dev), _timed("tbe_forward", dev, 1):
         check(lib.b200_tbe_forward_peer(_p(weights), _DT[weights.dtype], _p(weights_offsets), _p(D_offsets), T, B,
                                         total_D, max_D, int(all_D_mult8), _p(indices.contiguous()),
                                         _p(offsets.contiguous()), idt, _p(per_sample_weights), int(pooling_mode),
@@ -491,7 +517,7 @@ def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, sr
     scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
     if per_sample_weights is not None:
         per_sample_weights = per_sample_weights.float().contiguous()
-    with torch.cuda.device(dev), _timed("tbe_backward", dev, 2):
+    with _on(dev), _timed("tbe_backward", dev, 2):
         check(lib.b200_tbe_backward_peer(_p(grad_bases), grad_bases.numel(), int(B_src), int(grad_stride),
                                          _p(src_col), float(grad_scale), _p(srt.keys), _p(srt.payload),
                                          _p(srt.bag_of_pos), srt.N, srt.key_bits, _p(weights), _DT[weights.dtype],
@@ -509,7 +535,7 @@ def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: t
     dev = _need_cuda(stage, out, out_col4)
     if out_col4.dtype != torch.int32 or out_col4.numel() != Dw // 4:
         raise TypeError("out_col4 must be int32 with Dw // 4 entries")
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_peer_stage_reduce(_p(stage), int(W), int(B_local), int(Dw), _p(out), out.stride(0),
                                          _p(out_col4), int(bool(clear_stage)), _stream(dev)),
@@ -520,7 +546,7 @@ def peer_barrier(pad_bases: torch.Tensor, rank: int, W: int, epoch_ctr: torch.Te
     """Cross-rank barrier on the current stream: pad_bases (int64 [W]) are the ranks' uint32[W] signal pads,
     epoch_ctr a device-local int32/uint32 [1] counter of this barrier instance."""
     dev = _need_cuda(pad_bases, epoch_ctr)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_peer_barrier(_p(pad_bases), int(rank), int(W), _p(epoch_ctr), _stream(dev)),
               "b200_peer_barrier")
@@ -536,7 +562,7 @@ def peer_stage_reduce_flagged(stage: torch.Tensor, flags: torch.Tensor, W: int, 
         raise TypeError("flags must be uint8 [B_local, F, W]")
     if out_col4.dtype != torch.int32 or out_col4.numel() != Dw // 4 or feat_col4.dtype != torch.int32:
         raise TypeError("out_col4 / feat_col4 must be int32 with Dw // 4 / F + 1 entries")
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_peer_stage_reduce_flagged(_p(stage), _p(flags), int(W), int(B_local), int(Dw), int(F),
                                                  _p(feat_col4), _p(out), out.stride(0), _p(out_col4),
@@ -555,7 +581,7 @@ def interaction_forward(dense: torch.Tensor, sparse: torch.Tensor, pad_rows: boo
     width = D + (F + 1) * F // 2
     pitch = (width + 3) // 4 * 4 if pad_rows else width
     buf = torch.empty((B, pitch), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev), _timed("interaction_forward", dev, 1):
+    with _on(dev), _timed("interaction_forward", dev, 1):
         check(lib.b200_interaction_forward(_p(dense), _p(sparse), B, F, D, _p(buf), pitch, _stream(dev)),
               "b200_interaction_forward")
     return buf[:, :width] if pitch != width else buf
@@ -624,7 +650,7 @@ def interaction_backward(dense: torch.Tensor, sparse: torch.Tensor,
     if sink is not None and (sink.buf.dtype != sparse.dtype or sink.numel != sparse.numel()):
         sink = None
     gs = sink.buf.view(sparse.shape) if sink is not None else torch.empty_like(sparse)
-    with torch.cuda.device(dev), _timed("interaction_backward", dev, 1):
+    with _on(dev), _timed("interaction_backward", dev, 1):
         if sink is not None:
             sink.scattered = False
             if sink.feat_base is not None and sink.feat_base.numel() == F and F + 1 <= 32 and D % 32 == 0:
@@ -651,7 +677,7 @@ def linearize_seq_indices(indices: torch.Tensor, offsets: torch.Tensor, hash_siz
     T = hash_size_cumsum.numel() - 1
     N = indices.numel()
     out = torch.empty(N, dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_linearize_seq_indices(_p(indices.contiguous()), _p(offsets.contiguous()),
                                              _idx_dt(indices, "indices"), _p(hash_size_cumsum), T, int(B), N,
@@ -673,7 +699,7 @@ def relu_bias_grad(grad_out: torch.Tensor, out: torch.Tensor) -> Tuple[torch.Ten
     g = torch.empty((B, N), dtype=torch.float32, device=dev)
     gb = torch.empty(N, dtype=torch.float32, device=dev)
     scratch = torch.empty(lib.b200_relu_bias_grad_scratch_bytes(N) // 4, dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 2
         check(lib.b200_relu_bias_grad(_p(grad_out), grad_out.stride(0), _p(out), out.stride(0), B, N, _p(g), _p(gb),
                                       _p(scratch), _stream(dev)), "b200_relu_bias_grad")
@@ -687,7 +713,7 @@ def pooled_a2a_recat(src: torch.Tensor, dim_cumsum: torch.Tensor, B_local: int, 
     W = dim_cumsum.numel() - 1
     src = src.contiguous()
     dst = torch.empty_like(src)
-    with torch.cuda.device(dev):
+    with _on(dev):
         KernelProfile.launches += 1
         check(lib.b200_pooled_a2a_recat(_p(src), _p(dst), _p(dim_cumsum), W, int(B_local), int(forward),
                                         float(scale), _stream(dev)), "b200_pooled_a2a_recat")

@@ -533,6 +533,29 @@ def test_row_wise_exchange_with_presence_flags(ops, W, L):
             assert not bool(flags[d_].any()), "consumed flags must be cleared"
 
 
+@pytest.mark.parametrize("dims,B_local", [([128, 256, 128], 300), ([4], 7), ([64, 4, 8, 32, 12], 1025)])
+def test_pooled_a2a_recat_matches_split_view_cat(ops, dims, B_local):
+    """b200_pooled_a2a_recat == the reference's layout change around the pooled all-to-all: forward the
+    split + view + cat of comm_ops.py:555-560 ([W blocks of [B_local, D_r]] -> [B_local, sum D]), backward
+    _recat_pooled_embedding_grad_out :418-428 with the 1/W gradient division of :527-528.  Pure data movement:
+    bit-exact (the scale is a power of two)."""
+    rng = np.random.default_rng(len(dims) + B_local)
+    W, sumD = len(dims), sum(dims)
+    cum = dev(np.concatenate([[0], np.cumsum(dims)]).astype(np.int32))
+    src = torch.from_numpy(rng.standard_normal(B_local * sumD).astype(np.float32)).cuda()
+    got = ops.pooled_a2a_recat(src, cum, B_local, True)
+    parts = src.split([B_local * d for d in dims])
+    exp = torch.cat([p.view(B_local, d) for p, d in zip(parts, dims)], dim=1).reshape(-1)
+    assert torch.equal(got, exp)
+    g = torch.from_numpy(rng.standard_normal(B_local * sumD).astype(np.float32)).cuda()
+    scale = 1.0 / 8
+    got_b = ops.pooled_a2a_recat(g, cum, B_local, False, scale)
+    exp_b = torch.cat([p.contiguous().view(-1) for p in g.view(B_local, sumD).split(dims, dim=1)]) * scale
+    assert torch.equal(got_b, exp_b)
+    # round trip: backward(forward(x)) == x * scale
+    assert torch.equal(ops.pooled_a2a_recat(got, cum, B_local, False, scale), src * scale)
+
+
 def test_peer_barrier_single_rank_epochs(ops):
     """b200_peer_barrier with W = 1 (the cross-rank case runs in tests/dist_parity_worker.py): the device-resident
     epoch advances by one per call and the rank's own slot follows it; a barrier behind a kernel on the same

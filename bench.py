@@ -325,6 +325,19 @@ def run_ours(args) -> None:
                          "the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # At N >= 2 the step is bound by HOST time: give every rank its own slice of the host cores (its
+    # Python thread, autograd thread and NCCL proxy stop migrating / competing with the other ranks') and keep the
+    # cyclic garbage collector out of the timed loop.  B200_BENCH_PIN=1 enables both (off by default: an A/B at N = 2 was inside the run-to-run noise).
+    if world > 1 and os.environ.get("B200_BENCH_PIN", "0") == "1":
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = len(cores) // world
+            if per >= 2:
+                os.sched_setaffinity(0, cores[local_rank * per:(local_rank + 1) * per])
+        except (AttributeError, OSError):
+            pass
+        import gc
+        gc.disable()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29571")
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev,

@@ -62,6 +62,7 @@ SIGNATURES = {
     "b200_tbe_int8_forward": (_int, [_p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _int, _p,
                                      _int, _p, _int, _p]),
     "b200_interaction_forward": (_int, [_p, _p, _i32, _i32, _i32, _p, _i64, _p]),
+    "b200_interaction_forward_tma": (_int, [_p, _p, _i32, _i32, _i32, _p, _i64, _p]),
     "b200_interaction_backward": (_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p]),
     "b200_interaction_backward_scatter": (_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p]),
     "b200_linearize_seq_indices": (_int, [_p, _p, _int, _p, _i32, _i32, _i64, _p, _p]),

@@ -325,8 +325,12 @@ def test_interaction_forward_tma_is_bit_identical(ops, B, F, D):
     buf = torch.full((B, pitch), float("nan"), device="cuda")
     rc = lib.b200_interaction_forward_tma(dense.data_ptr(), sparse.data_ptr(), B, F, D, buf.data_ptr(), pitch,
                                           torch.cuda.current_stream().cuda_stream)
-    assert rc == 0, rc
     width = D + (F + 1) * F // 2
+    tma_smem = 16 * 3 * 4096 + 16 * ((width + 3) // 4 * 4) * 4 + 16 * 3 * 8 + 1024
+    if tma_smem > 227 * 1024:  # 32 rows x a 560-float output row per warp: refused, the caller keeps cp.async
+        assert rc == -2, rc
+        return
+    assert rc == 0, rc
     assert torch.equal(buf[:, :width], ref)
     assert not bool(torch.isnan(buf).any()) and float(buf[:, width:].abs().sum()) == 0.0
     exp = R.interaction_forward(dense.cpu().numpy(), sparse.cpu().numpy())

@@ -713,14 +713,17 @@ def _check_sort(ops, hsc, indices, offsets, B, bits, weighted=False, idx_dtype=n
         np.testing.assert_array_equal(srt.bag_of_pos.cpu().numpy(), bag)
 
 
+@pytest.mark.parametrize("fused", ["1", "0"])
 @pytest.mark.parametrize("case", ["criteo_rows", "zipf", "one_big_table", "tiny_tables", "empty_tables",
                                   "shared_tables", "unsorted_bases", "keys64", "many_tables", "int32_ids"])
-def test_index_transpose_is_a_stable_argsort(ops, case):
+def test_index_transpose_is_a_stable_argsort(ops, case, fused, monkeypatch):
     """b200_tbe_sort_indices (hand-written segmented LSD radix sort, csrc/tbe_sort.cu) == a stable argsort of
     the linearised keys, bit for bit, payload included (the reference: linearize + cub radix_sort_pairs,
     split_embeddings_utils.cu:139-306).  Cases cover every plan branch: 0/1/2/3+ passes per table, tables with
     no ids, features sharing a table (one segment), hash bases that are not grouped by table (single-segment
     fallback), 64-bit keys, tiles spanning several chunks, int32 ids, heavy duplicates."""
+    # both pass implementations: fused (one kernel per pass, decoupled look-back) and the three-kernel passes
+    monkeypatch.setenv("B200_SORT_FUSED", fused)
     rng = np.random.default_rng(sum(map(ord, case)))
     weighted, idt = False, np.int64
     if case == "criteo_rows":

@@ -20,6 +20,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "b200_sparse.h"
 #include "common.cuh"
@@ -50,9 +51,9 @@ struct SortPlanView {
   int32_t* seg_passes;
   int64_t* seg_p0;
   int32_t* seg_tile0;
-  int64_t* tile_rec;  // [max_tiles][5]: (passes << 32 | seg), begin, end, key base, segment start
+  int64_t* tile_rec;  // [max_tiles][6]: (passes << 32 | seg), begin, end, key base, segment start, first tile
 };
-constexpr int kTileRecWords = 5;
+constexpr int kTileRecWords = 6;
 constexpr int kHdrNseg = 0, kHdrPass = 1, kHdrTiles = 1 + kSortMaxPasses;
 
 // ------------------------------------------------------------------------------------ plan
@@ -161,6 +162,7 @@ sort_plan_kernel(const int64_t* __restrict__ hsc, const void* __restrict__ offse
     rec[2] = begin + tile_size < seg_end ? begin + tile_size : seg_end;
     rec[3] = pv.seg_base[lo];
     rec[4] = p0;
+    rec[5] = pv.seg_tile0[lo];
   }
 }
 
@@ -242,6 +244,7 @@ tbe_linearize_kernel(const void* __restrict__ indices, const void* __restrict__ 
 struct TileInfo {
   int32_t seg;
   int32_t passes;
+  int32_t first_tile;  // first tile of the segment
   int64_t begin, end;  // positions
   int64_t base;        // key base of the segment
   int64_t seg_p0;
@@ -253,8 +256,9 @@ __device__ __forceinline__ bool sort_tile_info(const SortPlanView& pv, int32_t t
   // all six loads are independent: one round trip (records past the last tile are garbage but mapped)
   const int64_t* rec = pv.tile_rec + (int64_t)tile * kTileRecWords;
   const int32_t total = pv.hdr[kHdrTiles];
-  const int64_t r0 = rec[0], r1 = rec[1], r2 = rec[2], r3 = rec[3], r4 = rec[4];
+  const int64_t r0 = rec[0], r1 = rec[1], r2 = rec[2], r3 = rec[3], r4 = rec[4], r5 = rec[5];
   if (tile >= total) return false;
+  ti.first_tile = (int32_t)r5;
   ti.seg = (int32_t)(r0 & 0xffffffff);
   ti.passes = (int32_t)(r0 >> 32);
   if (pass >= ti.passes) return false;
@@ -484,6 +488,227 @@ sort_scatter_kernel(K* __restrict__ keys_a, int32_t* __restrict__ pay_a, K* __re
   }
 }
 
+// ------------------------------------------------------------------------------------ fused passes
+// One kernel per pass ("onesweep"): the digit histograms of EVERY pass depend only on the keys, not on their
+// order, so they are taken once up front (sort_hist_all_kernel) and turned into per-segment bin bases
+// (sort_bases_kernel); a pass then needs, per tile and bin, only the number of such elements in the EARLIER
+// tiles of its segment, which it gets by decoupled look-back over the tiles' published counts (status words:
+// 2 flag bits + 30 count bits; tile ids are handed out by an atomic ticket, so a tile only ever waits for
+// tiles that are already running).  Per pass the keys are read once and written once; the separate histogram
+// and scan launches of the three-kernel path are gone.  Used when a tile is one chunk (N <= 4 M ids).
+constexpr uint32_t kStAgg = 1u << 30, kStIncl = 2u << 30, kStMask = (1u << 30) - 1;
+
+template <typename K>
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_all_kernel(const K* __restrict__ keys_a, const K* __restrict__ keys_b, int64_t tile_size, int P,
+                     uint32_t* __restrict__ ghist, SortPlanView pv) {
+  extern __shared__ uint32_t s_hist[];  // [P][512]
+  TileInfo ti;
+  if (!sort_tile_info(pv, blockIdx.x, 0, tile_size, ti)) return;  // pass 0: every segment with >= 1 pass
+  const K* __restrict__ src = (ti.passes & 1) ? keys_b : keys_a;     // where linearize put this segment
+  const int np = ti.passes < P ? ti.passes : P;
+  for (int i = threadIdx.x; i < np * kSortBins; i += kSortThreads) s_hist[i] = 0;
+  __syncthreads();
+  for (int64_t c0 = ti.begin; c0 < ti.end; c0 += kSortChunk) {
+    K key[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int64_t p = c0 + r * kSortThreads + threadIdx.x;
+      key[r] = p < ti.end ? src[p] : (K)0;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int64_t p = c0 + r * kSortThreads + threadIdx.x;
+      if (p < ti.end)
+        for (int q = 0; q < np; ++q)
+          atomicAdd(&s_hist[q * kSortBins + sort_digit<K>(key[r], ti.base, q * kSortDigitBits)], 1u);
+    }
+  }
+  __syncthreads();
+  uint32_t* g = ghist + (size_t)ti.seg * P * kSortBins;
+  for (int i = threadIdx.x; i < np * kSortBins; i += kSortThreads) {
+    const uint32_t v = s_hist[i];
+    if (v) atomicAdd(&g[i], v);
+  }
+}
+
+// ghist[seg][pass][:] -> exclusive scan over the 512 bins, in place.  grid (T, P), 512 threads.
+__global__ void __launch_bounds__(kSortBins)
+sort_bases_kernel(uint32_t* __restrict__ ghist, int P, SortPlanView pv) {
+  const int seg = blockIdx.x, pass = blockIdx.y;
+  if (seg >= pv.hdr[kHdrNseg] || pass >= pv.seg_passes[seg]) return;
+  __shared__ uint32_t warp_tot[kSortBins / 32];
+  uint32_t* g = ghist + ((size_t)seg * P + pass) * kSortBins;
+  const int bin = threadIdx.x, lane = bin & 31;
+  const uint32_t tot = g[bin];
+  uint32_t inc = tot;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(kFull, inc, d);
+    if (lane >= d) inc += v;
+  }
+  if (lane == 31) warp_tot[bin >> 5] = inc;
+  __syncthreads();
+  uint32_t before = 0;
+  for (int w = 0; w < (bin >> 5); ++w) before += warp_tot[w];
+  g[bin] = before + inc - tot;
+}
+
+__device__ __forceinline__ void st_release_v2(uint32_t* p, uint32_t a, uint32_t b) {
+  asm volatile("st.release.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ uint2 ld_acquire_v2(const uint32_t* p) {
+  uint2 v;
+  asm volatile("ld.acquire.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
+
+template <typename K>
+__global__ void __launch_bounds__(kSortThreads, 3)
+sort_onesweep_kernel(K* __restrict__ keys_a, int32_t* __restrict__ pay_a, K* __restrict__ keys_b,
+                     int32_t* __restrict__ pay_b, int pass, int P, int64_t max_tiles,
+                     const uint32_t* __restrict__ ghist, uint32_t* __restrict__ status,
+                     uint32_t* __restrict__ tickets, SortPlanView pv) {
+  __shared__ uint32_t off[kSortBins];
+  __shared__ uint32_t lbase[kSortBins];
+  __shared__ uint32_t wcnt[kSortWarps][kSortBins];
+  __shared__ uint32_t warp_sum[kSortWarps];
+  __shared__ K s_key[kSortChunk];
+  __shared__ int32_t s_pay[kSortChunk];
+  __shared__ int32_t s_tile;
+  if (threadIdx.x == 0) s_tile = (int32_t)atomicAdd(&tickets[pass], 1u);
+  for (int i = threadIdx.x; i < kSortWarps * kSortBins; i += kSortThreads) (&wcnt[0][0])[i] = 0;
+  __syncthreads();
+  const int32_t tile = s_tile;
+  TileInfo ti;
+  if (!sort_tile_info(pv, tile, pass, kSortChunk, ti)) return;
+  const bool from_b = ((ti.passes - pass) & 1) != 0;
+  const K* __restrict__ src_k = from_b ? keys_b : keys_a;
+  const int32_t* __restrict__ src_p = from_b ? pay_b : pay_a;
+  K* __restrict__ dst_k = from_b ? keys_a : keys_b;
+  int32_t* __restrict__ dst_p = from_b ? pay_a : pay_b;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  const int shift = pass * kSortDigitBits;
+  K key[8];
+  int32_t pay[8];
+  int32_t dg[8];
+  uint32_t rank[8];
+  const int64_t w0 = ti.begin + warp * 256;
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int64_t p = w0 + r * 32 + lane;
+    const bool valid = p < ti.end;
+    key[r] = valid ? src_k[p] : (K)0;
+    pay[r] = valid ? src_p[p] : 0;
+    dg[r] = valid ? sort_digit<K>(key[r], ti.base, shift) : -1;
+  }
+  // bin bases of the segment for this pass (independent of the look-back: loaded early)
+  const uint32_t* gb = ghist + ((size_t)ti.seg * P + pass) * kSortBins;
+  const uint32_t gb0 = gb[2 * threadIdx.x], gb1 = gb[2 * threadIdx.x + 1];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int d = dg[r] >= 0 ? dg[r] : kSortBins + lane;
+    const unsigned m = __match_any_sync(kFull, d);
+    if (dg[r] >= 0) rank[r] = wcnt[warp][d] + __popc(m & lt);
+    __syncwarp();
+    if (dg[r] >= 0 && (int)(__ffs(m) - 1) == lane) wcnt[warp][d] += __popc(m);
+    __syncwarp();
+  }
+  __syncthreads();
+  uint32_t tot[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int bin = 2 * threadIdx.x + j;
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) run += wcnt[w][bin];
+    tot[j] = run;
+  }
+  // publish this tile's counts, then look back over the earlier tiles of the segment
+  uint32_t* st_row = status + ((size_t)pass * max_tiles + tile) * kSortBins + 2 * threadIdx.x;
+  const bool first = tile == ti.first_tile;
+  st_release_v2(st_row, tot[0] | (first ? kStIncl : kStAgg), tot[1] | (first ? kStIncl : kStAgg));
+  uint32_t ex0 = 0, ex1 = 0;
+  if (!first) {
+    // four predecessors per round trip: the tiles of a segment start together, so at first only aggregates
+    // are published and the walk is as deep as the tile's position in its segment
+    int32_t t = tile - 1;
+    bool done = false;
+    while (!done) {
+      constexpr int kLook = 4;
+      uint2 u[kLook];
+      const int cnt = min(kLook, t - ti.first_tile + 1);
+#pragma unroll
+      for (int i = 0; i < kLook; ++i)
+        if (i < cnt)
+          u[i] = ld_acquire_v2(status + ((size_t)pass * max_tiles + (t - i)) * kSortBins + 2 * threadIdx.x);
+      int used = 0;
+#pragma unroll
+      for (int i = 0; i < kLook; ++i) {
+        if (i < cnt && i == used && !done) {
+          const uint32_t f = u[i].x >> 30;
+          if (f != 0) {
+            ex0 += u[i].x & kStMask;
+            ex1 += u[i].y & kStMask;
+            ++used;
+            if (f == 2u) done = true;
+          }
+        }
+      }
+      t -= used;
+      if (t < ti.first_tile) done = true;
+    }
+    st_release_v2(st_row, (ex0 + tot[0]) | kStIncl, (ex1 + tot[1]) | kStIncl);
+  }
+  off[2 * threadIdx.x] = gb0 + ex0;
+  off[2 * threadIdx.x + 1] = gb1 + ex1;
+  // slot bases inside the chunk (exclusive scan over the bins) and the reordered copy, as in sort_scatter_kernel
+  uint32_t inc = tot[0] + tot[1];
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(kFull, inc, d);
+    if (lane >= d) inc += v;
+  }
+  if (lane == 31) warp_sum[warp] = inc;
+  __syncthreads();
+  uint32_t before = 0;
+#pragma unroll
+  for (int w = 0; w < kSortWarps; ++w) before += w < warp ? warp_sum[w] : 0u;
+  uint32_t base = before + inc - (tot[0] + tot[1]);
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int bin = 2 * threadIdx.x + j;
+    lbase[bin] = base;
+    uint32_t run = base;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {  // counts -> slot bases of the warps' slices, in warp order
+      const uint32_t c = wcnt[w][bin];
+      wcnt[w][bin] = run;
+      run += c;
+    }
+    base += tot[j];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    if (dg[r] >= 0) {
+      const uint32_t slot = wcnt[warp][dg[r]] + rank[r];
+      s_key[slot] = key[r];
+      s_pay[slot] = pay[r];
+    }
+  }
+  __syncthreads();
+  const int n = (int)(ti.end - ti.begin);
+  for (int i = threadIdx.x; i < n; i += kSortThreads) {
+    const K k = s_key[i];
+    const int d = sort_digit<K>(k, ti.base, shift);
+    const int64_t q = ti.seg_p0 + off[d] + (uint32_t)(i - lbase[d]);
+    dst_k[q] = k;
+    dst_p[q] = s_pay[i];
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -494,6 +719,12 @@ struct SortWs {
   void* keys_b;
   int32_t* pay_b;
   uint32_t* counts;
+  uint32_t* zeroed;      // [ghist | status | tickets]: cleared with one memset per call (fused passes)
+  size_t zeroed_bytes;
+  uint32_t* ghist;       // [T][P][512]
+  uint32_t* status;      // [P][max_tiles][512]
+  uint32_t* tickets;     // [kSortMaxPasses]
+  int P;
   SortPlanView pv;
   int64_t tile_size;
   int64_t max_tiles;
@@ -530,6 +761,15 @@ SortWs sort_ws_layout(void* ws, int64_t N, int key_bits, int32_t T) {
   p += sort_align256(4 * n1);
   w.pv.tile_rec = (int64_t*)p;
   p += sort_align256(8 * (size_t)kTileRecWords * (size_t)w.max_tiles);
+  w.P = (key_bits + kSortDigitBits - 1) / kSortDigitBits;
+  w.zeroed = (uint32_t*)p;
+  w.ghist = (uint32_t*)p;
+  p += sort_align256((size_t)T * w.P * kSortBins * sizeof(uint32_t));
+  w.status = (uint32_t*)p;
+  p += sort_align256((size_t)w.P * (size_t)w.max_tiles * kSortBins * sizeof(uint32_t));
+  w.tickets = (uint32_t*)p;
+  p += 256;
+  w.zeroed_bytes = (size_t)(p - (char*)w.zeroed);
   w.bytes = (size_t)(p - (char*)ws) + 256;
   return w;
 }
@@ -562,6 +802,26 @@ int sort_impl(const void* indices, const void* offsets, bool idx64, const int64_
   B200_CUDA_TRY(cudaFuncSetAttribute(sort_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scan_smem));
   const int host_bits = max_table_bits > 0 && max_table_bits < key_bits ? max_table_bits : key_bits;
   const int passes = (host_bits + kSortDigitBits - 1) / kSortDigitBits;
+  // fused passes (one kernel per pass, decoupled look-back) when a tile is one chunk; B200_SORT_FUSED=0 keeps the
+  // three-kernel passes below, which also serve larger problems
+  const char* fused_env = getenv("B200_SORT_FUSED");  // read per call: the tests exercise both paths
+  const bool fused_on = !(fused_env && fused_env[0] == '0');
+  if (fused_on && w.tile_size == kSortChunk && N < (1LL << 30)) {
+    B200_CUDA_TRY(cudaMemsetAsync(w.zeroed, 0, w.zeroed_bytes, s));
+    B200_CUDA_TRY(cudaFuncSetAttribute(sort_hist_all_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(kSortMaxPasses * kSortBins * sizeof(uint32_t))));
+    sort_hist_all_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, (size_t)w.P * kSortBins * sizeof(uint32_t), s>>>(
+        keys_a, keys_b, w.tile_size, w.P, w.ghist, w.pv);
+    B200_LAUNCH_CHECK();
+    sort_bases_kernel<<<dim3((unsigned)T, (unsigned)passes), kSortBins, 0, s>>>(w.ghist, w.P, w.pv);
+    B200_LAUNCH_CHECK();
+    for (int pass = 0; pass < passes; ++pass) {
+      sort_onesweep_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(
+          keys_a, sorted_payload, keys_b, w.pay_b, pass, w.P, w.max_tiles, w.ghist, w.status, w.tickets, w.pv);
+      B200_LAUNCH_CHECK();
+    }
+    return B200_OK;
+  }
   for (int pass = 0; pass < passes; ++pass) {
     sort_hist_kernel<K><<<(unsigned)w.max_tiles, kSortThreads, 0, s>>>(keys_a, keys_b, pass, w.tile_size,
                                                                      w.counts, w.pv);

@@ -48,6 +48,9 @@ def parse_args():
     ap.add_argument("--cpu-batch", type=int, default=65536, help="batch of the bounded CPU sample")
     ap.add_argument("--cpu-row-cap", type=int, default=1000000, help="row cap of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--check", action="store_true",
+                    help="instead of timing: run the sharded-vs-unsharded multi-step parity check "
+                         "(tests/dist_parity_worker.py) on this launch's ranks and print its verdict")
     ap.add_argument("--cuda-graph", type=int, default=int(os.environ.get("B200_CUDA_GRAPH", "0")),
                     help="replay the steady-state step as a CUDA graph (TrainPipelineSparseDist(cuda_graph=True))")
     return ap.parse_args()
@@ -538,7 +541,21 @@ def run_ours(args) -> None:
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.check:
+        # N ranks (torchrun): six training steps of a table-wise + row-wise sharded DLRM against the unsharded model
+        # on the same global batches - every step's predictions and the final weights must agree
+        # (torchrec/distributed/test_utils/test_model_parallel_base.py:144-290 is the reference pattern)
+        import runpy
+        os.environ.setdefault("RANK", "0")
+        os.environ.setdefault("WORLD_SIZE", "1")
+        os.environ.setdefault("LOCAL_RANK", "0")
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29572")
+        runpy.run_path(os.path.join(ROOT, "tests", "dist_parity_worker.py"), run_name="__main__")
+        if int(os.environ["RANK"]) == 0:
+            print(json.dumps({"check": "ok", "world": int(os.environ["WORLD_SIZE"]),
+                              "what": "sharded == unsharded over B200_PARITY_STEPS (6) steps"}))
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)

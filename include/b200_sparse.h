@@ -315,7 +315,8 @@ int b200_tbe_forward_peer(const void* weights, int weight_dtype, const int64_t* 
 
 /* b200_tbe_backward whose gradient row of global sample b is read from
  * grad_bases[b / B_src] + (b % B_src) * grad_stride + src_col[t], scaled by grad_scale
- * (the 1/W of comm_ops.py:527-528, 883). */
+ * (the 1/W of comm_ops.py:527-528, 883).  per_sample_weights / bag_of_pos as in b200_tbe_backward (weighted
+ * features); stochastic_rounding, sr_seed, sr_offset as in b200_tbe_backward_sr (fp16 / bf16 tables). */
 int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, int32_t n_src,
                            int32_t B_src, int64_t grad_stride, const int32_t* src_col /*device [T]*/,
                            float grad_scale, const void* sorted_keys,
@@ -326,7 +327,8 @@ int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, in
                            int32_t all_D_mult8, const void* offsets, int index_dtype,
                            const float* per_sample_weights, int pooling_mode, int optimizer,
                            float* momentum1, const int64_t* momentum1_offsets,
-                           float learning_rate, float eps, void* partial_scratch, void* stream);
+                           float learning_rate, float eps, void* partial_scratch,
+                           int32_t stochastic_rounding, uint64_t sr_seed, uint64_t sr_offset, void* stream);
 
 /* Row-wise sharding: out[b, out_col4[c] : +4] = sum_r stage[r][b][4c : 4c+4] (rank order) for every
  * float4 column c of the stage [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer;

@@ -37,11 +37,15 @@ def main() -> None:
         return [EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r, feature_names=[keys[i]])
                 for i, r in enumerate(rows)]
 
+    # B200_PARITY_WEIGHTED=1: a weighted collection (per-id weights travel with the KJT through the input dist and
+    # scale the pooled rows / their gradients), which the peer exchange serves as well
+    weighted = os.environ.get("B200_PARITY_WEIGHTED", "0") == "1"
     torch.manual_seed(7)  # identical on every rank
-    glob = DLRM(EmbeddingBagCollection(tables(), device=dev), 13, [32, D], [32, 16, 1], dense_device=dev)
+    glob = DLRM(EmbeddingBagCollection(tables(), is_weighted=weighted, device=dev), 13, [32, D], [32, 16, 1],
+                dense_device=dev)
     torch.manual_seed(7)
-    local = DLRM(EmbeddingBagCollection(tables(), device=torch.device("meta")), 13, [32, D], [32, 16, 1],
-                 dense_device=dev)
+    local = DLRM(EmbeddingBagCollection(tables(), is_weighted=weighted, device=torch.device("meta")), 13, [32, D],
+                 [32, 16, 1], dense_device=dev)
     sharders = [EmbeddingBagCollectionSharder(fused_params={"learning_rate": lr, "optimizer": EmbOptimType.EXACT_SGD})]
     plan = EmbeddingShardingPlanner(Topology(world), {f"t{i}": ParameterConstraints(sharding_types=[s])
                                                       for i, s in enumerate(sharding)}).plan(local, sharders)
@@ -98,7 +102,12 @@ def main() -> None:
         vals_all = [torch.empty_like(batch.sparse_features.values()) for _ in range(world)]
         dist.all_gather(vals_all, batch.sparse_features.values())
         gvalues = torch.cat([v.view(F, B * 2) for v in vals_all], dim=1).reshape(-1)
-        gkjt = KeyedJaggedTensor(keys=keys, values=gvalues,
+        gweights = None
+        if weighted:
+            w_all = [torch.empty_like(batch.sparse_features.weights()) for _ in range(world)]
+            dist.all_gather(w_all, batch.sparse_features.weights())
+            gweights = torch.cat([v.view(F, B * 2) for v in w_all], dim=1).reshape(-1)
+        gkjt = KeyedJaggedTensor(keys=keys, values=gvalues, weights=gweights,
                                  lengths=torch.full((F * B * world,), 2, dtype=torch.int32, device=dev),
                                  stride=B * world)
         return torch.cat(dense_all, dim=0), gkjt
@@ -108,6 +117,12 @@ def main() -> None:
     for step in range(steps):
         batch = next(iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2,
                                            num_dense=13, manual_seed=100 + rank + 1000 * step))).to(dev)
+        if weighted:
+            kj = batch.sparse_features
+            gen = torch.Generator(device=dev).manual_seed(5000 + rank + 1000 * step)
+            batch.sparse_features = KeyedJaggedTensor(
+                keys=kj.keys(), values=kj.values(), lengths=kj.lengths(), stride=kj.stride(),
+                weights=torch.rand(kj.values().numel(), device=dev, generator=gen) + 0.5)
         gdense, gkjt = global_view(batch)
         opt_g.zero_grad()
         # DDP averages dense grads over ranks and the pooled collectives divide by W (GRADIENT_DIVISION):
@@ -148,7 +163,7 @@ def main() -> None:
         mode = "peer" if want_push else "peer_pull"
     dist.barrier()
     if rank == 0:
-        print(f"DIST PARITY OK world={world} exchange={mode} steps={steps}")
+        print(f"DIST PARITY OK world={world} exchange={mode} steps={steps} weighted={int(weighted)}")
     dist.destroy_process_group()
 
 

@@ -318,6 +318,25 @@ def test_multi_gpu_sharded_vs_unsharded(world, exchange):
     assert r.returncode == 0 and f"exchange={exchange}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
+def test_multi_gpu_weighted_collection_vs_unsharded(exchange):
+    """A WEIGHTED EmbeddingBagCollection (per-id weights) sharded table-wise + row-wise over 2 GPUs: the peer
+    exchange carries the weights into the fused lookup and the fused backward (weighted index transpose), six steps
+    against the unsharded model; the NCCL path likewise."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, B200_PEER_DIST="0" if exchange == "nccl" else "1", B200_PARITY_WEIGHTED="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29671",
+                        os.path.join(here, "dist_parity_worker.py")], capture_output=True, text=True, timeout=300,
+                       env=env)
+    assert r.returncode == 0 and f"exchange={exchange}" in r.stdout and "weighted=1" in r.stdout, \
+        r.stdout[-2000:] + r.stderr[-4000:]
+
+
 @pytest.mark.parametrize("world", [1, 2])
 def test_reference_torchrec_runs_over_this_fbgemm_gpu(world):
     """The drop-in claim shown, not asserted: the REFERENCE's torchrec (copied unmodified into the git-ignored

@@ -482,6 +482,38 @@ def test_backward_peer_gather(ops, case, opt):
         np.testing.assert_allclose(momg.cpu().numpy(), mom_ref, rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("variant", ["weighted", "fp16_sr", "weighted_bf16_sr"])
+def test_backward_peer_weighted_and_stochastic_rounding(ops, variant):
+    """b200_tbe_backward_peer with per-sample weights (weighted sort: payload = position, bag_of_pos) and with
+    stochastic rounding of 16-bit rows == b200_tbe_backward / b200_tbe_backward_sr on the same gradient held in one
+    local [B, total_D] buffer, bit for bit (same kernels, the gradient only arrives through the base-pointer table)."""
+    weighted = "weighted" in variant
+    wdt = "fp32" if variant == "weighted" else ("fp16" if "fp16" in variant else "bf16")
+    sr = wdt != "fp32"
+    rng = np.random.default_rng(len(variant))
+    rows, dims, B, L = [300, 17, 4000], [64, 32, 128], 256, 4
+    T = len(rows)
+    w, wo, Do, hsc = build_tables(rng, rows, dims, wdt)
+    _, offsets, indices = make_jagged(rng, T, B, L, rows, idx_dtype=np.int64)
+    psw = dev(rng.random(indices.size).astype(np.float32)) if weighted else None
+    total_D = int(Do[-1])
+    grad = dev(rng.standard_normal((B, total_D)).astype(np.float32))
+    mom = rng.random(int(hsc[-1])).astype(np.float32)
+    bits = int(np.log2(int(hsc[-1])) + 1)
+    d_off, d_wo, d_Do, d_hsc, d_mo = dev(offsets), dev(wo), dev(Do), dev(hsc), dev(hsc[:-1].copy())
+    srt = ops.tbe_sort_indices(dev(indices), d_off, d_hsc, bits, B, weighted)
+    mult8 = all(d % 8 == 0 for d in dims)
+    w_a, m_a = w.cuda(), dev(mom)
+    ops.tbe_backward(grad, srt, w_a, d_wo, d_Do, d_hsc, B, max(dims), mult8, d_off, psw, 0, 1, m_a, d_mo, 0.05, 1e-8,
+                     sr, 1234, 7)
+    w_b, m_b = w.cuda(), dev(mom)
+    bases = torch.tensor([grad.data_ptr()], dtype=torch.int64, device="cuda")
+    ops.tbe_backward_peer(bases, B, total_D, dev(Do[:-1].copy()), 1.0, srt, w_b, d_wo, d_Do, d_hsc, B, max(dims), mult8,
+                          d_off, psw, 0, 1, m_b, d_mo, 0.05, 1e-8, sr, 1234, 7)
+    assert not torch.equal(w_b, w.cuda())
+    assert torch.equal(w_a, w_b) and torch.equal(m_a, m_b)
+
+
 def test_peer_stage_reduce(ops):
     rng = np.random.default_rng(5)
     W, B, Dw, pitch, col = 3, 37, 24, 64, 16

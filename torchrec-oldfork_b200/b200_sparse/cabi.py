@@ -40,7 +40,7 @@ SIGNATURES = {
                                      _int, _p, _i32, _i32, _i64, _p, _int, _i32, _p, _i64, _p, _p]),
     "b200_tbe_backward_peer": (_int, [_p, _i32, _i32, _i64, _p, _f32, _p, _p, _p, _i64, _int, _p, _int, _p, _p,
                                       _p, _i32, _i32, _i32, _i32, _p, _int, _p, _int, _int, _p, _p, _f32, _f32,
-                                      _p, _p]),
+                                      _p, _i32, C.c_uint64, C.c_uint64, _p]),
     "b200_peer_stage_reduce": (_int, [_p, _i32, _i32, _i32, _p, _i64, _p, _i32, _p]),
     "b200_peer_barrier": (_int, [_p, _i32, _i32, _p, _p]),
     "b200_peer_stage_reduce_flagged": (_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _i64, _p, _p]),

@@ -507,8 +507,11 @@ def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, sr
                       D_offsets: torch.Tensor, hash_size_cumsum: torch.Tensor, B: int, max_D: int,
                       all_D_mult8: bool, offsets: torch.Tensor, per_sample_weights: Optional[torch.Tensor],
                       pooling_mode: int, optimizer: int, momentum1: Optional[torch.Tensor],
-                      momentum1_offsets: Optional[torch.Tensor], learning_rate: float, eps: float) -> None:
-    """Fused backward + optimizer reading the gradient row of sample b from grad_bases[b // B_src]."""
+                      momentum1_offsets: Optional[torch.Tensor], learning_rate: float, eps: float,
+                      stochastic_rounding: bool = False, sr_seed: int = 0, sr_offset: int = 0) -> None:
+    """Fused backward + optimizer reading the gradient row of sample b from grad_bases[b // B_src].
+    per_sample_weights needs a weighted sort (payload = position, srt.bag_of_pos); stochastic_rounding as in
+    tbe_backward."""
     dev = _need_cuda(grad_bases, src_col, weights, weights_offsets, D_offsets, hash_size_cumsum, offsets)
     if grad_bases.dtype != torch.int64 or src_col.dtype != torch.int32:
         raise TypeError("grad_bases must be int64 addresses and src_col int32 columns")
@@ -525,7 +528,8 @@ def tbe_backward_peer(grad_bases: torch.Tensor, B_src: int, grad_stride: int, sr
                                          int(all_D_mult8), _p(offsets), _idx_dt(offsets, "offsets"),
                                          _p(per_sample_weights), int(pooling_mode), int(optimizer), _p(momentum1),
                                          _p(momentum1_offsets), float(learning_rate), float(eps), _p(scratch),
-                                         _stream(dev)), "b200_tbe_backward_peer")
+                                         int(bool(stochastic_rounding)), int(sr_seed) & (2 ** 64 - 1),
+                                         int(sr_offset) & (2 ** 64 - 1), _stream(dev)), "b200_tbe_backward_peer")
 
 
 def peer_stage_reduce(stage: torch.Tensor, W: int, B_local: int, Dw: int, out: torch.Tensor,

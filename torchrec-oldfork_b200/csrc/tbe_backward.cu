@@ -1090,7 +1090,8 @@ extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_
                                       int index_dtype, const float* per_sample_weights,
                                       int pooling_mode, int optimizer, float* momentum1,
                                       const int64_t* momentum1_offsets, float learning_rate,
-                                      float eps, void* partial_scratch, void* stream) {
+                                      float eps, void* partial_scratch, int32_t stochastic_rounding,
+                                      uint64_t sr_seed, uint64_t sr_offset, void* stream) {
   if (!grad_bases || !src_col || n_src <= 0 || B_src <= 0 || (int64_t)n_src * B_src < B)
     return B200_EINVAL;
   return tbe_backward_impl(nullptr, grad_stride, sorted_keys, sorted_payload, bag_of_pos, N,
@@ -1098,5 +1099,5 @@ extern "C" int b200_tbe_backward_peer(const float* const* grad_bases, int32_t n_
                            hash_size_cumsum, T, B, max_D, all_D_mult8, offsets, index_dtype,
                            per_sample_weights, pooling_mode, optimizer, momentum1,
                            momentum1_offsets, learning_rate, eps, partial_scratch, grad_bases,
-                           B_src, src_col, grad_scale, 0, 0, 0, stream);
+                           B_src, src_col, grad_scale, stochastic_rounding ? 1 : 0, sr_seed, sr_offset, stream);
 }

@@ -226,7 +226,7 @@ class ShardedEmbeddingBagCollection(ShardedModule[SparseFeaturesList, List[torch
         if not self._peer_checked:
             from torchrec.distributed import peer_dist
             self._peer_checked = True
-            if not self._is_weighted and not self._variable_batch_size:
+            if not self._variable_batch_size:
                 self._peer = peer_dist.try_build(self, self._env.process_group, self._device)
         return self._peer
 

@@ -24,8 +24,10 @@ backward  table-wise : the kernel that PRODUCES the gradient of the pooled rows 
 
 Three stream-ordered cross-rank barriers per step bracket the peer accesses; no pooled
 [B_global, D_local] tensor, no NCCL pass over the embeddings and no split/cat copy exist.
-Enabled for CUDA process groups with world_size > 1 (B200_PEER_DIST=0 disables it); the NCCL path in
-comm_ops.py / dist_data.py stays as the portable implementation and is what the gloo tests run.
+Enabled for CUDA process groups with world_size > 1 (B200_PEER_DIST=0 disables it), for unweighted and weighted
+collections and for 16-bit tables with stochastic rounding; gradient clipping, variable batch sizes and sequence
+embeddings take the NCCL path in comm_ops.py / dist_data.py, which stays as the portable implementation and is what
+the gloo tests run.
 """
 from __future__ import annotations
 
@@ -195,6 +197,7 @@ class PeerLookupDist:
         self._tw_of: Dict[str, Tuple[int, int]] = {}  # embedding name -> (owner rank, column in its gin)
         self._tw_pitch = 0
         self._rw_dim = 0
+        self._weighted = False  # the collection's features carry per-id weights (id_score_list features)
         self._rw_col4: Optional[torch.Tensor] = None
         self._rw_feat_col4: Optional[torch.Tensor] = None
         self._rw_features = 0
@@ -203,18 +206,20 @@ class PeerLookupDist:
             return torch.tensor([col_of[n] for n in names], dtype=torch.int32, device=device)
 
         for sharding, lookup in zip(sebc._sharding_type_to_sharding.values(), sebc._lookups):
-            mods = list(lookup._emb_modules)
-            if len(lookup._score_emb_modules):
-                raise NotImplementedError("weighted features take the NCCL path")
-            if any(getattr(m.emb_module, "_sr_on", False) for m in mods):
-                raise NotImplementedError("stochastic rounding of fp16/bf16 tables takes the NCCL path")
+            # a collection is either unweighted (id_list features) or weighted (id_score_list features)
+            if len(lookup._emb_modules) and len(lookup._score_emb_modules):
+                raise NotImplementedError("mixed weighted / unweighted lookups take the NCCL path")
+            self._weighted = bool(len(lookup._score_emb_modules)) or getattr(self, "_weighted", False)
+            mods = list(lookup._score_emb_modules) if len(lookup._score_emb_modules) else list(lookup._emb_modules)
             if any(m.emb_module.optimizer_args.gradient_clipping for m in mods):
                 raise NotImplementedError("gradient clipping takes the NCCL path")
             parts: List[_Part] = []
             if isinstance(sharding, BaseTwEmbeddingSharding):
                 # every rank's table-wise features, in that rank's module order: the layout of its gin
                 tw_dims = []
-                for r, cfgs in enumerate(sharding._grouped_embedding_configs_per_rank):
+                per_rank = (sharding._score_grouped_embedding_configs_per_rank if self._weighted
+                            else sharding._grouped_embedding_configs_per_rank)
+                for r, cfgs in enumerate(per_rank):
                     local = 0
                     for cfg in cfgs:
                         for n, d in zip(cfg.embedding_names(), cfg.embedding_dims()):
@@ -280,16 +285,17 @@ class PeerLookupDist:
     def __call__(self, dist_input, B_local: int) -> torch.Tensor:
         """dist_input: SparseFeaturesList (one per sharding) after the KJT all-to-all; B_local: this
         rank's batch size (every rank must use the same one: no variable batch)."""
-        work = []  # (part, indices, offsets)
+        work = []  # (part, indices, offsets, per-sample weights)
         for parts, sf in zip(self._parts, dist_input):
-            kjt = sf.id_list_features
+            kjt = sf.id_score_list_features if self._weighted else sf.id_list_features
             if not parts:
                 continue
             pieces = kjt.split([p.n_features for p in parts]) if len(parts) > 1 else [kjt]
             for p, piece in zip(parts, pieces):
                 assert piece.stride() == B_local * self._W, "variable batch size per rank is out of scope"
                 idx, off = p.tbe.prepare_indices(piece.values(), piece.offsets())
-                work.append((p, idx, off))
+                psw = piece.weights().float().contiguous() if self._weighted else None
+                work.append((p, idx, off, psw))
         px = self.exchange(B_local)
         return _PeerLookup.apply(self, px, work, *self._placeholders)
 
@@ -308,7 +314,7 @@ class _PeerLookup(torch.autograd.Function):
                 "evaluation, or set B200_PEER_DIST=0 to use the NCCL path, which returns fresh tensors.")
         main = torch.cuda.current_stream(px.out.device)
         sorts = []
-        for p, idx, off in work:
+        for p, idx, off, psw in work:
             m = p.tbe
             T = m.D_offsets.numel() - 1
             B = (off.numel() - 1) // T
@@ -317,7 +323,7 @@ class _PeerLookup(torch.autograd.Function):
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
                     s = torch.ops.fbgemm.b200_tbe_sort_indices(idx, off, m.hash_size_cumsum,
-                                                               m.total_hash_size_bits, B, False,
+                                                               m.total_hash_size_bits, B, psw is not None,
                                                                getattr(m, "max_table_bits", 0))
                     ev = torch.cuda.Event()
                     ev.record(side)
@@ -336,12 +342,12 @@ class _PeerLookup(torch.autograd.Function):
         if not px.quiesced:
             px.barrier()
         px.quiesced = False
-        for (p, idx, off) in work:
+        for (p, idx, off, psw) in work:
             m = p.tbe
             bases = px.stage_bases if p.row_wise else px.out_bases
             pitch = px.rw_dim if p.row_wise else px.total_D
             _b200.tbe_forward_peer(m.weights_dev, m.weights_offsets, m.D_offsets, m.total_D, m.max_D,
-                                   m._all_D_mult8, idx, off, None, int(m.pooling_mode), bases, px.B_local, pitch,
+                                   m._all_D_mult8, idx, off, psw, int(m.pooling_mode), bases, px.B_local, pitch,
                                    p.dst_col, skip_empty=p.row_wise,
                                    flag_bases=px.flag_bases if p.row_wise else None,
                                    flag_pitch=px.rw_features * px.W, flag_col=p.flag_col if p.row_wise else None)
@@ -377,7 +383,7 @@ class _PeerLookup(torch.autograd.Function):
         px.barrier()  # C: every rank's gradient buffer is complete / every pushed row has landed
         px.quiesced = True
         scale = 1.0 / px.W if comm_ops.GRADIENT_DIVISION else 1.0
-        for (p, idx, off), (s, ev, B) in zip(ctx.work, ctx.sorts):
+        for (p, idx, off, psw), (s, ev, B) in zip(ctx.work, ctx.sorts):
             if s is None:
                 continue
             m = p.tbe
@@ -385,17 +391,18 @@ class _PeerLookup(torch.autograd.Function):
             assert not a.gradient_clipping  # refused at build time (PeerLookupDist.__init__)
             if ev is not None:
                 torch.cuda.current_stream(idx.device).wait_event(ev)
-            keys, payload, _bag = s
-            srt = _b200.SortedIndices(keys, payload, None, keys.numel(), max(1, m.total_hash_size_bits), None)
+            keys, payload, bag = s
+            srt = _b200.SortedIndices(keys, payload, bag if psw is not None else None, keys.numel(),
+                                      max(1, m.total_hash_size_bits), None)
             if pushed and not p.row_wise:  # my features' gradients of all B_global samples are in my gin
                 bases, B_src, pitch, src_col = px.gin_base, px.W * px.B_local, px.tw_pitch, p.gin_col
             else:
                 bases, B_src, pitch, src_col = px.grad_bases, px.B_local, px.total_D, p.src_col
             _b200.tbe_backward_peer(bases, B_src, pitch, src_col, scale, srt, m.weights_dev,
                                     m.weights_offsets, m.D_offsets, m.hash_size_cumsum, B, m.max_D, m._all_D_mult8,
-                                    off, None, int(m.pooling_mode), ta._OPT_CODE[m.optimizer],
+                                    off, psw, int(m.pooling_mode), ta._OPT_CODE[m.optimizer],
                                     m.momentum1_dev if m.momentum1_dev.numel() else None, m.momentum1_offsets,
-                                    a.learning_rate, a.eps)
+                                    a.learning_rate, a.eps, *m._next_sr_state())
         ctx.work = ctx.sorts = None
         return (None, None, None) + (None,) * ctx.n_placeholders
 

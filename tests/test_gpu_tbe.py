@@ -148,12 +148,38 @@ def test_backward(ops, case, wdt, opt, mode):
                      1 if mode == "mean" else 0, 0 if opt == "sgd" else 1,
                      momg if opt == "rowwise_adagrad" else None,
                      dev(mo) if opt == "rowwise_adagrad" else None, lr, eps)
-    tol = 1e-5 if wdt == "fp32" else 1e-2
-    # long runs (thousands of addends) are summed in a different association than the
-    # oracle's left-to-right loop: allow the fp32 reordering slack in atol
-    np.testing.assert_allclose(w_to_np(wg), w_ref.astype(np.float32), rtol=tol, atol=tol * 50)
-    if opt == "rowwise_adagrad":
-        np.testing.assert_allclose(momg.cpu().numpy(), mom_ref, rtol=1e-4, atol=1e-4)
+    # Tolerance, per table and DERIVED (north_star: rtol 1e-5 for fp32 tables, 1e-2 for 16-bit ones).  The only
+    # legitimate difference from the oracle's left-to-right loop is the association of the n addends of a run:
+    # every addition rounds by eps32 * |partial sum|, partial sums grow like sqrt(k) * sigma, so the sum is off by
+    # ~0.7 * n * eps32 * sigma; dG = 2 * n * eps32 * sigma (3x that) is the bound used.  The update scales it by lr
+    # (SGD) or lr / (sqrt(m) + eps) (rowwise Adagrad, m = the row's state after the step); the state itself moves
+    # by 2 |G| dG ~ 2 sqrt(n) sigma dG.  A table whose longest run is 3 ids is therefore held to ~1e-8 absolute
+    # beyond rtol; only the tiny tables (runs of thousands) get slack, exactly as much as their run length buys.
+    # 16-bit rows add one rounding of the stored value.
+    got_w, exp_w = w_to_np(wg), w_ref.astype(np.float32)
+    got_m = momg.cpu().numpy()
+    eps32, sigma = 2.0 ** -24, float(grad.std())
+    bag_of = np.repeat(np.arange(T * B), np.diff(offsets).astype(np.int64))
+    for t in range(T):
+        ids_t = indices[(bag_of // B) == t]
+        if ids_t.size == 0:
+            continue
+        uniq_t, counts = np.unique(ids_t, return_counts=True)
+        n_run = int(counts.max())
+        dG = 2.0 * n_run * eps32 * sigma
+        sl_w = slice(int(wo[t]), int(wo[t]) + rows[t] * dims[t])
+        sl_m = slice(int(hsc[t]), int(hsc[t + 1]))
+        if opt == "rowwise_adagrad":
+            m_touched = mom_ref[sl_m][uniq_t]
+            scale = lr / (np.sqrt(float(m_touched.min())) + eps)
+            np.testing.assert_allclose(got_m[sl_m], mom_ref[sl_m], rtol=1e-5,
+                                       atol=2.0 * np.sqrt(n_run) * sigma * dG + 1e-7,
+                                       err_msg=f"momentum1, table {t} (longest run {n_run})")
+        else:
+            scale = lr
+        atol = scale * dG + (0.0 if wdt == "fp32" else 2.0 ** -10 * float(np.abs(exp_w[sl_w]).max()))
+        np.testing.assert_allclose(got_w[sl_w], exp_w[sl_w], rtol=1e-5 if wdt == "fp32" else 1e-2, atol=atol,
+                                   err_msg=f"weights, table {t} (longest run {n_run}, atol {atol:.2e})")
     # determinism: a second run from the same state gives identical bits
     wg2 = w.cuda()
     momg2 = dev(mom)

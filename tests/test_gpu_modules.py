@@ -555,3 +555,59 @@ def test_train_pipeline_sparse_dist_matches_sequential(pg):
     np.testing.assert_allclose(pipe_losses, seq_losses, rtol=1e-5, atol=1e-6)
     for (k, va), (_, vb) in zip(a.state_dict().items(), b.state_dict().items()):
         torch.testing.assert_close(local_tensor(vb), local_tensor(va), rtol=1e-5, atol=1e-6, msg=k)
+
+
+def test_train_pipeline_cuda_graph_replay_matches_eager(pg):
+    """TrainPipelineSparseDist(cuda_graph=True): after the eager warm-up the step (forward, backward with the fused
+    table update) is captured once and replayed with the inputs copied into the graph's buffers; losses and final
+    weights equal the eager pipeline's on the same batches, and the replays really happened."""
+    from fbgemm_gpu.split_embedding_configs import EmbOptimType
+    from torchrec import EmbeddingBagCollection, EmbeddingBagConfig
+    from torchrec.datasets.random import RandomRecDataset
+    from torchrec.distributed import DistributedModelParallel, ShardingEnv
+    from torchrec.distributed.embedding_kernel import local_tensor
+    from torchrec.distributed.embeddingbag import EmbeddingBagCollectionSharder
+    from torchrec.distributed.train_pipeline import TrainPipelineSparseDist
+    from torchrec.models.dlrm import DLRMTrain
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda")
+    rows, D, B = [50, 7, 1000, 3], 32, 64
+    keys = [f"f{i}" for i in range(len(rows))]
+
+    def build():
+        torch.manual_seed(13)
+        ebc = EmbeddingBagCollection([EmbeddingBagConfig(name=f"t{i}", embedding_dim=D, num_embeddings=r,
+                                                         feature_names=[keys[i]]) for i, r in enumerate(rows)],
+                                     device=torch.device("meta"))
+        model = DLRMTrain(ebc, 13, [32, D], [32, 1], dense_device=dev)
+        sharders = [EmbeddingBagCollectionSharder(fused_params={"learning_rate": 0.05,
+                                                                "optimizer": EmbOptimType.EXACT_ROWWISE_ADAGRAD})]
+        dmp = DistributedModelParallel(model, env=ShardingEnv.from_process_group(pg), device=dev, sharders=sharders)
+        return dmp, torch.optim.SGD(list(dmp.parameters()), lr=0.05)
+
+    a, opt_a = build()
+    b, opt_b = build()
+    res = b.load_state_dict(a.state_dict())
+    assert not res.missing_keys and not res.unexpected_keys, res
+    ds = iter(RandomRecDataset(keys=keys, batch_size=B, hash_sizes=rows, ids_per_feature=2, num_dense=13,
+                               manual_seed=9))
+    host = [next(ds).pin_memory() for _ in range(12)]  # fixed pooling factor: every step has the same signature
+
+    def run(model, opt, graph):
+        pipe = TrainPipelineSparseDist(model, opt, dev, cuda_graph=graph, graph_warmup=3)
+        it, losses = iter(host), []
+        while True:
+            try:
+                out = pipe.progress(it)
+            except StopIteration:
+                break
+            losses.append(float(out[0]))
+        return losses, pipe
+
+    eager, _ = run(a, opt_a, False)
+    graphed, pipe = run(b, opt_b, True)
+    assert len(eager) == len(graphed) == len(host)
+    assert pipe.graph_replays >= 6, pipe.graph_replays
+    np.testing.assert_allclose(graphed, eager, rtol=1e-5, atol=1e-6)
+    for (k, va), (_, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+        torch.testing.assert_close(local_tensor(vb), local_tensor(va), rtol=1e-5, atol=1e-6, msg=k)

@@ -392,3 +392,45 @@ def test_combined_optimizer_checkpoint_is_flat_and_strict():
     sd["param_groups"][1]["lr"] = 0.5
     comb.load_state_dict(sd)
     assert o1.param_groups[0]["lr"] == 0.5 and o0.param_groups[0]["lr"] == 0.1
+
+
+def test_cuda_graph_step_signature_and_static_buffers():
+    """Host logic of TrainPipelineSparseDist's CUDA-graph mode (runs on CPU tensors): the step signature covers
+    shapes, dtypes, keys and the per-key id counts (they become pointer offsets inside a captured graph), the
+    static copy has the same structure with its own storage, and the flattened tensor lists line up one to one."""
+    from torchrec.datasets.utils import Batch
+    from torchrec.distributed.embedding_types import SparseFeatures, SparseFeaturesList
+    from torchrec.distributed.train_pipeline import _sig, _static_copy, _tensors
+    from torchrec.sparse.jagged_tensor import KeyedJaggedTensor
+
+    def kjt(lengths):
+        lengths = torch.tensor(lengths, dtype=torch.int32)
+        return KeyedJaggedTensor(keys=["a", "b"], values=torch.arange(int(lengths.sum())), lengths=lengths)
+
+    def step(lengths):
+        k = kjt(lengths)
+        batch = Batch(dense_features=torch.zeros(2, 3), sparse_features=k, labels=torch.zeros(2))
+        return (batch, [SparseFeaturesList([SparseFeatures(id_list_features=kjt(lengths))])])
+
+    a, b, c = step([1, 2, 0, 1]), step([1, 2, 0, 1]), step([1, 1, 1, 1])  # c: same total, other per-key counts
+    assert _sig(a) == _sig(b)
+    assert _sig(a) != _sig(c)
+    assert _sig(a) != _sig(step([1, 2, 0, 2]))
+    s = _static_copy(a)
+    ta, ts = _tensors(a, []), _tensors(s, [])
+    assert len(ta) == len(ts) > 0
+    for x, y in zip(ta, ts):
+        assert x.shape == y.shape and x.dtype == y.dtype and torch.equal(x, y) and x.data_ptr() != y.data_ptr()
+    assert s[0].sparse_features.length_per_key() == a[0].sparse_features.length_per_key()
+    with pytest.raises(TypeError):
+        _sig(object())
+
+
+def test_interaction_supported_shapes():
+    """InteractionArch routes shapes the kernels refuse (D % 4 != 0, or a 4-sample tile beyond 200 KB of shared
+    memory) to the plain torch formulation instead of failing at run time."""
+    import importlib
+    ops = importlib.import_module("b200_sparse.ops")
+    assert ops.interaction_supported(26, 128) and ops.interaction_supported(1, 4)
+    assert not ops.interaction_supported(26, 130)
+    assert not ops.interaction_supported(200, 512)

@@ -116,7 +116,7 @@ def tbe_bench(section, s, label, opt="rowwise_adagrad", iters=15):
     t_f = timeit(fwd, iters)
     report(section, "tbe_forward", shape, t_f, fwd_bytes)
     t_s = timeit(do_sort, iters)
-    report(section, "tbe_sort_indices (linearize + CUB radix sort)", shape, t_s, 0)
+    report(section, "tbe_sort_indices (linearize + segmented LSD radix sort)", shape, t_s, 0)
     t_b = timeit(bwd, iters)
     report(section, "tbe_backward (+rowwise Adagrad)", shape, t_b, bwd_bytes)
     report(section, "tbe fwd+bwd", shape, t_f + t_b, fwd_bytes + bwd_bytes)

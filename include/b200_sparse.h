@@ -242,7 +242,8 @@ int b200_interaction_forward(const float* dense, const float* sparse, int32_t B,
  * (B200_IX_TMA=1 routes b200_interaction_forward here). */
 int b200_interaction_forward_tma(const float* dense, const float* sparse, int32_t B, int32_t F, int32_t D,
                                  float* out, int64_t out_stride, void* stream);
-/* Backward of the same: grad_out [B, D + (F+1)F/2] at a pitch of grad_stride floats
+/* Backward of the same (autograd of the bmm + triu gather in torchrec/models/dlrm.py:205-219):
+ * grad_out [B, D + (F+1)F/2] at a pitch of grad_stride floats
  * -> grad_dense [B, D], grad_sparse [B,F,D]. */
 int b200_interaction_backward(const float* dense, const float* sparse, const float* grad_out,
                               int64_t grad_stride, int32_t B, int32_t F, int32_t D,
@@ -330,7 +331,8 @@ int b200_tbe_backward_peer(const float* const* grad_bases /*device [n_src]*/, in
                            float learning_rate, float eps, void* partial_scratch,
                            int32_t stochastic_rounding, uint64_t sr_seed, uint64_t sr_offset, void* stream);
 
-/* Row-wise sharding: out[b, out_col4[c] : +4] = sum_r stage[r][b][4c : 4c+4] (rank order) for every
+/* Row-wise sharding, the reduction half of reduce_scatter_pooled (torchrec/distributed/comm_ops.py:382,848-890;
+ * PooledEmbeddingsReduceScatter, dist_data.py:745): out[b, out_col4[c] : +4] = sum_r stage[r][b][4c : 4c+4] (rank order) for every
  * float4 column c of the stage [W][B_local][Dw] filled by the peers' b200_tbe_forward_peer;
  * out_col4 (device int32 [Dw/4], multiples of 4) places each feature anywhere in the output row.
  * clear_stage != 0: every non-zero slot read is zeroed again, ready for a skip_empty forward. */

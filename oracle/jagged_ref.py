@@ -8,7 +8,6 @@ the reference's own CPU ops compiled into oracle/_ref (tests/golden/*.npz).
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
 
 import numpy as np
 

@@ -6,7 +6,6 @@ repo's `fbgemm_gpu` package and `torch.ops.fbgemm.*` kernels, and one fused-SGD 
 unsharded EmbeddingBagCollection (nn.EmbeddingBag) on the global batch.  Nothing of this repo's torchrec mirror is
 imported: the first assertion checks where `torchrec` came from."""
 import os
-import sys
 
 import torch
 import torch.distributed as dist

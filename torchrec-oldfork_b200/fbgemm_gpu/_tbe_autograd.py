@@ -12,7 +12,7 @@ torch.ops.fbgemm like the reference's generated invokers.
 """
 from __future__ import annotations
 
-from typing import Dict, Optional, Tuple
+from typing import Dict, Optional
 
 import torch
 from torch import Tensor

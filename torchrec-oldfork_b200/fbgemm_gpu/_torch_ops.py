@@ -5,7 +5,6 @@ quantize_ops_cpu.cpp, codegen/embedding_bounds_check_host.cpp).  No CPU kernels 
 registered: a CPU tensor reaches the dispatcher and raises NotImplementedError — there is
 no CPU fallback in the product (the CPU oracle lives in tests/ only).
 """
-from typing import Optional, Tuple
 
 import torch
 

@@ -11,7 +11,6 @@ the other ten optimizers are out of scope and raise NotImplementedEr
 from __future__ import annotations
 
 import enum
-import logging
 from dataclasses import dataclass
 from itertools import accumulate
 from math import log2

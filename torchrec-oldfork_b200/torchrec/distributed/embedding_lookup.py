@@ -3,7 +3,7 @@ GroupedPooledEmbeddingsLookup :209, forward :287-337): the local KJT is split pe
 each group runs ONE table-batched lookup, outputs are concatenated along the embedding dim."""
 from __future__ import annotations
 
-from typing import Any, Dict, Iterator, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist

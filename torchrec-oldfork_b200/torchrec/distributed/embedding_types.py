@@ -2,7 +2,7 @@
 EmbeddingComputeKernel :45, ShardedEmbeddingTable, GroupedEmbeddingConfig :160, SparseFeatures)."""
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from enum import Enum, unique
 from typing import List, Optional
 

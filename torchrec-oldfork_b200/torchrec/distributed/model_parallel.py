@@ -5,7 +5,6 @@ remaining (dense) parameters, wraps them in DistributedDataParallel and collects
 optimizers of the sharded modules."""
 from __future__ import annotations
 
-from collections import OrderedDict
 from typing import Any, Dict, Iterator, List, Optional, Tuple
 
 import torch

@@ -16,7 +16,7 @@ losses to a hard-coded file on rank 0 (:538-543); here that is the optional `los
 from __future__ import annotations
 
 from collections import deque
-from typing import Callable, Deque, Generic, Iterator, List, Optional, Tuple, TypeVar
+from typing import Callable, Deque, Generic, Iterator, List, Optional, TypeVar
 
 import torch
 from torch import nn

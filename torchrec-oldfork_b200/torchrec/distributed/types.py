@@ -4,9 +4,9 @@ ShardingPlan, ModuleSharder)."""
 from __future__ import annotations
 
 import abc
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from enum import Enum, unique
-from typing import Any, Dict, Generic, Iterator, List, Optional, Tuple, Type, TypeVar
+from typing import Dict, Generic, List, Optional, Type, TypeVar
 
 import torch
 import torch.distributed as dist

@@ -434,3 +434,35 @@ def test_interaction_supported_shapes():
     assert ops.interaction_supported(26, 128) and ops.interaction_supported(1, 4)
     assert not ops.interaction_supported(26, 130)
     assert not ops.interaction_supported(200, 512)
+
+
+def test_bench_reference_arm_line_and_isolation():
+    """`bench.py --impl reference` (the CPU arm the driver times beside ours): prints ONE JSON line with the
+    contract's keys, runs the reference's own CPU kernels when oracle/_ref is built (else the C port, and says so),
+    and loads neither the product package nor libb200sparse.so."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    probe = ("import runpy, sys; sys.argv = ['bench.py', '--impl', 'reference', '--steps', '1', '--warmup', '1', "
+             "'--cpu-batch', '512', '--cpu-row-cap', '20000']; "
+             "runpy.run_path('bench.py', run_name='__main__'); "
+             "bad = [m for m in sys.modules if m.split('.')[0] in ('b200_sparse', 'fbgemm_gpu', 'torchrec')]; "
+             "maps = open('/proc/self/maps').read(); "
+             "print('LOADED', bad, 'libb200sparse' in maps)")
+    out = subprocess.run([sys.executable, "-c", probe], cwd=root, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "dlrm_train_samples_per_sec" and d["unit"] == "samples/s"
+    assert d["higher_is_better"] is True and d["steps"] == 1 and d["value"] > 0
+    assert d["e2e"] == {"value": d["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    cb = d["cpu_baseline"]
+    assert cb["value"] == d["value"] and cb["cores"] >= 1 and cb["kind"] in ("reference", "port")
+    if os.path.exists(os.path.join(root, "oracle", "_ref", "libfbgemm_tbe_ref.so")):
+        assert cb["kind"] == "reference"
+    assert d["gpu_launches"] == 0
+    loaded = [ln for ln in out.stdout.splitlines() if ln.startswith("LOADED")][0]
+    assert loaded == "LOADED [] False", loaded
